@@ -1,0 +1,310 @@
+#!/usr/bin/env python3
+"""bench.py -- the hot path's headline metric on B200.
+
+Headline (BASELINE.json `metric`): f32 GEMM GFLOP/s at 8192^2.  A "step" is one
+C = A x B of 8192 x 8192 f32 matrices through la_mul_mat_mat (A^T staging + TMA SIMT kernel),
+operands resident in HBM.  With N GPUs the 8192^2 problem is row-block sharded (A and C split by
+rows, B replicated, no data-path collective): strong scaling, value = total flop / max-over-ranks
+time.  `e2e` is the same GEMM through the public Matrix API with pinned HOST buffers (upload A, B;
+multiply; download C inside the timed region).  `extra` carries the vector-op HBM GB/s figures
+the metric also names (elementwise 2^28 f32, dot/sum, Matrix x Vector at 32768^2, i32 8192^2).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-extra]
+
+`--impl reference` times the reference's own kernels (src/kernels.cl compiled as C++ into
+oracle/_ref, all host cores) on a bounded sample of the same GEMM.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_GEMM = 8192
+METRIC = "f32_gemm_gflops_8192"
+UNIT = "GFLOP/s"
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("sm_max_mhz", 1965.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1965.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.samples, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def window(self, t0, t1):
+        rows = [s.split(", ") for t, s in self.samples if t0 - 0.05 <= t <= t1 + 0.15] or [s.split(", ") for _, s in self.samples[-3:]]
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        reasons = set()
+        for r in rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.strip().lower() == "active":
+                    reasons.add(name)
+        mx = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(rows)}
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+
+
+# ----------------------------------------------------------------------------- reference arm / cpu baseline
+def time_reference_gemm(budget_s):
+    """The reference's {T}_mul_mat_mat (kernels.cl:161-169), compiled verbatim as C++ (oracle/_ref),
+    all host cores, on the first `rows` rows of the 8192^2 product (gws = rows*8192 work-items)."""
+    import ctypes
+    import oracle
+    kind = "reference"
+    try:
+        R = oracle.ref()
+        fn = R.lib.ref_float_mul_mat_mat
+    except Exception:
+        R, fn, kind = oracle.port(), None, "port"
+    n = N_GEMM
+    rng = np.random.default_rng(1)
+    a = rng.uniform(-1, 1, n * n).astype(np.float32); b = rng.uniform(-1, 1, n * n).astype(np.float32)
+
+    def run(rows):
+        c = np.empty(rows * n, np.float32)
+        t = time.perf_counter()
+        if fn is not None:
+            fn(c.ctypes.data_as(ctypes.c_void_p), a.ctypes.data_as(ctypes.c_void_p), b.ctypes.data_as(ctypes.c_void_p),
+               ctypes.c_int(n), ctypes.c_int(n), ctypes.c_long(rows))
+        else:
+            R.lib.oracle_mul_mat_mat(8, c.ctypes.data_as(ctypes.c_void_p), a.ctypes.data_as(ctypes.c_void_p), b.ctypes.data_as(ctypes.c_void_p), rows, n, n, 0)
+        return time.perf_counter() - t
+
+    t1 = run(1)
+    rows = int(max(1, min(512, budget_s / max(t1, 1e-6))))
+    t = run(rows)
+    cores = os.cpu_count() or 1
+    return {"value": 2.0 * n * n * rows / t / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "seconds": t,
+            "sample": "first %d of %d rows of the 8192^2 f32 product (%d work-items of kernels.cl mul_mat_mat, OpenMP over work-items)" % (rows, n, rows * n)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    for _ in range(args.warmup):
+        time_reference_gemm(1.0)
+    for _ in range(args.steps):
+        vals.append(time_reference_gemm(max(2.0, 30.0 / max(1, args.steps))))
+    v = statistics.mean(x["value"] for x in vals)
+    cb = dict(vals[-1]); cb["value"] = v
+    ms = statistics.mean(x["seconds"] for x in vals) * 1e3
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": "f32 GEMM 8192x8192x8192 (bounded row sample per step)", "M": N_GEMM, "K": N_GEMM, "N": N_GEMM},
+                      "cpu_baseline": cb, "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ----------------------------------------------------------------------------- our arm
+def timed(la, fn, iters, warmup=3):
+    for _ in range(warmup):
+        fn()
+    la.synchronize()
+    e0, e1 = la.Event(), la.Event()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    return e0.elapsed_ms(e1) / iters
+
+
+def extras(la, hbm_peak, peak_src):
+    """Vector-op HBM numbers (BASELINE.json configs[1], [2], [4]); operands >> L2 (126 MB)."""
+    lib = la._lib
+    out = {}
+    n = 1 << 28
+    A = la.Vector.uninitialized(n, "f32"); B = la.Vector.uninitialized(n, "f32"); C = la.Vector.uninitialized(n, "f32")
+    one = np.array([1.0], np.float32); two = np.array([1.0000001], np.float32)
+    lib.call("la_fill", 8, A.ptr, one.ctypes.data, n, None); lib.call("la_fill", 8, B.ptr, two.ctypes.data, n, None)
+
+    def rec(name, ms, nbytes):
+        gbs = nbytes / ms / 1e6
+        out[name] = {"ms": round(ms, 4), "GB/s": round(gbs, 1), "frac_of_measured_hbm": round(gbs / hbm_peak, 3), "frac_of_nominal_8TBs": round(gbs / 8000.0, 3)}
+
+    for opname, op in (("add", 0), ("sub", 1), ("mul", 2)):
+        rec("ew_%s_f32_2^28" % opname, timed(la, lambda: lib.call("la_ew_vec_vec", 8, op, C.ptr, A.ptr, B.ptr, n, None), 10), 12 * n)
+    rec("ew_add_assign_f32_2^28", timed(la, lambda: lib.call("la_ew_assign_vec_vec", 8, 0, C.ptr, B.ptr, n, None), 10), 12 * n)
+    rec("scale_f32_2^28", timed(la, lambda: lib.call("la_ew_vec_scl", 8, 2, C.ptr, A.ptr, two.ctypes.data, n, None), 10), 8 * n)
+    res = la.Vector.uninitialized(4, "f32")
+    rec("dot_f32_2^28", timed(la, lambda: lib.call("la_dot_vec_vec_dev", 8, A.ptr, B.ptr, n, res.ptr, None), 10), 8 * n)
+    rec("sum_f32_2^28", timed(la, lambda: lib.call("la_sum_vec_dev", 8, A.ptr, n, res.ptr, None), 10), 4 * n)
+    del B, C
+    # Matrix x Vector at 32768^2 (4 GiB): reuse A's storage? allocate a fresh matrix
+    r = 32768
+    M = la.Vector.uninitialized(r * r, "f32"); v = la.Vector.uninitialized(r, "f32"); y = la.Vector.uninitialized(r, "f32")
+    lib.call("la_fill", 8, M.ptr, one.ctypes.data, r * r, None); lib.call("la_fill", 8, v.ptr, two.ctypes.data, r, None)
+    rec("mat_x_vec_f32_32768^2", timed(la, lambda: lib.call("la_mul_vec_transpose_mat", 8, y.ptr, v.ptr, M.ptr, r, r, None), 5, 2), 4 * (r * r + 2 * r))
+    rec("vec_x_mat_f32_32768^2", timed(la, lambda: lib.call("la_mul_vec_mat", 8, y.ptr, v.ptr, M.ptr, r, r, None), 5, 2), 4 * (r * r + 2 * r))
+    del M, v, y, A
+    # i32 at 8192^2: transpose + GEMM
+    k = 8192
+    X = la.Vector.uninitialized(k * k, "i32"); Y = la.Vector.uninitialized(k * k, "i32"); Z = la.Vector.uninitialized(k * k, "i32")
+    three = np.array([3], np.int32)
+    lib.call("la_fill", 5, X.ptr, three.ctypes.data, k * k, None); lib.call("la_fill", 5, Y.ptr, three.ctypes.data, k * k, None)
+    rec("transpose_i32_8192^2", timed(la, lambda: lib.call("la_transpose", 5, Z.ptr, X.ptr, k, k, None), 10), 8 * k * k)
+    ms = timed(la, lambda: lib.call("la_mul_mat_mat", 5, Z.ptr, X.ptr, Y.ptr, k, k, k, None), 3, 1)
+    out["gemm_i32_8192^2"] = {"ms": round(ms, 3), "Gop/s": round(2.0 * k ** 3 / ms / 1e6, 1)}
+    out["_hbm_peak_GB/s"] = hbm_peak
+    out["_hbm_peak_source"] = peak_src
+    return out
+
+
+def run_ours(args):
+    import linear_algebra_b200 as la
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    la.init(local)
+    lib = la._lib
+    hbm_peak, sm_max_mhz, peak_src = measured_peaks()
+    sm_count = __import__("ctypes").c_int(); lib.call("la_sm_count", __import__("ctypes").byref(sm_count))
+
+    n = N_GEMM
+    rows = n // world                              # row-block shard of A and C; B replicated
+    rng = np.random.default_rng(1000 + rank)
+    hA = la.pinned(rows * n, "f32"); hB = la.pinned(n * n, "f32"); hC = la.pinned(rows * n, "f32")
+    hA[:] = rng.uniform(-1, 1, rows * n).astype(np.float32)
+    hB[:] = np.random.default_rng(999).uniform(-1, 1, n * n).astype(np.float32)
+    A = la.Matrix.from_vec(hA, rows, n); B = la.Matrix.from_vec(hB, n, n)
+    C = la.Matrix.uninitialized(rows, n, "f32")
+
+    def step():
+        lib.call("la_mul_mat_mat", 8, C.data.ptr, A.data.ptr, B.data.ptr, rows, n, n, None)
+
+    def barrier():
+        la.synchronize()
+        if dist is not None:
+            dist.barrier()
+        la.synchronize()
+
+    sampler = ClockSampler(local); sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    e0, e1 = la.Event(), la.Event()
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    ms_total = e0.elapsed_ms(e1)
+    barrier()
+    t1 = time.time()
+    clocks = sampler.window(t0, t1)
+
+    # e2e: public API, host buffers, H2D of A and B and D2H of C inside the timed region
+    def e2e_step():
+        a = la.Matrix.from_vec(hA, rows, n); b = la.Matrix.from_vec(hB, n, n)
+        (a * b).to_vec(out=hC)
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e2e_steps = max(3, min(args.steps, 10))
+    w0 = time.perf_counter()
+    f0, f1 = la.Event(), la.Event()
+    f0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    f1.record()
+    e2e_ms = f0.elapsed_ms(f1)
+    barrier()
+    e2e_wall_ms = (time.perf_counter() - w0) * 1e3
+    e2e_ms = max(e2e_ms, e2e_wall_ms)              # host-blocking copies: the wall clock is the honest one
+    sampler.stop()
+
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms_total, e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms = float(t[0]), float(t[1])
+    ms_step = ms_total / args.steps
+    flop = 2.0 * n * n * n                         # whole job: all ranks' row blocks together
+    value = flop / ms_step / 1e6
+    e2e_value = flop / (e2e_ms / e2e_steps) / 1e6
+
+    if rank == 0:
+        simt_peak = sm_count.value * 128 * 2 * sm_max_mhz * 1e6 / 1e12        # TFLOP/s at max clock
+        per_gpu_tflops = value / world / 1e3
+        line = {
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "f32 GEMM 8192x8192x8192, C = A x B, A/C row-block sharded over %d GPU(s), B replicated" % world,
+                       "M": n, "K": n, "N": n, "rows_per_gpu": rows, "l2": "operands 768 MB >> 126 MB L2 (no flush needed)",
+                       "engine": "TMA-fed FP32 SIMT (FFMA2), A^T staged per call"},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int((rows * n + n * n) * 4), "d2h_bytes_per_step": int(rows * n * 4),
+                    "steps": e2e_steps, "api": "Matrix.from_vec(pinned) x2 -> A * B -> to_vec(pinned)"},
+            "gpu_launches": 2 * args.steps,
+            "roofline": {"bound": "fp32-fma (SIMT; MEASURED_PEAKS.json has no FP32 figure)", "achieved": round(per_gpu_tflops, 2),
+                         "peak": round(simt_peak, 2), "unit": "TFLOP/s", "frac": round(per_gpu_tflops / simt_peak, 4),
+                         "peak_source": "nominal: %d SMs x 128 lanes x 2 x %.0f MHz" % (sm_count.value, sm_max_mhz), "traffic": None,
+                         "frac_at_observed_clock": (round(per_gpu_tflops / (sm_count.value * 256 * clocks["sm_mhz"] * 1e6 / 1e12), 4) if clocks.get("sm_mhz") else None)},
+        }
+        if world == 1:
+            if not args.no_extra:
+                line["extra"] = extras(la, hbm_peak, peak_src)
+            cb = time_reference_gemm(12.0)
+            cb.pop("seconds", None)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extra", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,165 @@
+/* include/linalg_b200.h -- C ABI of liblinalg_b200.so
+ *
+ * The B200-native (sm_100a CUDA) replacement for the OpenCL layer of usbalbin/linear_algebra:
+ * everything its Vector<T>/Matrix<T> operators reach through `get_kernels::<T>()` /
+ * `cl_data::<T>()` (src/lib.rs:125-154) -- the 18 kernels of src/kernels.cl and the ocl::Buffer
+ * plumbing around them.  Plain C: pointers, sizes, enums.  No torch/C++ types cross this boundary.
+ *
+ * Conventions
+ *  - Pointers named C/A/B/data/a/b/out/in are DEVICE pointers on the current CUDA device, dense
+ *    and contiguous; matrices are row-major, element (r,c) at r*cols + c (src/matrix.rs:294,
+ *    src/kernels.cl:165-168).  Any alignment is accepted; 16-byte aligned pointers (what
+ *    la_malloc returns) take the 128-bit vectorised paths.
+ *  - Sizes are 64-bit element counts (the reference passes `as i32`, src/vector.rs:277,
+ *    src/matrix.rs:255-256; 2^31 elements and more are fine here).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Compute
+ *    entry points are stream-ordered and return without waiting unless they hand a scalar back
+ *    to the host (la_sum_vec, la_dot_vec_vec, la_eq_vec).  The reference blocks on every kernel
+ *    (event.wait_for(), src/vector.rs:108); its drop-in wrappers call la_stream_sync() after
+ *    each op to keep that behaviour.
+ *  - Every function returns la_status; LA_OK == 0.  la_last_error() gives the thread-local
+ *    message.  The library never aborts and has no CPU fallback: without a CUDA device every
+ *    compute call fails with LA_ERR_CUDA.
+ *  - Integer arithmetic wraps mod 2^n; division truncates toward zero; x/0 and MIN/-1 are
+ *    unspecified values (undefined in OpenCL C).  Floating point: add/sub/mul/div are single
+ *    IEEE operations (bit-exact with the reference); sum/dot/GEMV/GEMM accumulate in the
+ *    element type in a fixed, deterministic order that differs from the reference's
+ *    device-dependent order (tolerance: DESIGN.md).
+ *  - Thread safety: any thread may call any function; scratch memory is keyed by
+ *    (device, stream), so concurrent calls must use distinct streams.
+ */
+#ifndef LINALG_B200_H
+#define LINALG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int la_status;
+enum {
+    LA_OK = 0,
+    LA_ERR_ARG = 1,    /* null pointer, unknown dtype/op, negative size */
+    LA_ERR_SHAPE = 2,  /* shapes do not agree (the wrappers' assert_eq!, src/vector.rs:97,327,513,545) */
+    LA_ERR_DTYPE = 3,  /* operation not defined for this dtype */
+    LA_ERR_OOM = 4,    /* device allocation failed */
+    LA_ERR_CUDA = 5,   /* CUDA runtime / driver error, incl. "no device" */
+    LA_ERR_UNSUPPORTED = 6
+};
+
+/* Element types = the Rust types of `impl_type_to_str!` (src/traits.rs:30-57,76) / the OpenCL
+ * names of TYPES (src/lib.rs:84-92).  Note src/traits.rs:36 maps Rust i8 to "uchar": a drop-in
+ * wrapper passes LA_U8 for Vector<i8> to reproduce that; LA_I8 is OpenCL "char". */
+typedef enum {
+    LA_U8 = 0,  /* uchar  */
+    LA_I8 = 1,  /* char   */
+    LA_U16 = 2, /* ushort */
+    LA_I16 = 3, /* short  */
+    LA_U32 = 4, /* uint   */
+    LA_I32 = 5, /* int    */
+    LA_U64 = 6, /* ulong  (usize) */
+    LA_I64 = 7, /* long   (isize) */
+    LA_F32 = 8, /* float  */
+    LA_F64 = 9  /* double (opt-in in the reference, src/lib.rs:343-347) */
+} la_dtype;
+
+typedef enum { LA_ADD = 0, LA_SUB = 1, LA_MUL = 2, LA_DIV = 3 } la_op;
+
+/* ------------------------------------------------------------------ runtime
+ * Replaces the lazy `CL_DATA` singleton, device pick and program build of src/lib.rs:125-149,
+ * 310-335 (kernels here are compiled ahead of time for sm_100a; there is nothing to JIT). */
+la_status la_init(int device);               /* select device, create its scratch; idempotent  */
+la_status la_device_count(int* count);
+la_status la_device_name(char* buf, size_t buf_len);
+la_status la_sm_count(int* count);
+const char* la_last_error(void);             /* thread-local, never NULL                        */
+const char* la_version(void);
+size_t la_dtype_size(int dtype);             /* 0 for an unknown dtype                          */
+
+/* ------------------------------------------------------------------ buffers
+ * Replace ocl::Buffer creation / read / copy: Vector::uninitialized_lock_free
+ * (src/vector.rs:36-46), from_vec_lock_free (:58-69, COPY_HOST_PTR upload), to_vec (:71-78,
+ * blocking read), Clone (:700-708, device-to-device copy), Vector::new (:30-34, fill). */
+la_status la_malloc(void** dev_ptr, size_t bytes);                 /* 256-byte aligned; bytes==0 ok */
+la_status la_free(void* dev_ptr);
+la_status la_upload(void* dst_dev, const void* src_host, size_t bytes, void* stream);   /* async if src is pinned */
+la_status la_download(void* dst_host, const void* src_dev, size_t bytes, void* stream); /* returns after the copy */
+la_status la_copy(void* dst_dev, const void* src_dev, size_t bytes, void* stream);
+la_status la_fill(int dtype, void* dst_dev, const void* value_host, size_t n, void* stream);
+la_status la_host_alloc(void** host_ptr, size_t bytes);            /* pinned host memory */
+la_status la_host_free(void* host_ptr);
+la_status la_stream_create(void** stream);
+la_status la_stream_destroy(void* stream);
+la_status la_stream_sync(void* stream);      /* the reference's event.wait_for() */
+/* Device-side timing on the launching stream (ocl::Event profiling has no user in the
+ * reference; used by bench.py). */
+la_status la_event_create(void** event);
+la_status la_event_destroy(void* event);
+la_status la_event_record(void* event, void* stream);
+la_status la_event_elapsed_ms(void* start, void* stop, float* ms);   /* waits for `stop` */
+
+/* ------------------------------------------------------------------ elementwise
+ * {T}_add/sub/mul/div_vec_vec            src/kernels.cl:15-29   C[i] = A[i] op B[i]
+ *   host: Vector::from_for_each2_lock_free src/vector.rs:96-112 (ops :366-379,403-416,482-496,571-586)
+ * {T}_add/sub/mul/div_assign_vec_vec     src/kernels.cl:33-47   C[i] op= B[i]
+ *   host: Vector::for_each_mut src/vector.rs:114-125 (ops :381-391,418-427,498-505,588-595)
+ * {T}_mul/div_vec_scl                    src/kernels.cl:51-57   C[i] = A[i] op s
+ *   host: src/vector.rs:430-456, 598-625        (op must be LA_MUL or LA_DIV)
+ * {T}_mul/div_assign_vec_scl             src/kernels.cl:61-67   C[i] op= s
+ *   host: src/vector.rs:458-470, 627-643
+ * Matrix operators delegate to these (src/matrix.rs:134-218, 268-277).
+ * `scalar_host` points at ONE element of `dtype` in host memory (passed by value to the kernel). */
+la_status la_ew_vec_vec(int dtype, int op, void* C, const void* A, const void* B, size_t n, void* stream);
+la_status la_ew_assign_vec_vec(int dtype, int op, void* C, const void* B, size_t n, void* stream);
+la_status la_ew_vec_scl(int dtype, int op, void* C, const void* A, const void* scalar_host, size_t n, void* stream);
+la_status la_ew_assign_vec_scl(int dtype, int op, void* C, const void* scalar_host, size_t n, void* stream);
+
+/* {T}_eq_vec src/kernels.cl:71-74 + PartialEq src/vector.rs:645-675 (the 1-byte flag upload,
+ * launch, and flag download become one call).  *equal_host = 1 iff A[i] == B[i] for all i
+ * (`!=` semantics: NaN != NaN, +0 == -0); n == 0 gives 1.  Length/shape mismatch is decided by
+ * the caller without a launch (src/vector.rs:649-651, src/matrix.rs:283-285).  Blocks. */
+la_status la_eq_vec(int dtype, const void* A, const void* B, size_t n, int* equal_host, void* stream);
+
+/* ------------------------------------------------------------------ reductions
+ * {T}_sum_vec src/kernels.cl:83-102 + Vector::sum src/vector.rs:256-293 (kernel, 64-partial
+ * download and host iter::sum() become one launch); {T}_dot_vec_vec src/kernels.cl:105-124 +
+ * dot() src/vector.rs:326-363.  `out_host` / `out_dev` receive ONE element of `dtype`.
+ * The host variants block; the _dev variants are stream-ordered (used before an all-reduce). */
+la_status la_sum_vec(int dtype, const void* data, size_t n, void* out_host, void* stream);
+la_status la_dot_vec_vec(int dtype, const void* a, const void* b, size_t n, void* out_host, void* stream);
+la_status la_sum_vec_dev(int dtype, const void* data, size_t n, void* out_dev, void* stream);
+la_status la_dot_vec_vec_dev(int dtype, const void* a, const void* b, size_t n, void* out_dev, void* stream);
+
+/* ------------------------------------------------------------------ matrix x vector
+ * {T}_mul_vec_mat src/kernels.cl:143-147, host `&Vector * &Matrix` src/vector.rs:508-539:
+ *   C[col] = sum_j A[j] * B[j*cols + col],  A has `rows` elements, C has `cols`.
+ * {T}_mul_vec_transpose_mat src/kernels.cl:150-152, host mul_transpose_mat src/vector.rs:542-569:
+ *   C[r] = sum_j A[j] * B[r*cols + j],      A has `cols` elements, C has `rows`.
+ * B is the rows x cols matrix. */
+la_status la_mul_vec_mat(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream);
+la_status la_mul_vec_transpose_mat(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream);
+
+/* ------------------------------------------------------------------ matrix x matrix
+ * {T}_mul_mat_mat src/kernels.cl:161-169 (+ {T}_dot_product :134-140), host mul_helper
+ * src/matrix.rs:240-265 (`&Matrix * &Matrix` :221-232, mul_column_row :236-238 with K == 1):
+ *   C[M x N] = A[M x K] * B[K x N].  C must not alias A or B. */
+la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream);
+
+/* f32 GEMM engine: LA_GEMM_SIMT (default; FP32 FMA pipe, k-ascending per element like the
+ * reference) or LA_GEMM_3XTF32 (tcgen05 tensor cores, 3-term TF32 split with FP32 accumulate;
+ * falls back to SIMT for shapes it does not cover).  Process-wide. */
+enum { LA_GEMM_SIMT = 0, LA_GEMM_3XTF32 = 1 };
+la_status la_set_gemm_mode(int mode);
+la_status la_get_gemm_mode(int* mode);
+
+/* ------------------------------------------------------------------ transpose
+ * No counterpart in the reference (it only has mul_vec_transpose_mat); named by the
+ * north star.  out[c*rows + r] = in[r*cols + c]; out must not alias in. */
+la_status la_transpose(int dtype, void* out, const void* in, size_t rows, size_t cols, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LINALG_B200_H */

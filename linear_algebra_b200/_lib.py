@@ -1,0 +1,98 @@
+"""ctypes binding of liblinalg_b200.so (the C ABI declared in include/linalg_b200.h).
+
+There is no fallback of any kind: if the shared library is missing this module raises on
+import, and without a CUDA device every compute call raises LaError (LA_ERR_CUDA)."""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liblinalg_b200.so")
+
+LA_OK, LA_ERR_ARG, LA_ERR_SHAPE, LA_ERR_DTYPE, LA_ERR_OOM, LA_ERR_CUDA, LA_ERR_UNSUPPORTED = range(7)
+ADD, SUB, MUL, DIV = 0, 1, 2, 3
+GEMM_SIMT, GEMM_3XTF32 = 0, 1
+
+
+class LaError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__("liblinalg_b200: status %d: %s" % (status, message))
+        self.status = status
+
+
+def build():
+    """Compile the library in-tree with nvcc for sm_100a (works without a GPU)."""
+    import subprocess
+    subprocess.run(["make", "-C", os.path.join(HERE, "csrc"), "-j8"], check=True, stdout=subprocess.DEVNULL)
+
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` or "
+        "`make -C linear_algebra_b200/csrc` (there is no CPU fallback)" % LIB_PATH)
+
+lib = ctypes.CDLL(LIB_PATH)
+
+_V, _Z, _I = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int
+_PV, _PI = ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int)
+
+# name -> (argtypes); every one returns la_status except the three noted below.
+SIGNATURES = {
+    "la_init": [_I],
+    "la_device_count": [_PI],
+    "la_device_name": [ctypes.c_char_p, _Z],
+    "la_sm_count": [_PI],
+    "la_malloc": [_PV, _Z],
+    "la_free": [_V],
+    "la_upload": [_V, _V, _Z, _V],
+    "la_download": [_V, _V, _Z, _V],
+    "la_copy": [_V, _V, _Z, _V],
+    "la_fill": [_I, _V, _V, _Z, _V],
+    "la_host_alloc": [_PV, _Z],
+    "la_host_free": [_V],
+    "la_stream_create": [_PV],
+    "la_stream_destroy": [_V],
+    "la_stream_sync": [_V],
+    "la_event_create": [_PV],
+    "la_event_destroy": [_V],
+    "la_event_record": [_V, _V],
+    "la_event_elapsed_ms": [_V, _V, ctypes.POINTER(ctypes.c_float)],
+    "la_ew_vec_vec": [_I, _I, _V, _V, _V, _Z, _V],
+    "la_ew_assign_vec_vec": [_I, _I, _V, _V, _Z, _V],
+    "la_ew_vec_scl": [_I, _I, _V, _V, _V, _Z, _V],
+    "la_ew_assign_vec_scl": [_I, _I, _V, _V, _Z, _V],
+    "la_eq_vec": [_I, _V, _V, _Z, _PI, _V],
+    "la_sum_vec": [_I, _V, _Z, _V, _V],
+    "la_dot_vec_vec": [_I, _V, _V, _Z, _V, _V],
+    "la_sum_vec_dev": [_I, _V, _Z, _V, _V],
+    "la_dot_vec_vec_dev": [_I, _V, _V, _Z, _V, _V],
+    "la_mul_vec_mat": [_I, _V, _V, _V, _Z, _Z, _V],
+    "la_mul_vec_transpose_mat": [_I, _V, _V, _V, _Z, _Z, _V],
+    "la_mul_mat_mat": [_I, _V, _V, _V, _Z, _Z, _Z, _V],
+    "la_set_gemm_mode": [_I],
+    "la_get_gemm_mode": [_PI],
+    "la_transpose": [_I, _V, _V, _Z, _Z, _V],
+}
+NON_STATUS = {"la_last_error": ctypes.c_char_p, "la_version": ctypes.c_char_p, "la_dtype_size": ctypes.c_size_t}
+
+for _name, _args in SIGNATURES.items():
+    _f = getattr(lib, _name)
+    _f.argtypes = _args
+    _f.restype = ctypes.c_int
+lib.la_last_error.argtypes = []
+lib.la_last_error.restype = ctypes.c_char_p
+lib.la_version.argtypes = []
+lib.la_version.restype = ctypes.c_char_p
+lib.la_dtype_size.argtypes = [_I]
+lib.la_dtype_size.restype = ctypes.c_size_t
+# tuning hook (not declared in the public header)
+lib.la_gemm_set_variant.argtypes = [_I]
+lib.la_gemm_set_variant.restype = ctypes.c_int
+
+
+def check(status):
+    if status != LA_OK:
+        raise LaError(status, lib.la_last_error().decode("utf-8", "replace"))
+
+
+def call(name, *args):
+    check(getattr(lib, name)(*args))

@@ -1,0 +1,148 @@
+// csrc/common.cuh -- shared pieces of liblinalg_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <type_traits>
+#include "../../include/linalg_b200.h"
+
+// ---------------------------------------------------------------- errors
+void la_set_error(const char* fmt, ...);
+la_status la_fail(la_status code, const char* fmt, ...);
+la_status la_cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define LA_CUDA(call)                                                       \
+    do {                                                                    \
+        cudaError_t e_ = (call);                                            \
+        if (e_ != cudaSuccess) return la_cuda_fail(e_, #call, __FILE__, __LINE__); \
+    } while (0)
+
+#define LA_TRY(call)                           \
+    do {                                       \
+        la_status s_ = (call);                 \
+        if (s_ != LA_OK) return s_;            \
+    } while (0)
+
+// Launch check: configuration errors surface here, execution errors at the next sync.
+#define LA_LAUNCH_CHECK() LA_CUDA(cudaGetLastError())
+
+// ---------------------------------------------------------------- runtime state
+struct LaDeviceInfo {
+    int device;
+    int sm_count;
+    int max_smem_optin;
+};
+la_status la_ensure_init(LaDeviceInfo** info);   // lazily binds the current device
+
+// Scratch: global memory beyond a kernel's inputs and outputs (reduction partials, tickets,
+// GEMV strip partials, eq flags).  One growing block per (device, stream); contents undefined
+// except for the first LA_SCRATCH_ZEROED bytes, which every kernel leaves zeroed on exit
+// (tickets / flags).
+enum { LA_SCRATCH_ZEROED = 256 };
+la_status la_scratch(cudaStream_t stream, size_t bytes, void** ptr);
+
+// ---------------------------------------------------------------- dtype traits
+template <typename T> struct Arith {                       // wrap-safe arithmetic
+    using U = typename std::make_unsigned<T>::type;        // same width, unsigned
+    using Acc = typename std::conditional<(sizeof(T) < 4), uint32_t, U>::type;  // accumulators
+    static __host__ __device__ __forceinline__ T add(T a, T b) { return (T)((U)a + (U)b); }
+    static __host__ __device__ __forceinline__ T sub(T a, T b) { return (T)((U)a - (U)b); }
+    static __host__ __device__ __forceinline__ T mul(T a, T b) { return (T)((U)a * (U)b); }
+    static __host__ __device__ __forceinline__ T div(T a, T b) { return (T)(a / b); }
+    static __host__ __device__ __forceinline__ Acc to_acc(T a) { return (Acc)(U)a; }    // zero- or sign-agnostic: mod 2^n
+    static __host__ __device__ __forceinline__ Acc widen(T a) { return (Acc)a; }        // value-preserving (sign-extends)
+    static __host__ __device__ __forceinline__ T from_acc(Acc a) { return (T)a; }
+    static __host__ __device__ __forceinline__ Acc fma(T a, T b, Acc c) { return (Acc)a * (Acc)b + c; }
+    static __host__ __device__ __forceinline__ bool ne(T a, T b) { return a != b; }
+};
+template <> struct Arith<float> {
+    using U = float; using Acc = float;
+    static __host__ __device__ __forceinline__ float add(float a, float b) { return a + b; }
+    static __host__ __device__ __forceinline__ float sub(float a, float b) { return a - b; }
+    static __host__ __device__ __forceinline__ float mul(float a, float b) { return a * b; }
+    static __host__ __device__ __forceinline__ float div(float a, float b) { return a / b; }
+    static __host__ __device__ __forceinline__ float widen(float a) { return a; }
+    static __host__ __device__ __forceinline__ float from_acc(float a) { return a; }
+    static __device__ __forceinline__ float fma(float a, float b, float c) { return fmaf(a, b, c); }
+    static __host__ __device__ __forceinline__ bool ne(float a, float b) { return a != b; }
+};
+template <> struct Arith<double> {
+    using U = double; using Acc = double;
+    static __host__ __device__ __forceinline__ double add(double a, double b) { return a + b; }
+    static __host__ __device__ __forceinline__ double sub(double a, double b) { return a - b; }
+    static __host__ __device__ __forceinline__ double mul(double a, double b) { return a * b; }
+    static __host__ __device__ __forceinline__ double div(double a, double b) { return a / b; }
+    static __host__ __device__ __forceinline__ double widen(double a) { return a; }
+    static __host__ __device__ __forceinline__ double from_acc(double a) { return a; }
+    static __device__ __forceinline__ double fma(double a, double b, double c) { return ::fma(a, b, c); }
+    static __host__ __device__ __forceinline__ bool ne(double a, double b) { return a != b; }
+};
+
+template <typename T, int OP> struct ApplyOp {
+    static __device__ __forceinline__ T apply(T a, T b) {
+        if (OP == LA_ADD) return Arith<T>::add(a, b);
+        if (OP == LA_SUB) return Arith<T>::sub(a, b);
+        if (OP == LA_MUL) return Arith<T>::mul(a, b);
+        return Arith<T>::div(a, b);
+    }
+};
+
+// dtype -> C++ type dispatch.  F is a generic lambda taking a value-initialised T.
+#define LA_DISPATCH_DTYPE(dtype, T, ...)                                         \
+    switch (dtype) {                                                             \
+    case LA_U8:  { using T = uint8_t;  __VA_ARGS__; } break;                     \
+    case LA_I8:  { using T = int8_t;   __VA_ARGS__; } break;                     \
+    case LA_U16: { using T = uint16_t; __VA_ARGS__; } break;                     \
+    case LA_I16: { using T = int16_t;  __VA_ARGS__; } break;                     \
+    case LA_U32: { using T = uint32_t; __VA_ARGS__; } break;                     \
+    case LA_I32: { using T = int32_t;  __VA_ARGS__; } break;                     \
+    case LA_U64: { using T = uint64_t; __VA_ARGS__; } break;                     \
+    case LA_I64: { using T = int64_t;  __VA_ARGS__; } break;                     \
+    case LA_F32: { using T = float;    __VA_ARGS__; } break;                     \
+    case LA_F64: { using T = double;   __VA_ARGS__; } break;                     \
+    default: return la_fail(LA_ERR_ARG, "unknown dtype %d", (int)(dtype));       \
+    }
+
+static inline bool la_valid_dtype(int d) { return d >= LA_U8 && d <= LA_F64; }
+static inline bool la_aligned16(const void* p) { return (((uintptr_t)p) & 15u) == 0; }
+
+// ---------------------------------------------------------------- 128-bit streaming access
+// One 16-byte packet of T.  Streaming (evict-first) loads/stores: every hot-path operand of the
+// HBM-bound kernels is touched exactly once.
+template <typename T> struct alignas(16) Pack {
+    static constexpr int N = 16 / sizeof(T);
+    T v[N];
+};
+template <typename T> __device__ __forceinline__ Pack<T> ld_stream(const Pack<T>* p) {
+    uint4 r = __ldcs(reinterpret_cast<const uint4*>(p));
+    return *reinterpret_cast<Pack<T>*>(&r);
+}
+template <typename T> __device__ __forceinline__ void st_stream(Pack<T>* p, const Pack<T>& x) {
+    __stcs(reinterpret_cast<uint4*>(p), *reinterpret_cast<const uint4*>(&x));
+}
+template <typename T> __device__ __forceinline__ Pack<T> ld_cached(const Pack<T>* p) {
+    uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
+    return *reinterpret_cast<Pack<T>*>(&r);
+}
+
+// ---------------------------------------------------------------- warp / block reductions
+template <typename A> __device__ __forceinline__ A warp_sum(A v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// All threads of the block must call; result valid in thread 0.  `smem` holds >= 32 A's.
+// Fixed shape => deterministic floating-point result for a given block size.
+template <typename A> __device__ __forceinline__ A block_sum(A v, A* smem) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    A r = A(0);
+    if (warp == 0) {
+        r = lane < nwarps ? smem[lane] : A(0);
+        r = warp_sum(r);
+    }
+    __syncthreads();
+    return r;
+}

@@ -1,0 +1,399 @@
+// csrc/gemm.cu -- Matrix x Matrix.
+//
+// Replaces {T}_mul_mat_mat (src/kernels.cl:161-169) and its serial {T}_dot_product
+// (src/kernels.cl:134-140), launched by mul_helper (src/matrix.rs:240-265).  The reference
+// runs one work-item per C element with two global loads per multiply-add and no reuse.
+//
+// Two engines here:
+//  * gemm_tma_kernel  (4-byte element types, M % 4 == 0, N % 4 == 0, 16-byte aligned bases):
+//      TMA-fed, shared-memory-staged, register-tiled SIMT kernel.  A dedicated producer warp
+//      issues cp.async.bulk.tensor.2d loads of a [BK x BM] slab of A^T and a [BK x BN] slab of
+//      B into a STAGES-deep ring guarded by full/empty mbarriers; 8 consumer warps read both
+//      operands k-major with conflict-free LDS.128 and keep a TM x TN accumulator tile per
+//      thread.  f32 uses the sm_100 packed FFMA2 (two FMAs per issued instruction); integers
+//      use IMAD and wrap.  Each C element is accumulated k-ascending with one fused
+//      multiply-add per k -- the reference's order (kernels.cl:136-138) with contraction.
+//      A^T is produced once per call by the transpose kernel into scratch (8 B/element of A,
+//      <1% of the GEMM time at 8192^2), so both operand fragments are contiguous in k-major
+//      shared memory; edge tiles rely on TMA's out-of-bounds zero fill.
+//  * gemm_generic_kernel (every dtype, any shape / alignment): 64x64x16 shared-memory tiling
+//      with guarded scalar loads.  8/16-bit integers accumulate in 32 bits and truncate.
+//
+// Roofline: FP32 FMA pipe (f32), integer multiply-add pipe (i32/u32).  Work: 2*M*N*K flop.
+#include "common.cuh"
+#include <cuda.h>
+#include <mutex>
+
+la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st);   // transpose.cu
+
+namespace {
+
+// ------------------------------------------------------------------ generic engine
+constexpr int GG_BM = 64, GG_BN = 64, GG_BK = 16, GG_THREADS = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(GG_THREADS)
+gemm_generic_kernel(T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ B, size_t M, size_t K, size_t N, unsigned tiles_n) {
+    using Acc = typename Arith<T>::Acc;
+    __shared__ T As[GG_BK][GG_BM + 4];     // k-major
+    __shared__ T Bs[GG_BK][GG_BN + 4];
+    const size_t m0 = (size_t)(blockIdx.x / tiles_n) * GG_BM, n0 = (size_t)(blockIdx.x % tiles_n) * GG_BN;
+    const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;     // 16 x 16 threads, 4 x 4 outputs each
+    Acc acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = Acc(0);
+
+    for (size_t k0 = 0; k0 < K; k0 += GG_BK) {
+        // A tile: 64 rows x 16 k  -> As[k][m];  B tile: 16 k x 64 cols -> Bs[k][n]
+#pragma unroll
+        for (int idx = threadIdx.x; idx < GG_BM * GG_BK; idx += GG_THREADS) {
+            const int m = idx / GG_BK, k = idx % GG_BK;
+            As[k][m] = (m0 + m < M && k0 + k < K) ? A[(m0 + m) * K + k0 + k] : T(0);
+        }
+#pragma unroll
+        for (int idx = threadIdx.x; idx < GG_BK * GG_BN; idx += GG_THREADS) {
+            const int k = idx / GG_BN, n = idx % GG_BN;
+            Bs[k][n] = (k0 + k < K && n0 + n < N) ? B[(k0 + k) * N + n0 + n] : T(0);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < GG_BK; ++k) {
+            T a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[k][ty * 4 + i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[k][tx * 4 + j];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = Arith<T>::fma(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const size_t m = m0 + ty * 4 + i, n = n0 + tx * 4 + j;
+            if (m < M && n < N) C[m * N + n] = Arith<T>::from_acc(acc[i][j]);
+        }
+}
+
+template <typename T>
+la_status gemm_generic(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, cudaStream_t st) {
+    const size_t tm = (M + GG_BM - 1) / GG_BM, tn = (N + GG_BN - 1) / GG_BN;
+    if (tm * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "mul_mat_mat: %zu x %zu output is too large", M, N);
+    gemm_generic_kernel<T><<<(unsigned)(tm * tn), GG_THREADS, 0, st>>>(C, A, B, M, K, N, (unsigned)tn);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
+// ------------------------------------------------------------------ TMA-fed SIMT engine
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// Bounded wait: a broken pipeline traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (!done && spin > (1u << 22)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
+}
+
+template <typename T> struct Mac;       // multiply-accumulate on the 4-byte element types
+template <> struct Mac<float> {
+    using Acc = float;
+    static __device__ __forceinline__ void mac(float& c, float a, float b) { c = fmaf(a, b, c); }
+};
+template <> struct Mac<uint32_t> {
+    using Acc = uint32_t;
+    static __device__ __forceinline__ void mac(uint32_t& c, uint32_t a, uint32_t b) { c += a * b; }
+};
+
+// Geometry: lanes are 4 (m) x 8 (n); a thread's TM rows are TM/4 chunks of 4 rows, 16 rows
+// apart; its TN columns are TN/4 chunks of 4 columns, 32 columns apart.  So an A fragment load
+// is a broadcast within each quarter-warp and a B fragment load is 128 contiguous bytes per
+// quarter-warp: both conflict-free LDS.128.
+template <int TM_, int TN_, int WARPS_M_, int WARPS_N_, int BK_, int STAGES_, int MIN_BLOCKS_, int CONSUMER_REGS_>
+struct GemmShape {
+    static constexpr int TM = TM_, TN = TN_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, BK = BK_, STAGES = STAGES_;
+    static constexpr int MIN_BLOCKS = MIN_BLOCKS_, CONSUMER_REGS = CONSUMER_REGS_, PRODUCER_REGS = 24;
+    static constexpr int WM = 4 * TM, WN = 8 * TN;
+    static constexpr int BM = WARPS_M * WM, BN = WARPS_N * WN;
+    static constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
+    static_assert(CONSUMER_WARPS == 8, "two consumer warpgroups");
+    // 8 consumer warps + one producer warpgroup (setmaxnreg moves registers between whole
+    // warpgroups; a 9th lone warp would put 3 warps on one SM sub-partition and cap everyone
+    // at 168 registers).
+    static constexpr int THREADS = (CONSUMER_WARPS + 4) * 32;
+    static constexpr int STAGE_ELEMS = (BM + BN) * BK;
+    static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_ELEMS * 4;
+    static_assert((128 * PRODUCER_REGS + 256 * CONSUMER_REGS) * MIN_BLOCKS <= 65536, "register file");
+};
+
+template <typename T, typename S, bool PACKED>
+__global__ void __launch_bounds__(S::THREADS, S::MIN_BLOCKS)
+gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, const __grid_constant__ CUtensorMap map_b,
+                int M, int N, int K, int tiles_m) {
+    constexpr int TM = S::TM, TN = S::TN, BK = S::BK, BM = S::BM, BN = S::BN, STAGES = S::STAGES;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ alignas(8) uint64_t full_bar[STAGES];
+    __shared__ alignas(8) uint64_t empty_bar[STAGES];
+    T* smem = reinterpret_cast<T*>(smem_raw);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = (blockIdx.x % tiles_m) * BM, n0 = (blockIdx.x / tiles_m) * BN;
+    const int num_kb = (K + BK - 1) / BK;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], S::CONSUMER_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp >= S::CONSUMER_WARPS) {
+        // ---------------- producer warpgroup: gives its registers away, one lane drives TMA
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(S::PRODUCER_REGS));
+        if (warp == S::CONSUMER_WARPS && lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                mbar_wait(&empty_bar[s], ph ^ 1u);
+                T* as = smem + (size_t)s * S::STAGE_ELEMS;
+                T* bs = as + BM * BK;
+                mbar_expect_tx(&full_bar[s], (uint32_t)(S::STAGE_ELEMS * 4));
+                tma_load_2d(as, &map_at, &full_bar[s], m0, kb * BK);      // A^T slab: BK rows of BM
+                tma_load_2d(bs, &map_b, &full_bar[s], n0, kb * BK);       // B slab:   BK rows of BN
+            }
+        }
+        return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(S::CONSUMER_REGS));
+
+    // ---------------- consumer warps
+    using Acc = typename Mac<T>::Acc;
+    const int wm = warp % S::WARPS_M, wn = warp / S::WARPS_M;
+    const int mi = lane >> 3, ni = lane & 7;
+    const int a_off = wm * S::WM + mi * 4;        // + cm*16
+    const int b_off = wn * S::WN + ni * 4;        // + cn*32
+
+    Acc acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = Acc(0);
+
+    for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        const T* as = smem + (size_t)s * S::STAGE_ELEMS + a_off;
+        const T* bs = smem + (size_t)s * S::STAGE_ELEMS + BM * BK + b_off;
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            T a[TM], b[TN];
+#pragma unroll
+            for (int cm = 0; cm < TM / 4; ++cm)
+                *reinterpret_cast<uint4*>(&a[cm * 4]) = *reinterpret_cast<const uint4*>(as + k * BM + cm * 16);
+#pragma unroll
+            for (int cn = 0; cn < TN / 4; ++cn)
+                *reinterpret_cast<uint4*>(&b[cn * 4]) = *reinterpret_cast<const uint4*>(bs + k * BN + cn * 32);
+            if constexpr (PACKED) {
+                // f32 only: two FMAs per issued FFMA2.  Pairs run along the longer side of the
+                // thread tile so that only the shorter fragment has to be duplicated.
+                if constexpr (TM >= TN) {
+#pragma unroll
+                    for (int j = 0; j < TN; ++j) {
+                        const float2 bb = make_float2(b[j], b[j]);
+#pragma unroll
+                        for (int i = 0; i < TM; i += 2) {
+                            float2 c = make_float2(acc[i][j], acc[i + 1][j]);
+                            c = __ffma2_rn(make_float2(a[i], a[i + 1]), bb, c);
+                            acc[i][j] = c.x; acc[i + 1][j] = c.y;
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < TM; ++i) {
+                        const float2 aa = make_float2(a[i], a[i]);
+#pragma unroll
+                        for (int j = 0; j < TN; j += 2) {
+                            float2 c = make_float2(acc[i][j], acc[i][j + 1]);
+                            c = __ffma2_rn(aa, make_float2(b[j], b[j + 1]), c);
+                            acc[i][j] = c.x; acc[i][j + 1] = c.y;
+                        }
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < TM; ++i)
+#pragma unroll
+                    for (int j = 0; j < TN; ++j) Mac<T>::mac(acc[i][j], a[i], b[j]);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
+    }
+
+    // ---------------- epilogue: 16-byte stores, 128 contiguous bytes per quarter-warp
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+        const int m = m0 + a_off + (i / 4) * 16 + (i % 4);
+        if (m < M) {
+#pragma unroll
+            for (int cn = 0; cn < TN / 4; ++cn) {
+                const int n = n0 + b_off + cn * 32;
+                if (n < N) {   // N % 4 == 0: a 4-column chunk is wholly inside or outside
+                    uint4 v;
+                    memcpy(&v, &acc[i][cn * 4], 16);
+                    __stcs(reinterpret_cast<uint4*>(C + (size_t)m * N + n), v);
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+la_status get_encode(EncodeTiledFn* out) {
+    static EncodeTiledFn fn = nullptr;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        LA_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (q != cudaDriverEntryPointSuccess || !p) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+        fn = (EncodeTiledFn)p;
+    }
+    *out = fn;
+    return LA_OK;
+}
+
+// 2-D row-major tensor of 4-byte elements: `rows` x `cols`, box `box_rows` x `box_cols`.
+la_status make_map(CUtensorMap* map, const void* base, size_t rows, size_t cols, int box_rows, int box_cols, bool is_float) {
+    EncodeTiledFn enc; LA_TRY(get_encode(&enc));
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, is_float ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base),
+                     dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%zu cols=%zu box=%dx%d)", (int)r, rows, cols, box_rows, box_cols);
+    return LA_OK;
+}
+
+int g_gemm_variant = 0;     // la_gemm_set_variant (tuning hook, not part of the reference surface)
+
+template <typename T, typename S, bool PACKED>
+la_status gemm_tma_launch(T* C, const T* At, const T* B, size_t M, size_t K, size_t N, cudaStream_t st) {
+    CUtensorMap map_at, map_b;
+    LA_TRY(make_map(&map_at, At, K, M, S::BK, S::BM, std::is_same<T, float>::value));
+    LA_TRY(make_map(&map_b, B, K, N, S::BK, S::BN, std::is_same<T, float>::value));
+    auto kern = gemm_tma_kernel<T, S, PACKED>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM_BYTES));
+    const size_t tm = (M + S::BM - 1) / S::BM, tn = (N + S::BN - 1) / S::BN;
+    kern<<<(unsigned)(tm * tn), S::THREADS, S::SMEM_BYTES, st>>>(C, map_at, map_b, (int)M, (int)N, (int)K, (int)tm);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
+//                        TM  TN  WM WN  BK ST  blocks/SM  consumer regs
+using Shape_16x8  = GemmShape<16,  8, 4, 2, 16, 4, 1, 240>;    // 256 x 128 block
+using Shape_16x8b = GemmShape<16,  8, 2, 4, 16, 4, 1, 240>;    // 128 x 256 block
+using Shape_8x16  = GemmShape< 8, 16, 4, 2, 16, 4, 1, 240>;    // 128 x 256 block
+using Shape_16x8k = GemmShape<16,  8, 4, 2,  8, 8, 1, 240>;    // 256 x 128 block, BK 8
+using Shape_8x8   = GemmShape< 8,  8, 4, 2, 16, 4, 2, 112>;    // 128 x 128 block, two per SM
+using Shape_8x8s  = GemmShape< 8,  8, 4, 2, 16, 6, 1, 240>;    // 128 x 128 block, one per SM
+
+template <typename T>
+la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, cudaStream_t st) {
+    // A^T (K x M) into scratch
+    void* scratch; LA_TRY(la_scratch(st, M * K * 4, &scratch));
+    T* At = (T*)((char*)scratch + LA_SCRATCH_ZEROED);
+    LA_TRY(la_transpose_raw32((uint32_t*)At, (const uint32_t*)A, M, K, st));
+    constexpr bool F = std::is_same<T, float>::value;
+    switch (g_gemm_variant) {
+    default:
+    case 0: return gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);
+    case 1: return gemm_tma_launch<T, Shape_16x8, false>(C, At, B, M, K, N, st);
+    case 2: return gemm_tma_launch<T, Shape_8x8, F>(C, At, B, M, K, N, st);
+    case 3: return gemm_tma_launch<T, Shape_8x8, false>(C, At, B, M, K, N, st);
+    case 4: return gemm_tma_launch<T, Shape_8x16, F>(C, At, B, M, K, N, st);
+    case 5: return gemm_tma_launch<T, Shape_16x8b, F>(C, At, B, M, K, N, st);
+    case 6: return gemm_tma_launch<T, Shape_16x8k, F>(C, At, B, M, K, N, st);
+    case 7: return gemm_tma_launch<T, Shape_8x8s, F>(C, At, B, M, K, N, st);
+    case 8: return gemm_tma_launch<T, Shape_8x16, false>(C, At, B, M, K, N, st);
+    }
+}
+
+int g_gemm_mode = LA_GEMM_SIMT;
+
+}  // namespace
+
+la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled);   // gemm_tc.cu
+
+extern "C" la_status la_set_gemm_mode(int mode) {
+    if (mode != LA_GEMM_SIMT && mode != LA_GEMM_3XTF32) return la_fail(LA_ERR_ARG, "unknown GEMM mode %d", mode);
+    g_gemm_mode = mode;
+    return LA_OK;
+}
+extern "C" la_status la_get_gemm_mode(int* mode) {
+    if (!mode) return la_fail(LA_ERR_ARG, "mode is NULL");
+    *mode = g_gemm_mode;
+    return LA_OK;
+}
+// Tuning hook used by tools/ and bench.py --sweep: picks the tile shape of the TMA engine
+// (0 = default).  -1 forces the generic engine.
+extern "C" la_status la_gemm_set_variant(int v) { g_gemm_variant = v; return LA_OK; }
+
+extern "C" la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream) {
+    if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: unknown dtype %d", dtype);
+    if (M == 0 || N == 0) return LA_OK;
+    if (!C || !A || !B) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: NULL operand");
+    if (C == A || C == B) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: C must not alias A or B");
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (K == 0) { LA_CUDA(cudaMemsetAsync(C, 0, M * N * la_dtype_size(dtype), st)); return LA_OK; }
+
+    const bool four_byte = (dtype == LA_F32 || dtype == LA_U32 || dtype == LA_I32);
+    const bool tma_ok = four_byte && g_gemm_variant >= 0 && M % 4 == 0 && N % 4 == 0 && la_aligned16(A) && la_aligned16(B) && la_aligned16(C) &&
+                        M >= 64 && N >= 64 && K >= 16 && M < (1u << 31) && N < (1u << 31) && K < (1u << 31);
+    if (dtype == LA_F32 && g_gemm_mode == LA_GEMM_3XTF32) {
+        bool handled = false;
+        LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
+        if (handled) return LA_OK;
+    }
+    if (tma_ok) {
+        if (dtype == LA_F32) return gemm_tma<float>((float*)C, (const float*)A, (const float*)B, M, K, N, st);
+        return gemm_tma<uint32_t>((uint32_t*)C, (const uint32_t*)A, (const uint32_t*)B, M, K, N, st);   // i32 == u32 mod 2^32
+    }
+    LA_DISPATCH_DTYPE(dtype, T, return gemm_generic<T>((T*)C, (const T*)A, (const T*)B, M, K, N, st));
+    return LA_OK;
+}

@@ -1,0 +1,122 @@
+"""Matrix: host-side mirror of the reference's `Matrix<T>` (src/matrix.rs): a Vector of
+rows*cols elements plus the two counts, dense row-major (matrix.rs:9-13)."""
+from . import vector as _v
+from ._lib import call
+from .vector import Vector
+
+
+class Matrix:
+    __slots__ = ("data", "row_count", "col_count")
+    __hash__ = None
+
+    def __init__(self, data, row_count, col_count):
+        self.data, self.row_count, self.col_count = data, int(row_count), int(col_count)
+
+    # ---- construction (matrix.rs:16-66)
+    @staticmethod
+    def new(default_value, row_count, col_count, dtype):
+        return Matrix(Vector.new(default_value, row_count * col_count, dtype), row_count, col_count)
+
+    @staticmethod
+    def uninitialized(row_count, col_count, dtype):
+        return Matrix(Vector.uninitialized(row_count * col_count, dtype), row_count, col_count)
+
+    @staticmethod
+    def from_vec(v, row_count, col_count, dtype=None):
+        data = Vector.from_vec(v, dtype)
+        assert data.len() == row_count * col_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (data.len(), row_count * col_count)
+        return Matrix(data, row_count, col_count)
+
+    @property
+    def dtype(self):
+        return self.data.dtype
+
+    def len(self):
+        return (self.row_count, self.col_count)
+
+    def get_row_count(self):
+        return self.row_count
+
+    def get_col_count(self):
+        return self.col_count
+
+    def to_vec(self, out=None):
+        return self.data.to_vec(out)
+
+    def clone(self):
+        return Matrix(self.data.clone(), self.row_count, self.col_count)
+
+    def _check_shape(self, other):
+        assert isinstance(other, Matrix), "expected a Matrix"
+        assert self.row_count == other.row_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (self.row_count, other.row_count)
+        assert self.col_count == other.col_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (self.col_count, other.col_count)
+
+    # ---- elementwise operators delegate to Vector (matrix.rs:134-218, 268-277)
+    def __add__(self, other):
+        self._check_shape(other)
+        return Matrix(self.data + other.data, self.row_count, self.col_count)
+
+    def __iadd__(self, other):
+        self._check_shape(other)
+        self.data += other.data
+        return self
+
+    def __sub__(self, other):
+        self._check_shape(other)
+        return Matrix(self.data - other.data, self.row_count, self.col_count)
+
+    def __isub__(self, other):
+        self._check_shape(other)
+        self.data -= other.data
+        return self
+
+    def __mul__(self, other):
+        if isinstance(other, Matrix):             # matrix.rs:221-232
+            assert self.col_count == other.row_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (self.col_count, other.row_count)
+            return _mul_helper(self.data, other.data, self.row_count, self.col_count, other.col_count)
+        return Matrix(self.data * other, self.row_count, self.col_count)     # scale, matrix.rs:195-204
+
+    def __imul__(self, scalar):
+        assert not isinstance(scalar, (Matrix, Vector)), "`*=` takes a scalar (matrix.rs:206-210)"
+        self.data *= scalar
+        return self
+
+    def __truediv__(self, scalar):                # matrix.rs:268-277
+        assert not isinstance(scalar, (Matrix, Vector)), "`/` takes a scalar"
+        return Matrix(self.data / scalar, self.row_count, self.col_count)
+
+    def __eq__(self, other):                      # matrix.rs:279-287
+        if not isinstance(other, Matrix):
+            return NotImplemented
+        return self.row_count == other.row_count and self.col_count == other.col_count and self.data == other.data
+
+    def __ne__(self, other):
+        r = self.__eq__(other)
+        return r if r is NotImplemented else not r
+
+    def transpose(self):
+        """Not in the reference; named by the north star: out[c*rows + r] = in[r*cols + c]."""
+        res = Matrix.uninitialized(self.col_count, self.row_count, self.dtype)
+        call("la_transpose", self.dtype.code, res.data.ptr, self.data.ptr, self.row_count, self.col_count, _v._STREAM)
+        _v._done()
+        return res
+
+    def __repr__(self):                           # matrix.rs:289-317
+        v = self.to_vec()
+        rows = ["\t " + ", ".join(repr(x.item()) for x in v[r * self.col_count:(r + 1) * self.col_count]) for r in range(self.row_count)]
+        return "Mat%dx%d {\n%s\n}\n" % (self.row_count, self.col_count, "\n".join(rows))
+
+    __str__ = __repr__
+
+
+def _mul_helper(a, b, a_row_count, a_col_count, b_col_count):     # matrix.rs:240-265
+    assert a.dtype.code == b.dtype.code, "element types differ"
+    res = Matrix.uninitialized(a_row_count, b_col_count, a.dtype)
+    call("la_mul_mat_mat", a.dtype.code, res.data.ptr, a.ptr, b.ptr, a_row_count, a_col_count, b_col_count, _v._STREAM)
+    _v._done()
+    return res
+
+
+def mul_column_row(column, row):                  # matrix.rs:236-238
+    """Outer product: column (as an n x 1 matrix) times row (as a 1 x m matrix)."""
+    return _mul_helper(column, row, column.len(), 1, row.len())

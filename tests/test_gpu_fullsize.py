@@ -1,0 +1,107 @@
+"""Parity at BASELINE.json's full sizes, through size-independent properties (the oracle would
+take minutes to hours there): sampled entries against the f64/integer truth on the host,
+involution of transpose, checksum-of-checksums for integer elementwise ops, Freivalds' check for
+the integer GEMM (exact mod 2^32) and sampled f64 dot products for the f32 GEMM."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def la():
+    import linear_algebra_b200 as la
+    la.init(0)
+    return la
+
+
+def test_elementwise_256M_f32(la):             # configs[1]
+    n = 1 << 28
+    rng = np.random.default_rng(100)
+    a = rng.random(n, dtype=np.float32); b = rng.random(n, dtype=np.float32) + np.float32(1.0)
+    A = la.Vector.from_vec(a); B = la.Vector.from_vec(b)
+    idx = rng.integers(0, n, 1 << 20); idx[:4] = (0, 1, n - 2, n - 1)
+    for got, expect in ((A + B, a[idx] + b[idx]), (A - B, a[idx] - b[idx]), (A * B, a[idx] * b[idx]), (A / B, a[idx] / b[idx]),
+                        (A * np.float32(1.5), a[idx] * np.float32(1.5))):
+        h = got.to_vec()
+        assert h[idx].tobytes() == expect.tobytes()
+        del got
+    C = A.clone(); C += B; C -= B      # not exact in floating point, but close; checks the in-place forms run at size
+    h = C.to_vec()
+    assert np.max(np.abs(h[idx] - a[idx])) <= 2.5e-7
+    # dot/sum at 2^28 against f64 (pairwise-style accumulation keeps f32 error tiny)
+    d = float(la.dot(A, B)); t = float(np.dot(a.astype(np.float64), b.astype(np.float64)))
+    assert abs(d - t) <= 2e-6 * t
+    s = float(A.sum()); t = float(a.sum(dtype=np.float64))
+    assert abs(s - t) <= 2e-6 * t
+
+
+def test_integer_8192_square(la):              # configs[4]: i32 elementwise + GEMM + transpose at 8192^2
+    n = 8192
+    rng = np.random.default_rng(101)
+    a = rng.integers(-2**31, 2**31 - 1, n * n, dtype=np.int32, endpoint=True)
+    b = rng.integers(-2**31, 2**31 - 1, n * n, dtype=np.int32, endpoint=True)
+    A = la.Matrix.from_vec(a, n, n); B = la.Matrix.from_vec(b, n, n)
+    au = a.view(np.uint32).astype(np.uint64); bu = b.view(np.uint32).astype(np.uint64)
+    M32 = np.uint64(0xFFFFFFFF)
+    # elementwise: checksum of checksums, exact mod 2^32
+    sa = int(au.sum() & M32); sb = int(bu.sum() & M32)
+    assert int(np.uint32((A + B).data.sum())) == (sa + sb) & 0xFFFFFFFF
+    assert int(np.uint32((A - B).data.sum())) == (sa - sb) & 0xFFFFFFFF
+    assert int(np.uint32((A.data * B.data).sum())) == int(np.uint32(la.dot(A.data, B.data))) == int((au * bu & M32).sum() & M32)
+    # transpose: involution + sampled definition
+    T = A.transpose()
+    assert T.transpose() == A
+    t = T.to_vec()
+    idx = rng.integers(0, n, (4096, 2))
+    assert np.array_equal(t[idx[:, 1] * n + idx[:, 0]], a[idx[:, 0] * n + idx[:, 1]])
+    del T, t
+    # GEMM: Freivalds, exact mod 2^32: C x == A (B x) for random x (device GEMV cross-checks the GEMM) ...
+    C = A * B
+    for seed in range(4):
+        x = la.Vector.from_vec(np.random.default_rng(seed).integers(-2**31, 2**31 - 1, n, dtype=np.int32))
+        assert la.mul_transpose_mat(x, C) == la.mul_transpose_mat(la.mul_transpose_mat(x, B), A)
+    # ... and 64 sampled entries against the host
+    c = C.to_vec()
+    A2 = a.reshape(n, n); B2 = b.reshape(n, n)
+    for r, col in rng.integers(0, n, (64, 2)):
+        expect = int((A2[r].view(np.uint32).astype(np.uint64) * B2[:, col].view(np.uint32).astype(np.uint64) & M32).sum() & M32)
+        assert int(np.uint32(c[r * n + col])) == expect
+
+
+def test_f32_gemm_8192(la):                    # the headline config
+    n = 8192
+    rng = np.random.default_rng(102)
+    a = rng.random(n * n, dtype=np.float32) * np.float32(2) - np.float32(1); b = rng.random(n * n, dtype=np.float32) * np.float32(2) - np.float32(1)
+    C = (la.Matrix.from_vec(a, n, n) * la.Matrix.from_vec(b, n, n)).to_vec()
+    A2 = a.reshape(n, n).astype(np.float64); B2 = b.reshape(n, n)
+    worst = 0.0
+    for r, col in rng.integers(0, n, (256, 2)):
+        bc = B2[:, col].astype(np.float64)
+        truth = float(A2[r] @ bc); scale = float(np.abs(A2[r]) @ np.abs(bc))
+        # reference order error bound for a serial f32 sum of K terms is ~K * 2^-24 * scale; ours must be well inside
+        worst = max(worst, abs(float(C[r * n + col]) - truth) / scale)
+    assert worst <= 64 * 2.0 ** -24, worst
+    # two full rows, normwise
+    for r in (0, n - 1):
+        truth = A2[r] @ B2.astype(np.float64)
+        assert np.linalg.norm(C[r * n:(r + 1) * n] - truth) / np.linalg.norm(truth) <= 1e-5
+
+
+def test_matvec_32768(la):                     # configs[2], one GPU
+    n = 32768
+    rng = np.random.default_rng(103)
+    m = rng.random(n * n, dtype=np.float32) * np.float32(2) - np.float32(1)
+    v = rng.random(n, dtype=np.float32) * np.float32(2) - np.float32(1)
+    M = la.Matrix.from_vec(m, n, n); V = la.Vector.from_vec(v)
+    M2 = m.reshape(n, n)
+    y = la.mul_transpose_mat(V, M).to_vec()             # M x v
+    rows = rng.integers(0, n, 64)
+    for r in rows:
+        truth = float(M2[r].astype(np.float64) @ v.astype(np.float64)); scale = float(np.abs(M2[r]).astype(np.float64) @ np.abs(v).astype(np.float64))
+        assert abs(float(y[r]) - truth) <= 2.0 ** -20 * scale
+    z = (V * M).to_vec()                                 # v x M
+    for c in rng.integers(0, n, 64):
+        col = M2[:, c].astype(np.float64)
+        truth = float(col @ v.astype(np.float64)); scale = float(np.abs(col) @ np.abs(v).astype(np.float64))
+        assert abs(float(z[c]) - truth) <= 2.0 ** -20 * scale

@@ -1,0 +1,279 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle on the same seeded inputs.
+
+Bars (DESIGN.md "Parity"):
+  * integers, every op incl. sum/dot/GEMV/GEMM/transpose: BIT-EXACT (wrap-around arithmetic is
+    order independent);
+  * f32/f64 add/sub/mul/div/scale and transpose: BIT-EXACT (single IEEE operation);
+  * f32 sum/dot/GEMV/GEMM (different, fixed summation order): with x64 the f64 truth and
+    e(x) = |x - x64| / sum_k |a_k b_k|, require e(ours) <= max(e(oracle order), 2^-22) per
+    output, and normwise ||ours - oracle|| / ||oracle|| <= 1e-5.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+import gen
+import oracle
+from oracle import ADD, SUB, MUL, DIV, NP
+
+pytestmark = pytest.mark.gpu
+
+F32_EPS_FLOOR = 2.0 ** -22
+NORMWISE_TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def la():
+    import linear_algebra_b200 as la
+    la.init(0)
+    return la
+
+
+def same(x, y):
+    x = np.asarray(x); y = np.asarray(y)
+    return x.dtype == y.dtype and x.shape == y.shape and x.tobytes() == y.tobytes()
+
+
+def dt(la, name):
+    # oracle name -> device Parameter ("i8" in the oracle is OpenCL char = I8_CHAR here)
+    return la.I8_CHAR if name == "i8" else la.parameter(name)
+
+
+# ------------------------------------------------------------------ elementwise
+@pytest.mark.parametrize("name", gen.ALL_NAMES)
+def test_elementwise_all_forms(la, name):
+    P = oracle.port()
+    for n in (1, 7, 1000, 4099, (1 << 20) + 3):
+        a = gen.values(name, n, 1); b = gen.values(name, n, 2); d = gen.divisors(name, n, 3)
+        A = la.Vector.from_vec(a, dt(la, name)); B = la.Vector.from_vec(b, dt(la, name)); D = la.Vector.from_vec(d, dt(la, name))
+        assert same((A + B).to_vec(), P.ew_vec_vec(ADD, a, b)), (name, n, "add")
+        assert same((A - B).to_vec(), P.ew_vec_vec(SUB, a, b)), (name, n, "sub")
+        assert same((A * B).to_vec(), P.ew_vec_vec(MUL, a, b)), (name, n, "mul")
+        assert same((A / D).to_vec(), P.ew_vec_vec(DIV, a, d)), (name, n, "div")
+        assert same((A * b[0]).to_vec(), P.ew_vec_scl(MUL, a, b[0])), (name, n, "mul_scl")
+        assert same((A / d[0]).to_vec(), P.ew_vec_scl(DIV, a, d[0])), (name, n, "div_scl")
+        for op, rhs, RHS, f in ((ADD, b, B, "__iadd__"), (SUB, b, B, "__isub__"), (MUL, b, B, "__imul__"), (DIV, d, D, "__itruediv__")):
+            C = A.clone(); getattr(C, f)(RHS)
+            assert same(C.to_vec(), P.ew_assign_vec_vec(op, a, rhs)), (name, n, f)
+        C = A.clone(); C *= b[0]
+        assert same(C.to_vec(), P.ew_assign_vec_scl(MUL, a, b[0]))
+        C = A.clone(); C /= d[0]
+        assert same(C.to_vec(), P.ew_assign_vec_scl(DIV, a, d[0]))
+        assert same(A.to_vec(), a)        # operands untouched
+
+
+def test_rust_i8_maps_to_uchar_like_the_reference(la):
+    # traits.rs:36: Vector<i8> runs the "uchar" kernels -> unsigned divide
+    P = oracle.port()
+    a = np.array([-128, -7, 100, -1], np.int8); d = np.array([3, 2, 7, 5], np.int8)
+    got = (la.Vector.from_vec(a, la.I8) / la.Vector.from_vec(d, la.I8)).to_vec()
+    assert same(got.view(np.uint8), P.ew_vec_vec(DIV, a.view(np.uint8), d.view(np.uint8)))
+    got_signed = (la.Vector.from_vec(a, la.I8_CHAR) / la.Vector.from_vec(d, la.I8_CHAR)).to_vec()
+    assert same(got_signed, P.ew_vec_vec(DIV, a, d))
+    assert not same(got, got_signed)
+
+
+@pytest.mark.parametrize("name", ["u8", "i16", "f32", "u64"])
+def test_elementwise_unaligned_pointers(la, name):
+    """Raw C-ABI call with operands that are not 16-byte aligned (element-granular path)."""
+    P = oracle.port(); lib = la._lib.lib; code = dt(la, name).code; sz = np.dtype(NP[name]).itemsize
+    n = 10001
+    a = gen.values(name, n + 1, 4); b = gen.values(name, n + 1, 5)
+    A = la.Vector.from_vec(a, dt(la, name)); B = la.Vector.from_vec(b, dt(la, name)); C = la.Vector.uninitialized(n + 1, dt(la, name))
+    la._lib.call("la_ew_vec_vec", code, MUL, C.ptr + sz, A.ptr + sz, B.ptr + sz, n, None)
+    la.synchronize()
+    assert same(C.to_vec()[1:], P.ew_vec_vec(MUL, a[1:], b[1:]))
+    out = np.zeros(1, NP[name])
+    la._lib.call("la_dot_vec_vec", code, A.ptr + sz, B.ptr + sz, n, out.ctypes.data, None)
+    if np.dtype(NP[name]).kind != "f":
+        assert out[0] == P.dot_vec_vec(a[1:], b[1:])
+    eq = ctypes.c_int(-1)
+    la._lib.call("la_eq_vec", code, A.ptr + sz, A.ptr + sz, n, ctypes.byref(eq), None)
+    assert eq.value == 1
+    assert lib.la_last_error() is not None
+
+
+# ------------------------------------------------------------------ eq
+@pytest.mark.parametrize("name", gen.ALL_NAMES)
+def test_eq(la, name):
+    a = gen.values(name, 300001, 6)
+    A = la.Vector.from_vec(a, dt(la, name))
+    for pos in (None, 0, 150000, 300000):
+        b = a.copy()
+        if pos is not None:
+            b[pos] = b[pos] + NP[name](1)
+        B = la.Vector.from_vec(b, dt(la, name))
+        assert (A == B) == (pos is None) == oracle.port().eq_vec(a, b)
+        assert (A != B) == (pos is not None)
+    assert A != la.Vector.from_vec(a[:-1], dt(la, name))      # vector.rs:649-651
+    assert la.Vector.from_vec([], dt(la, name)) == la.Vector.from_vec([], dt(la, name))
+
+
+def test_eq_float_semantics(la):
+    nan = la.Vector.from_vec(np.array([1.0, np.nan, 2.0], np.float32))
+    assert not (nan == nan)                   # kernels.cl:72 uses !=
+    assert la.Vector.from_vec(np.array([0.0], np.float32)) == la.Vector.from_vec(np.array([-0.0], np.float32))
+
+
+# ------------------------------------------------------------------ sum / dot
+SIZES_RED = (1, 2, 64, 65, 971, 70001, (1 << 22) + 5)
+
+
+@pytest.mark.parametrize("name", gen.INT_NAMES)
+def test_sum_dot_integers_bit_exact(la, name):
+    P = oracle.port()
+    for n in SIZES_RED:
+        a = gen.values(name, n, 7); b = gen.values(name, n, 8)
+        A = la.Vector.from_vec(a, dt(la, name)); B = la.Vector.from_vec(b, dt(la, name))
+        assert A.sum() == P.sum_vec(a), (name, n)
+        assert la.dot(A, B) == P.dot_vec_vec(a, b), (name, n)
+    assert la.Vector.from_vec([], dt(la, name)).sum() == 0
+
+
+def check_float_dot_like(ours, orc, truth, absdot, what):
+    ours = np.atleast_1d(np.asarray(ours, np.float64)); orc = np.atleast_1d(np.asarray(orc, np.float64))
+    truth = np.atleast_1d(truth); absdot = np.maximum(np.atleast_1d(absdot), np.finfo(np.float64).tiny)
+    e_ours = np.abs(ours - truth) / absdot
+    e_orc = np.abs(orc - truth) / absdot
+    bound = np.maximum(e_orc, F32_EPS_FLOOR)
+    assert np.all(e_ours <= bound), (what, float(e_ours.max()), float(e_orc.max()))
+    denom = np.linalg.norm(orc)
+    if denom > 0:
+        assert np.linalg.norm(ours - orc) / denom <= NORMWISE_TOL, what
+
+
+def test_sum_dot_f32_tolerance(la):
+    P = oracle.port()
+    for n in SIZES_RED:
+        a = gen.values("f32", n, 9); b = gen.values("f32", n, 10)
+        A = la.Vector.from_vec(a); B = la.Vector.from_vec(b)
+        d64, ad = P.f32_dot_truth(a, b)
+        check_float_dot_like(la.dot(A, B), P.dot_vec_vec(a, b), d64, ad, ("dot", n))
+        s64, asum = P.f32_dot_truth(a, np.ones_like(a))
+        check_float_dot_like(A.sum(), P.sum_vec(a), s64, asum, ("sum", n))
+
+
+def test_sum_dot_f64(la):
+    a = gen.values("f64", 100003, 11); b = gen.values("f64", 100003, 12)
+    A = la.Vector.from_vec(a); B = la.Vector.from_vec(b)
+    assert abs(float(la.dot(A, B)) - float(np.dot(a, b))) <= 1e-12 * float(np.abs(a * b).sum())
+    assert abs(float(A.sum()) - float(a.sum())) <= 1e-12 * float(np.abs(a).sum())
+
+
+def test_sum_dot_are_reproducible(la):
+    a = gen.values("f32", (1 << 22) + 5, 13); A = la.Vector.from_vec(a)
+    first = la.dot(A, A)
+    assert all(same(la.dot(A, A), first) for _ in range(5))
+
+
+def test_dev_result_variants(la):
+    a = gen.values("i32", 100000, 14); A = la.Vector.from_vec(a)
+    out = la.Vector.uninitialized(2, "i32")
+    la._lib.call("la_sum_vec_dev", A.dtype.code, A.ptr, A.len(), out.ptr, None)
+    la._lib.call("la_dot_vec_vec_dev", A.dtype.code, A.ptr, A.ptr, A.len(), out.ptr + 4, None)
+    got = out.to_vec()
+    assert got[0] == oracle.port().sum_vec(a) and got[1] == oracle.port().dot_vec_vec(a, a)
+
+
+# ------------------------------------------------------------------ matrix x vector
+SHAPES_MV = ((1, 1), (4, 3), (3, 4), (37, 53), (128, 64), (1000, 4096), (4096, 1000), (513, 2052), (5000, 128), (2, 40000))
+
+
+@pytest.mark.parametrize("name", gen.INT_NAMES)
+def test_matvec_integers_bit_exact(la, name):
+    P = oracle.port()
+    for rows, cols in SHAPES_MV:
+        m = gen.values(name, rows * cols, 15); vr = gen.values(name, rows, 16); vc = gen.values(name, cols, 17)
+        M = la.Matrix.from_vec(m, rows, cols, dt(la, name))
+        assert same((la.Vector.from_vec(vr, dt(la, name)) * M).to_vec(), P.mul_vec_mat(vr, m, rows, cols)), (name, rows, cols, "v*M")
+        assert same(la.mul_transpose_mat(la.Vector.from_vec(vc, dt(la, name)), M).to_vec(), P.mul_vec_transpose_mat(vc, m, rows, cols)), (name, rows, cols, "M*v")
+
+
+def test_matvec_f32_tolerance(la):
+    P = oracle.port()
+    for rows, cols in SHAPES_MV:
+        m = gen.values("f32", rows * cols, 18); vr = gen.values("f32", rows, 19); vc = gen.values("f32", cols, 20)
+        M = la.Matrix.from_vec(m, rows, cols)
+        m64 = m.astype(np.float64).reshape(rows, cols)
+        ours = (la.Vector.from_vec(vr) * M).to_vec()
+        check_float_dot_like(ours, P.mul_vec_mat(vr, m, rows, cols), vr.astype(np.float64) @ m64, np.abs(vr.astype(np.float64)) @ np.abs(m64), ("v*M", rows, cols))
+        ours = la.mul_transpose_mat(la.Vector.from_vec(vc), M).to_vec()
+        check_float_dot_like(ours, P.mul_vec_transpose_mat(vc, m, rows, cols), m64 @ vc.astype(np.float64), np.abs(m64) @ np.abs(vc.astype(np.float64)), ("M*v", rows, cols))
+
+
+# ------------------------------------------------------------------ matrix x matrix
+SHAPES_MM = ((1, 1, 1), (2, 3, 2), (5, 1, 7), (33, 17, 29), (64, 64, 64), (256, 256, 256), (320, 100, 192), (512, 1000, 384), (130, 70, 258))
+
+
+@pytest.mark.parametrize("name", gen.INT_NAMES)
+def test_matmat_integers_bit_exact(la, name):
+    P = oracle.port()
+    for M, K, N in SHAPES_MM:
+        a = gen.values(name, M * K, 21); b = gen.values(name, K * N, 22)
+        C = la.Matrix.from_vec(a, M, K, dt(la, name)) * la.Matrix.from_vec(b, K, N, dt(la, name))
+        assert C.len() == (M, N)
+        assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (name, M, K, N)
+
+
+def check_f32_gemm(la, a, b, M, K, N, what):
+    P = oracle.port()
+    C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+    truth, absab = P.f32_mul_mat_mat_truth(a, b, M, K, N)
+    check_float_dot_like(C, P.mul_mat_mat(a, b, M, K, N), truth, absab, what)
+
+
+def test_matmat_f32_tolerance(la):
+    for M, K, N in SHAPES_MM:
+        check_f32_gemm(la, gen.values("f32", M * K, 23), gen.values("f32", K * N, 24), M, K, N, (M, K, N))
+
+
+@pytest.mark.parametrize("variant", list(range(0, 9)) + [-1])
+def test_matmat_every_engine_variant(la, variant):
+    """All tile shapes of the TMA engine (and the generic engine, -1) on shapes with ragged
+    edge tiles and a K tail."""
+    P = oracle.port(); lib = la._lib.lib
+    lib.la_gemm_set_variant(variant)
+    try:
+        for M, K, N in ((512, 256, 384), (388, 1001, 260)):
+            check_f32_gemm(la, gen.values("f32", M * K, 25), gen.values("f32", K * N, 26), M, K, N, (variant, M, K, N))
+            a = gen.values("i32", M * K, 27); b = gen.values("i32", K * N, 28)
+            C = la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)
+            assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (variant, M, K, N)
+    finally:
+        lib.la_gemm_set_variant(0)
+
+
+def test_matmat_f64(la):
+    M, K, N = 70, 33, 65
+    a = gen.values("f64", M * K, 29); b = gen.values("f64", K * N, 30)
+    C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+    np.testing.assert_allclose(C, (a.reshape(M, K) @ b.reshape(K, N)).reshape(-1), rtol=1e-12, atol=1e-12)
+
+
+def test_mul_column_row(la):                   # matrix.rs:236-238
+    col = gen.values("i32", 50, 31); row = gen.values("i32", 70, 32)
+    m = la.mul_column_row(la.Vector.from_vec(col), la.Vector.from_vec(row))
+    assert m.len() == (50, 70)
+    assert same(m.to_vec(), oracle.port().mul_mat_mat(col, row, 50, 1, 70))
+
+
+def test_matrix_elementwise_delegates(la):     # matrix.rs:134-218, 268-277
+    P = oracle.port()
+    a = gen.values("i32", 6 * 7, 33); b = gen.values("i32", 6 * 7, 34)
+    A = la.Matrix.from_vec(a, 6, 7); B = la.Matrix.from_vec(b, 6, 7)
+    assert same((A + B).to_vec(), P.ew_vec_vec(ADD, a, b)) and same((A - B).to_vec(), P.ew_vec_vec(SUB, a, b))
+    assert same((A * 3).to_vec(), P.ew_vec_scl(MUL, a, 3)) and same((A / 3).to_vec(), P.ew_vec_scl(DIV, a, 3))
+    C = A.clone(); C += B; C -= B; C *= 5
+    assert same(C.to_vec(), P.ew_vec_scl(MUL, a, 5))
+
+
+# ------------------------------------------------------------------ transpose
+@pytest.mark.parametrize("name", gen.ALL_NAMES)
+def test_transpose(la, name):
+    P = oracle.port()
+    for R, C in ((1, 1), (1, 9), (9, 1), (33, 65), (64, 32), (128, 256), (1000, 516), (520, 1000), (2049, 31)):
+        a = gen.values(name, R * C, 35)
+        T = la.Matrix.from_vec(a, R, C, dt(la, name)).transpose()
+        assert T.len() == (C, R)
+        assert same(T.to_vec(), P.transpose(a, R, C)), (name, R, C)

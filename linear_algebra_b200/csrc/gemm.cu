@@ -148,7 +148,10 @@ struct GemmShape {
     static constexpr int THREADS = (CONSUMER_WARPS + 4) * 32;
     static constexpr int STAGE_ELEMS = (BM + BN) * BK;
     static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_ELEMS * 4;
-    static_assert((128 * PRODUCER_REGS + 256 * CONSUMER_REGS) * MIN_BLOCKS <= 65536, "register file");
+    // setmaxnreg trades registers inside the CTA's own launch-time pool: THREADS * (launch regs),
+    // launch regs = 65536 / (THREADS * MIN_BLOCKS) rounded down to a multiple of 8.
+    static constexpr int LAUNCH_REGS = (65536 / (THREADS * MIN_BLOCKS)) / 8 * 8;
+    static_assert(128 * PRODUCER_REGS + 256 * CONSUMER_REGS <= THREADS * LAUNCH_REGS, "CTA register pool");
 };
 
 template <typename T, typename S, bool PACKED>
@@ -329,7 +332,7 @@ using Shape_16x8  = GemmShape<16,  8, 4, 2, 16, 4, 1, 240>;    // 256 x 128 bloc
 using Shape_16x8b = GemmShape<16,  8, 2, 4, 16, 4, 1, 240>;    // 128 x 256 block
 using Shape_8x16  = GemmShape< 8, 16, 4, 2, 16, 4, 1, 240>;    // 128 x 256 block
 using Shape_16x8k = GemmShape<16,  8, 4, 2,  8, 8, 1, 240>;    // 256 x 128 block, BK 8
-using Shape_8x8   = GemmShape< 8,  8, 4, 2, 16, 4, 2, 112>;    // 128 x 128 block, two per SM
+using Shape_8x8   = GemmShape< 8,  8, 4, 2, 16, 4, 2, 104>;    // 128 x 128 block, two per SM
 using Shape_8x8s  = GemmShape< 8,  8, 4, 2, 16, 6, 1, 240>;    // 128 x 128 block, one per SM
 
 template <typename T>

@@ -141,6 +141,20 @@ la_status la_dot_vec_vec_dev(int dtype, const void* a, const void* b, size_t n, 
 la_status la_mul_vec_mat(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream);
 la_status la_mul_vec_transpose_mat(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream);
 
+/* la_mul_vec_mat for callers that must not allocate.  No counterpart in the reference (its
+ * host code allocates a cl_mem per result, src/vector.rs:516-519); added for host programs that
+ * own all device memory themselves or cannot take the synchronisation of a cudaMalloc.  Same
+ * arguments and results as la_mul_vec_mat.  The per-strip partial vectors live in a fixed
+ * 8 MiB block inside the library image (held by every GPU that loads the library until the
+ * process exits) instead of grown scratch; it calls no cudaMalloc/cudaFree or other allocating
+ * routine.  Shapes whose partials exceed the block return LA_ERR_UNSUPPORTED with the byte
+ * counts in la_last_error() -- roughly strips * cols * sizeof(accumulator) <= 8 MiB, e.g.
+ * 32768 x 32768 f32 fits, 64 x 2^21 u8 does not.  One block per device, shared by all calls on
+ * all streams: calls that overlap on the GPU race; the block keeps the previous call's contents
+ * and none of it needs to start at zero.  The first call on a device resolves the block's
+ * device address (cudaGetSymbolAddress) and should be made before any stream capture begins. */
+la_status la_mul_vec_mat_noalloc(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream);
+
 /* ------------------------------------------------------------------ matrix x matrix
  * {T}_mul_mat_mat src/kernels.cl:161-169 (+ {T}_dot_product :134-140), host mul_helper
  * src/matrix.rs:240-265 (`&Matrix * &Matrix` :221-232, mul_column_row :236-238 with K == 1):

@@ -67,6 +67,7 @@ SIGNATURES = {
     "la_dot_vec_vec_dev": [_I, _V, _V, _Z, _V, _V],
     "la_mul_vec_mat": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_vec_transpose_mat": [_I, _V, _V, _V, _Z, _Z, _V],
+    "la_mul_vec_mat_noalloc": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_mat_mat": [_I, _V, _V, _V, _Z, _Z, _Z, _V],
     "la_set_gemm_mode": [_I],
     "la_get_gemm_mode": [_PI],

@@ -17,6 +17,7 @@
 // Roofline: HBM.  Algorithmic bytes: sizeof(T) * (rows*cols + rows + cols).
 // Accumulation is in T's accumulator type (wraps for integers; f32 stays f32), in a fixed order.
 #include "common.cuh"
+#include <mutex>
 
 namespace {
 
@@ -244,5 +245,107 @@ extern "C" la_status la_mul_vec_mat(int dtype, void* C, const void* A, const voi
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     if (rows == 0) { LA_CUDA(cudaMemsetAsync(C, 0, cols * la_dtype_size(dtype), (cudaStream_t)stream)); return LA_OK; }
     LA_DISPATCH_DTYPE(dtype, T, return vecmat_cols<T>((T*)C, (const T*)A, (const T*)B, rows, cols, (cudaStream_t)stream, info->sm_count));
+    return LA_OK;
+}
+
+// =====================================================================================
+// la_mul_vec_mat_noalloc -- the same v x M computation for callers that must not allocate.
+//
+// Who needs it: a host program that has already handed (nearly) all device memory to its own
+// allocator, so that a cudaMalloc issued from inside this library would fail; and a caller in a
+// latency-critical section that cannot afford the device-wide synchronisation a cudaMalloc /
+// cudaFree implies.  la_mul_vec_mat gets its per-strip partial vectors from la_scratch(), which
+// grows by cudaMalloc on demand.  This variant keeps them in the fixed block below instead and
+// calls no cudaMalloc, cudaFree, cudaMallocAsync or any other allocating routine, on any call.
+//
+// The price: the block is part of the library image, so every GPU that loads the library
+// holds LA_NOALLOC_SCRATCH_BYTES of device memory until the process exits, and problems whose
+// partials do not fit are refused (LA_ERR_UNSUPPORTED) rather than served more slowly.
+//
+// Sharing: there is ONE block per device, used by every call whatever its stream.  Two calls
+// whose kernels overlap on the GPU (different streams, or different host threads) race on it
+// and produce garbage; serialise them.  The block keeps whatever the previous call left in
+// it.  Nothing in it has to start at zero: every partial the finishing kernel reads is
+// written first by the main kernel of the same call, so no clearing pass is needed.
+//
+// First call on a device: looks up the device address of the block (cudaGetSymbolAddress) and
+// the SM count, once, with that device current.  Make that first call before starting any
+// stream capture.  Later calls only launch kernels.
+constexpr size_t LA_NOALLOC_SCRATCH_BYTES = size_t(8) << 20;      // 8 MiB per GPU
+static __device__ __align__(256) unsigned char la_noalloc_scratch[LA_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int LA_NOALLOC_MAX_DEVICES = 64;
+struct NoallocDevice { bool ready; void* scratch; int sm_count; };
+NoallocDevice g_noalloc[LA_NOALLOC_MAX_DEVICES];     // zero-initialised: ready == false
+std::mutex g_noalloc_mu;
+
+// In host code `la_noalloc_scratch` is only a handle for the runtime, not an address a kernel
+// can use; the device address has to be asked for, per device.
+la_status noalloc_setup(NoallocDevice** out) {
+    int dev = -1;
+    LA_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= LA_NOALLOC_MAX_DEVICES) return la_fail(LA_ERR_UNSUPPORTED, "la_mul_vec_mat_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    NoallocDevice& d = g_noalloc[dev];
+    if (!d.ready) {
+        void* p = nullptr;
+        LA_CUDA(cudaGetSymbolAddress(&p, la_noalloc_scratch));
+        if (!p) return la_fail(LA_ERR_CUDA, "la_mul_vec_mat_noalloc: cudaGetSymbolAddress returned NULL");
+        int sms = 0;
+        LA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        d.scratch = p; d.sm_count = sms; d.ready = true;
+    }
+    *out = &d;
+    return LA_OK;
+}
+
+// Same decomposition as vecmat_cols() above (so the two entry points give identical results),
+// with the partials in the fixed block.
+template <typename T>
+la_status vecmat_cols_noalloc(T* C, const T* A, const T* B, size_t rows, size_t cols, cudaStream_t st, const NoallocDevice& d) {
+    using Acc = typename Arith<T>::Acc;
+    const int sm = d.sm_count;
+    const bool packed = la_aligned16(C) && la_aligned16(B) && (cols % Pack<T>::N == 0);
+    const size_t units = packed ? cols / Pack<T>::N : cols;
+    const size_t col_blocks = (units + VM_THREADS - 1) / VM_THREADS;
+    size_t strips = ((size_t)sm * 16 + col_blocks - 1) / col_blocks;
+    const size_t max_strips = (rows + 4 * VM_UNROLL - 1) / (4 * VM_UNROLL);
+    if (strips > max_strips) strips = max_strips;
+    if (strips > 65535) strips = 65535;
+    if (strips < 1) strips = 1;
+    const size_t rows_per_strip = (rows + strips - 1) / strips;
+    strips = (rows + rows_per_strip - 1) / rows_per_strip;
+    if (col_blocks > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "la_mul_vec_mat_noalloc: too many columns");
+    Acc* part = nullptr;
+    if (strips > 1) {
+        const size_t need = strips * cols * sizeof(Acc);
+        if (need > LA_NOALLOC_SCRATCH_BYTES)
+            return la_fail(LA_ERR_UNSUPPORTED,
+                           "la_mul_vec_mat_noalloc: %zu x %zu needs %zu bytes of partials (%zu strips), the fixed block holds %zu; use la_mul_vec_mat",
+                           rows, cols, need, strips, (size_t)LA_NOALLOC_SCRATCH_BYTES);
+        part = (Acc*)d.scratch;
+    }
+    dim3 grid((unsigned)col_blocks, (unsigned)strips);
+    if (packed) vecmat_pack_kernel<T><<<grid, VM_THREADS, 0, st>>>(C, part, A, B, rows, cols, rows_per_strip);
+    else        vecmat_elem_kernel<T><<<grid, VM_THREADS, 0, st>>>(C, part, A, B, rows, cols, rows_per_strip);
+    LA_LAUNCH_CHECK();
+    if (strips > 1) {
+        vecmat_finish_kernel<T><<<(unsigned)((cols + 255) / 256), 256, 0, st>>>(C, part, cols, (int)strips);
+        LA_LAUNCH_CHECK();
+    }
+    return LA_OK;
+}
+
+}  // namespace
+
+extern "C" la_status la_mul_vec_mat_noalloc(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream) {
+    LA_TRY(check("la_mul_vec_mat_noalloc", dtype, C, A, B));
+    if (cols == 0) return LA_OK;
+    NoallocDevice* d = nullptr;
+    LA_TRY(noalloc_setup(&d));
+    if (rows == 0) { LA_CUDA(cudaMemsetAsync(C, 0, cols * la_dtype_size(dtype), (cudaStream_t)stream)); return LA_OK; }
+    LA_DISPATCH_DTYPE(dtype, T, return vecmat_cols_noalloc<T>((T*)C, (const T*)A, (const T*)B, rows, cols, (cudaStream_t)stream, *d));
     return LA_OK;
 }

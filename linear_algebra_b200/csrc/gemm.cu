@@ -114,6 +114,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (!done && spin > (1u << 22)) __trap();
     }
 }
+// Non-blocking probe (test_wait never suspends the thread).
+__device__ __forceinline__ uint32_t mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return done;
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y) {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -208,24 +218,48 @@ gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, c
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = Acc(0);
 
+    // Fragments are double-buffered in registers and loaded one k-step ahead, ACROSS slab
+    // boundaries: the next slab's barrier is probed (non-blocking test_wait) half a slab early
+    // and its k=0 fragments are fetched before the current slab's last k-step is multiplied, so
+    // neither the barrier round trip nor the first LDS latency ever leaves the FMA pipe idle
+    // (both warps of a sub-partition reach a slab boundary at the same moment).
+    T fa[2][TM], fb[2][TN];
+    auto load_frag = [&](int buf, const T* as, const T* bs, int k) {
+#pragma unroll
+        for (int cm = 0; cm < TM / 4; ++cm)
+            *reinterpret_cast<uint4*>(&fa[buf][cm * 4]) = *reinterpret_cast<const uint4*>(as + k * BM + cm * 16);
+#pragma unroll
+        for (int cn = 0; cn < TN / 4; ++cn)
+            *reinterpret_cast<uint4*>(&fb[buf][cn * 4]) = *reinterpret_cast<const uint4*>(bs + k * BN + cn * 32);
+    };
+    static_assert(BK % 2 == 0, "fragment double-buffering alternates per k-step");
+
+    mbar_wait(&full_bar[0], 0);
+    load_frag(0, smem + a_off, smem + BM * BK + b_off, 0);
+
     for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % STAGES;
-        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-        mbar_wait(&full_bar[s], ph);
         const T* as = smem + (size_t)s * S::STAGE_ELEMS + a_off;
         const T* bs = smem + (size_t)s * S::STAGE_ELEMS + BM * BK + b_off;
+        const int kn = kb + 1;
+        const int sn = kn % STAGES;
+        const uint32_t phn = (uint32_t)(kn / STAGES) & 1u;
+        const bool has_next = kn < num_kb;
+        uint32_t next_ready = 0;
 #pragma unroll
         for (int k = 0; k < BK; ++k) {
-            T a[TM], b[TN];
-#pragma unroll
-            for (int cm = 0; cm < TM / 4; ++cm)
-                *reinterpret_cast<uint4*>(&a[cm * 4]) = *reinterpret_cast<const uint4*>(as + k * BM + cm * 16);
-#pragma unroll
-            for (int cn = 0; cn < TN / 4; ++cn)
-                *reinterpret_cast<uint4*>(&b[cn * 4]) = *reinterpret_cast<const uint4*>(bs + k * BN + cn * 32);
+            if (k == BK / 2 && has_next) next_ready = mbar_test(&full_bar[sn], phn);
+            if (k + 1 < BK) {
+                load_frag((k + 1) & 1, as, bs, k + 1);
+            } else if (has_next) {
+                if (!next_ready) mbar_wait(&full_bar[sn], phn);
+                load_frag(0, smem + (size_t)sn * S::STAGE_ELEMS + a_off, smem + (size_t)sn * S::STAGE_ELEMS + BM * BK + b_off, 0);
+            }
+            const T* a = fa[k & 1];
+            const T* b = fb[k & 1];
             if constexpr (PACKED) {
-                // f32 only: two FMAs per issued FFMA2.  Pairs run along the longer side of the
-                // thread tile so that only the shorter fragment has to be duplicated.
+                // f32 only: two FMAs per issued FFMA2 (its scalar-broadcast operand form takes
+                // the unpaired fragment).  Pairs run along the longer side of the thread tile.
                 if constexpr (TM >= TN) {
 #pragma unroll
                     for (int j = 0; j < TN; ++j) {
@@ -256,6 +290,7 @@ gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, c
                     for (int j = 0; j < TN; ++j) Mac<T>::mac(acc[i][j], a[i], b[j]);
             }
         }
+        // every fragment of slab `kb` has been consumed by the FMAs above: hand the slot back
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[s]);
     }

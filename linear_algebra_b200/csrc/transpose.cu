@@ -24,25 +24,35 @@ transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
     const size_t r0 = (size_t)(blockIdx.x / tiles_x) * TILE, c0 = (size_t)(blockIdx.x % tiles_x) * TILE;
 
     // R % V == 0 and C % V == 0 on this path: a packet is either wholly inside or wholly outside.
+    constexpr int PER_THREAD = TILE * VPR / TR_THREADS;
+    static_assert(TILE * VPR % TR_THREADS == 0, "whole packets per thread");
+    // all global loads first (PER_THREAD independent 16-byte requests in flight per thread) ...
+    P in_p[PER_THREAD];
 #pragma unroll
-    for (int idx = threadIdx.x; idx < TILE * VPR; idx += TR_THREADS) {
+    for (int j = 0; j < PER_THREAD; ++j) {
+        const int idx = threadIdx.x + j * TR_THREADS;
         const int r = idx / VPR, q = idx % VPR;
-        if (r0 + r < R && c0 + (size_t)q * V < C) {
-            P p = ld_stream(reinterpret_cast<const P*>(in + (r0 + r) * C + c0 + (size_t)q * V));
+        if (r0 + r < R && c0 + (size_t)q * V < C)
+            in_p[j] = ld_stream(reinterpret_cast<const P*>(in + (r0 + r) * C + c0 + (size_t)q * V));
+    }
+    // ... then scatter them into the tile
 #pragma unroll
-            for (int e = 0; e < V; ++e) tile[r][q * V + e] = p.v[e];
-        }
+    for (int j = 0; j < PER_THREAD; ++j) {
+        const int idx = threadIdx.x + j * TR_THREADS;
+        const int r = idx / VPR, q = idx % VPR;
+#pragma unroll
+        for (int e = 0; e < V; ++e) tile[r][q * V + e] = in_p[j].v[e];
     }
     __syncthreads();
 #pragma unroll
-    for (int idx = threadIdx.x; idx < TILE * VPR; idx += TR_THREADS) {
+    for (int j = 0; j < PER_THREAD; ++j) {
+        const int idx = threadIdx.x + j * TR_THREADS;
         const int cc = idx / VPR, q = idx % VPR;      // output row c0+cc, output columns r0 + q*V ...
-        if (c0 + cc < C && r0 + (size_t)q * V < R) {
-            P p;
+        P p;
 #pragma unroll
-            for (int e = 0; e < V; ++e) p.v[e] = tile[q * V + e][cc];
+        for (int e = 0; e < V; ++e) p.v[e] = tile[q * V + e][cc];
+        if (c0 + cc < C && r0 + (size_t)q * V < R)
             st_stream(reinterpret_cast<P*>(out + (c0 + cc) * R + r0 + (size_t)q * V), p);
-        }
     }
 }
 

@@ -1,0 +1,254 @@
+"""Row-block sharding of Vector / Matrix over one process per GPU.
+
+The reference is single-device (src/lib.rs:310-335: one context, one in-order queue); this is
+the multi-GPU layer the north star adds.  `torch.distributed` (NCCL on GPUs, gloo in the CPU
+tests) is only plumbing: ranks exchange raw bytes with all_gather and every rank finishes the
+combination locally IN RANK ORDER, so results are deterministic, identical on all ranks, and
+need no NCCL support for the element type (NCCL has no 16-bit integers).
+
+  op                         partition                              exchange
+  elementwise / scale        co-sharded ranges                      none
+  sum / dot / ==             local partial (la_*_dev)               all_gather of one element
+  M x v (mul_transpose_mat)  M by rows, v replicated -> rows shard  none
+  v x M                      v and M by rows -> full-length partial all_gather of `cols` elements,
+                                                                    rank-ordered adds (la_ew_assign_vec_vec)
+  M x M                      A, C by rows, B replicated             none
+
+`Comm` wraps the process group; `local` is the module providing Vector/Matrix (the real one by
+default; the CPU tests inject a numpy stand-in to exercise this file's logic under gloo)."""
+import numpy as np
+
+
+def partition(n, world, rank):
+    """Contiguous block partition of range(n): the first n % world ranks get one extra element."""
+    base, extra = divmod(int(n), int(world))
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+class Comm:
+    """Byte-level collectives over a torch.distributed process group."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.backend = dist.get_backend(group)
+
+    def _tensor(self, ptr, nbytes):
+        import torch
+        if self.backend == "gloo":
+            raise RuntimeError("device pointers need the nccl backend")
+
+        class _View:      # zero-copy view of library-owned device memory
+            __cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2, "strides": None}
+        return torch.as_tensor(_View(), device="cuda")
+
+    def all_gather_host(self, payload: bytes):
+        """All ranks contribute `payload` (same length everywhere); returns the list in rank order."""
+        import torch
+        device = "cuda" if self.backend == "nccl" else "cpu"
+        mine = torch.frombuffer(bytearray(payload), dtype=torch.uint8).to(device)
+        out = [torch.empty_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(out, mine, group=self.group)
+        return [bytes(t.cpu().numpy().tobytes()) for t in out]
+
+    def all_gather_device(self, dst_ptr, src_ptr, nbytes):
+        """dst (world * nbytes device bytes, rank order) <- every rank's src (nbytes device bytes)."""
+        out = self._tensor(dst_ptr, nbytes * self.world)
+        self.dist.all_gather_into_tensor(out, self._tensor(src_ptr, nbytes), group=self.group)
+
+    def barrier(self):
+        self.dist.barrier(group=self.group)
+
+
+def combine_scalars(parts, np_dtype):
+    """Rank-ordered sum of per-rank partials with the element type's own arithmetic (integers
+    wrap, f32 rounds after every add): what a single device would produce from those partials."""
+    dt = np.dtype(np_dtype)
+    acc = dt.type(0)
+    with np.errstate(over="ignore"):
+        for p in parts:
+            acc = dt.type(acc + np.frombuffer(p, dtype=dt, count=1)[0])
+    return acc
+
+
+class ShardedVector:
+    """This rank's contiguous range [lo, hi) of a global vector of `global_len` elements."""
+
+    def __init__(self, comm, local_vec, global_len, local_mod=None):
+        self.comm, self.local, self.global_len = comm, local_vec, int(global_len)
+        self.lo, self.hi = partition(global_len, comm.world, comm.rank)
+        assert self.local.len() == self.hi - self.lo, "local shard has the wrong length"
+        self._m = local_mod
+
+    @staticmethod
+    def from_global(comm, host_array, dtype=None, local_mod=None):
+        """Every rank passes the same full host array and keeps only its range."""
+        m = local_mod or _default_local()
+        host = np.ascontiguousarray(host_array).reshape(-1)
+        lo, hi = partition(host.size, comm.world, comm.rank)
+        return ShardedVector(comm, m.Vector.from_vec(host[lo:hi], dtype), host.size, m)
+
+    def _mod(self):
+        return self._m or _default_local()
+
+    def _wrap(self, v):
+        return ShardedVector(self.comm, v, self.global_len, self._m)
+
+    def _co(self, other):
+        assert isinstance(other, ShardedVector) and other.global_len == self.global_len, \
+            "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (self.global_len, getattr(other, "global_len", -1))
+        return other.local
+
+    def len(self):
+        return self.global_len
+
+    # elementwise: purely local
+    def __add__(self, o): return self._wrap(self.local + self._co(o))
+    def __sub__(self, o): return self._wrap(self.local - self._co(o))
+    def __iadd__(self, o): self.local += self._co(o); return self
+    def __isub__(self, o): self.local -= self._co(o); return self
+
+    def __mul__(self, o):
+        if isinstance(o, ShardedMatrix):
+            return _sharded_vec_mat(self, o)
+        return self._wrap(self.local * (self._co(o) if isinstance(o, ShardedVector) else o))
+
+    def __imul__(self, o):
+        self.local *= (self._co(o) if isinstance(o, ShardedVector) else o)
+        return self
+
+    def __truediv__(self, o):
+        return self._wrap(self.local / (self._co(o) if isinstance(o, ShardedVector) else o))
+
+    # one exchange: a single element per rank, combined in rank order
+    def sum(self):
+        part = self.local.sum()
+        return combine_scalars(self.comm.all_gather_host(np.asarray(part).tobytes()), self.local.dtype.np)
+
+    def __eq__(self, other):
+        if not isinstance(other, ShardedVector):
+            return NotImplemented
+        same_shape = self.global_len == other.global_len and self.local.dtype.code == other.local.dtype.code
+        mine = bool(same_shape and self.local == other.local)
+        return all(p == b"\x01" for p in self.comm.all_gather_host(b"\x01" if mine else b"\x00"))
+
+    __hash__ = None
+
+    def gather(self):
+        """The full vector on every rank (host array)."""
+        parts = self.comm.all_gather_host(_pad(self.local.to_vec().tobytes(), self._max_shard_bytes()))
+        dt = self.local.dtype.np
+        out = []
+        for r, p in enumerate(parts):
+            lo, hi = partition(self.global_len, self.comm.world, r)
+            out.append(np.frombuffer(p, dtype=dt, count=hi - lo))
+        return np.concatenate(out) if out else np.empty(0, dt)
+
+    def _max_shard_bytes(self):
+        lo, hi = partition(self.global_len, self.comm.world, 0)
+        return (hi - lo) * self.local.dtype.size
+
+
+def _pad(b, n):
+    return b + b"\x00" * (n - len(b))
+
+
+def dot(a, b):
+    a._co(b)
+    part = a._mod().dot(a.local, b.local)
+    return combine_scalars(a.comm.all_gather_host(np.asarray(part).tobytes()), a.local.dtype.np)
+
+
+class ShardedMatrix:
+    """Rows [lo, hi) of a global rows x cols matrix (all columns)."""
+
+    def __init__(self, comm, local_mat, global_rows, local_mod=None):
+        self.comm, self.local, self.global_rows = comm, local_mat, int(global_rows)
+        self.lo, self.hi = partition(global_rows, comm.world, comm.rank)
+        assert self.local.get_row_count() == self.hi - self.lo
+        self.col_count = self.local.get_col_count()
+        self._m = local_mod
+
+    @staticmethod
+    def from_global(comm, host_array, rows, cols, dtype=None, local_mod=None):
+        m = local_mod or _default_local()
+        host = np.ascontiguousarray(host_array).reshape(rows, cols)
+        lo, hi = partition(rows, comm.world, comm.rank)
+        return ShardedMatrix(comm, m.Matrix.from_vec(host[lo:hi].reshape(-1), hi - lo, cols, dtype), rows, m)
+
+    def _mod(self):
+        return self._m or _default_local()
+
+    def len(self):
+        return (self.global_rows, self.col_count)
+
+    def _co(self, o):
+        assert isinstance(o, ShardedMatrix) and o.len() == self.len(), "matrix shapes differ"
+        return o.local
+
+    def __add__(self, o): return ShardedMatrix(self.comm, self.local + self._co(o), self.global_rows, self._m)
+    def __sub__(self, o): return ShardedMatrix(self.comm, self.local - self._co(o), self.global_rows, self._m)
+
+    def __mul__(self, o):
+        m = self._mod()
+        if isinstance(o, m.Matrix):            # A (row-sharded) x B (replicated): no exchange
+            return ShardedMatrix(self.comm, self.local * o, self.global_rows, self._m)
+        assert not isinstance(o, (ShardedMatrix, ShardedVector)), "right operand of a sharded GEMM must be replicated"
+        return ShardedMatrix(self.comm, self.local * o, self.global_rows, self._m)
+
+    def gather(self):
+        rows_max = partition(self.global_rows, self.comm.world, 0)
+        nbytes = (rows_max[1] - rows_max[0]) * self.col_count * self.local.dtype.size
+        parts = self.comm.all_gather_host(_pad(self.local.to_vec().tobytes(), nbytes))
+        out = []
+        for r, p in enumerate(parts):
+            lo, hi = partition(self.global_rows, self.comm.world, r)
+            out.append(np.frombuffer(p, dtype=self.local.dtype.np, count=(hi - lo) * self.col_count))
+        return np.concatenate(out)
+
+
+def mul_transpose_mat(vector, sharded_m):
+    """M x v with M row-sharded and v replicated (a plain Vector): each rank owns a slice of the
+    result; no exchange."""
+    m = sharded_m._mod()
+    return ShardedVector(sharded_m.comm, m.mul_transpose_mat(vector, sharded_m.local), sharded_m.global_rows, sharded_m._m)
+
+
+def _sharded_vec_mat(sv, sm):
+    """v x M with v and M co-sharded by rows: local full-length partial, then one all_gather and
+    rank-ordered adds.  Returns a replicated plain Vector of `cols` elements."""
+    assert sv.global_len == sm.global_rows, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (sv.global_len, sm.global_rows)
+    m = sm._mod()
+    comm = sv.comm
+    partial = sv.local * sm.local                  # la_mul_vec_mat on the local rows
+    if comm.world == 1:
+        return partial
+    if comm.backend == "nccl":
+        dt = partial.dtype
+        nbytes = partial.len() * dt.size
+        gathered = m.Vector.uninitialized(partial.len() * comm.world, dt)
+        m.synchronize()
+        comm.all_gather_device(gathered.ptr, partial.ptr, nbytes)
+        import torch
+        torch.cuda.current_stream().synchronize()
+        acc = m.Vector(dt, gathered.ptr, partial.len(), owner=False)
+        for r in range(1, comm.world):             # ascending rank order: deterministic
+            acc += m.Vector(dt, gathered.ptr + r * nbytes, partial.len(), owner=False)
+        out = acc.clone()
+        del acc
+        return out
+    # host path (gloo / CPU tests)
+    parts = comm.all_gather_host(partial.to_vec().tobytes())
+    dt = partial.dtype.np
+    acc = np.frombuffer(parts[0], dtype=dt).copy()
+    with np.errstate(over="ignore"):
+        for p in parts[1:]:
+            acc = (acc + np.frombuffer(p, dtype=dt)).astype(dt)
+    return m.Vector.from_vec(acc, partial.dtype)
+
+
+def _default_local():
+    import linear_algebra_b200 as la
+    return la

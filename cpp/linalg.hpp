@@ -1,0 +1,195 @@
+// cpp/linalg.hpp -- header-only C++ mirror of the reference's public surface over the C ABI.
+//
+// The reference is compiled code (Rust); its toolchain is absent from this image, so the host
+// side above the C ABI is mirrored here in C++ with the same names, argument meaning and error
+// behaviour: linalg::Vector<T> (src/vector.rs), linalg::Matrix<T> (src/matrix.rs), dot(),
+// mul_transpose_mat(), mul_column_row(), Parameter<T>/Real (src/traits.rs).  Shape mismatches
+// throw linalg::Panic where the reference's assert_eq! panics; every operator blocks until the
+// device is done (event.wait_for(), vector.rs:108); out-of-place operators allocate a fresh result.
+// Rust's `&a + &b` is `a + b` here; `a += &b` is `a += b`.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../include/linalg_b200.h"
+
+namespace linalg {
+
+struct Panic : std::runtime_error { using std::runtime_error::runtime_error; };
+
+inline void check(la_status s) {           // the reference unwrap()s every OpenCL call
+    if (s != LA_OK) throw Panic("liblinalg_b200: status " + std::to_string(s) + ": " + la_last_error());
+}
+inline void assert_eq(size_t left, size_t right) {
+    if (left != right) throw Panic("assertion failed: `(left == right)` left: `" + std::to_string(left) + "`, right: `" + std::to_string(right) + "`");
+}
+
+// ---- traits.rs:13-57: element type -> device type
+template <typename T> struct Parameter;
+#define LINALG_PARAM(T, CODE, NAME) \
+    template <> struct Parameter<T> { static constexpr int DTYPE = CODE; static const char* type_to_str() { return NAME; } };
+LINALG_PARAM(uint8_t, LA_U8, "uchar")
+LINALG_PARAM(int8_t, LA_U8, "uchar")        // traits.rs:36: i8 -> "uchar" (kept for drop-in parity)
+LINALG_PARAM(uint16_t, LA_U16, "ushort")
+LINALG_PARAM(int16_t, LA_I16, "short")
+LINALG_PARAM(uint32_t, LA_U32, "uint")
+LINALG_PARAM(int32_t, LA_I32, "int")
+LINALG_PARAM(uint64_t, LA_U64, "ulong")
+LINALG_PARAM(int64_t, LA_I64, "long")
+LINALG_PARAM(float, LA_F32, "float")
+LINALG_PARAM(double, LA_F64, "double")
+#undef LINALG_PARAM
+
+template <typename T> class Matrix;
+
+template <typename T>
+class Vector {                              // vector.rs:23-27
+  public:
+    Vector(const Vector&) = delete;
+    Vector& operator=(const Vector&) = delete;
+    Vector(Vector&& o) noexcept : ptr_(o.ptr_), len_(o.len_) { o.ptr_ = nullptr; o.len_ = 0; }
+    Vector& operator=(Vector&& o) noexcept { std::swap(ptr_, o.ptr_); std::swap(len_, o.len_); return *this; }
+    ~Vector() { if (ptr_) la_free(ptr_); }
+
+    static Vector uninitialized(size_t size) {                      // vector.rs:36-51
+        void* p = nullptr; check(la_malloc(&p, size * sizeof(T))); return Vector(p, size);
+    }
+    static Vector create(T default_val, size_t size) {              // Vector::new, vector.rs:30-34
+        Vector v = uninitialized(size); check(la_fill(D, v.ptr_, &default_val, size, nullptr)); sync(); return v;
+    }
+    static Vector from_vec(const std::vector<T>& v) {               // vector.rs:53-69
+        Vector r = uninitialized(v.size()); check(la_upload(r.ptr_, v.data(), v.size() * sizeof(T), nullptr)); sync(); return r;
+    }
+    std::vector<T> to_vec() const {                                 // vector.rs:71-78
+        std::vector<T> out(len_); check(la_download(out.data(), ptr_, len_ * sizeof(T), nullptr)); return out;
+    }
+    size_t len() const { return len_; }
+    void* ptr() const { return ptr_; }
+    Vector clone() const {                                          // vector.rs:700-708
+        Vector r = uninitialized(len_); check(la_copy(r.ptr_, ptr_, len_ * sizeof(T), nullptr)); sync(); return r;
+    }
+
+    // vector.rs:366-643
+    Vector operator+(const Vector& o) const { return each2(o, LA_ADD); }
+    Vector operator-(const Vector& o) const { return each2(o, LA_SUB); }
+    Vector operator*(const Vector& o) const { return each2(o, LA_MUL); }
+    Vector operator/(const Vector& o) const { return each2(o, LA_DIV); }
+    Vector& operator+=(const Vector& o) { return each_mut(o, LA_ADD); }
+    Vector& operator-=(const Vector& o) { return each_mut(o, LA_SUB); }
+    Vector& operator*=(const Vector& o) { return each_mut(o, LA_MUL); }
+    Vector& operator/=(const Vector& o) { return each_mut(o, LA_DIV); }
+    Vector operator*(T s) const { return scl(s, LA_MUL); }
+    Vector operator/(T s) const { return scl(s, LA_DIV); }
+    Vector& operator*=(T s) { check(la_ew_assign_vec_scl(D, LA_MUL, ptr_, &s, len_, nullptr)); sync(); return *this; }
+    Vector& operator/=(T s) { check(la_ew_assign_vec_scl(D, LA_DIV, ptr_, &s, len_, nullptr)); sync(); return *this; }
+    Vector operator*(const Matrix<T>& m) const;                     // vector.rs:508-539
+
+    bool operator==(const Vector& o) const {                        // vector.rs:645-675
+        if (len_ != o.len_) return false;
+        int eq = 0; check(la_eq_vec(D, ptr_, o.ptr_, len_, &eq, nullptr)); return eq != 0;
+    }
+    bool operator!=(const Vector& o) const { return !(*this == o); }
+
+    T sum() const { T out{}; check(la_sum_vec(D, ptr_, len_, &out, nullptr)); return out; }      // vector.rs:256-293
+    T length() const;                                               // vector.rs:303-305
+    Vector normalized() const { T inv = T(1) / length(); return *this * inv; }                  // vector.rs:320-323
+    Vector normalize() && { T inv = T(1) / length(); *this *= inv; return std::move(*this); }   // vector.rs:313-317
+
+  private:
+    static constexpr int D = Parameter<T>::DTYPE;
+    Vector(void* p, size_t n) : ptr_(p), len_(n) {}
+    static void sync() { check(la_stream_sync(nullptr)); }
+    Vector each2(const Vector& o, int op) const {                   // from_for_each2_lock_free, vector.rs:96-112
+        assert_eq(len_, o.len_);
+        Vector r = uninitialized(len_); check(la_ew_vec_vec(D, op, r.ptr_, ptr_, o.ptr_, len_, nullptr)); sync(); return r;
+    }
+    Vector& each_mut(const Vector& o, int op) {                     // for_each_mut, vector.rs:114-125
+        assert_eq(len_, o.len_);
+        check(la_ew_assign_vec_vec(D, op, ptr_, o.ptr_, len_, nullptr)); sync(); return *this;
+    }
+    Vector scl(T s, int op) const {
+        Vector r = uninitialized(len_); check(la_ew_vec_scl(D, op, r.ptr_, ptr_, &s, len_, nullptr)); sync(); return r;
+    }
+    void* ptr_; size_t len_;
+    template <typename U> friend class Matrix;
+    template <typename U> friend U dot(const Vector<U>&, const Vector<U>&);
+    template <typename U> friend Vector<U> mul_transpose_mat(const Vector<U>&, const Matrix<U>&);
+    template <typename U> friend Matrix<U> mul_column_row(const Vector<U>&, const Vector<U>&);
+};
+
+template <typename T>
+T dot(const Vector<T>& a, const Vector<T>& b) {                     // vector.rs:326-363
+    assert_eq(a.len(), b.len());
+    T out{}; check(la_dot_vec_vec(Parameter<T>::DTYPE, a.ptr_, b.ptr_, a.len_, &out, nullptr)); return out;
+}
+template <typename T> T Vector<T>::length() const { return std::sqrt(dot(*this, *this)); }
+
+template <typename T>
+class Matrix {                                                      // matrix.rs:9-13
+  public:
+    Matrix(Matrix&&) noexcept = default;
+    Matrix& operator=(Matrix&&) noexcept = default;
+    static Matrix create(T v, size_t rows, size_t cols) { return Matrix(Vector<T>::create(v, rows * cols), rows, cols); }
+    static Matrix uninitialized(size_t rows, size_t cols) { return Matrix(Vector<T>::uninitialized(rows * cols), rows, cols); }
+    static Matrix from_vec(const std::vector<T>& v, size_t rows, size_t cols) {     // matrix.rs:39-46
+        assert_eq(v.size(), rows * cols); return Matrix(Vector<T>::from_vec(v), rows, cols);
+    }
+    std::pair<size_t, size_t> len() const { return {rows_, cols_}; }
+    size_t get_row_count() const { return rows_; }
+    size_t get_col_count() const { return cols_; }
+    std::vector<T> to_vec() const { return data_.to_vec(); }
+    const Vector<T>& data() const { return data_; }
+
+    // matrix.rs:134-218, 268-277: shape asserts, then delegate to Vector
+    Matrix operator+(const Matrix& o) const { same(o); return Matrix(data_ + o.data_, rows_, cols_); }
+    Matrix operator-(const Matrix& o) const { same(o); return Matrix(data_ - o.data_, rows_, cols_); }
+    Matrix& operator+=(const Matrix& o) { same(o); data_ += o.data_; return *this; }
+    Matrix& operator-=(const Matrix& o) { same(o); data_ -= o.data_; return *this; }
+    Matrix operator*(T s) const { return Matrix(data_ * s, rows_, cols_); }
+    Matrix& operator*=(T s) { data_ *= s; return *this; }
+    Matrix operator/(T s) const { return Matrix(data_ / s, rows_, cols_); }
+    Matrix operator*(const Matrix& o) const {                       // matrix.rs:221-232
+        assert_eq(cols_, o.rows_); return mul_helper(data_.ptr_, o.data_.ptr_, rows_, cols_, o.cols_);
+    }
+    bool operator==(const Matrix& o) const { return rows_ == o.rows_ && cols_ == o.cols_ && data_ == o.data_; }   // matrix.rs:279-287
+    bool operator!=(const Matrix& o) const { return !(*this == o); }
+    Matrix transpose() const {                                      // not in the reference (north star)
+        Matrix r = uninitialized(cols_, rows_);
+        check(la_transpose(Parameter<T>::DTYPE, r.data_.ptr_, data_.ptr_, rows_, cols_, nullptr)); check(la_stream_sync(nullptr)); return r;
+    }
+    static Matrix mul_helper(const void* a, const void* b, size_t a_rows, size_t a_cols, size_t b_cols) {   // matrix.rs:240-265
+        Matrix r = uninitialized(a_rows, b_cols);
+        check(la_mul_mat_mat(Parameter<T>::DTYPE, r.data_.ptr_, a, b, a_rows, a_cols, b_cols, nullptr)); check(la_stream_sync(nullptr)); return r;
+    }
+
+  private:
+    Matrix(Vector<T>&& d, size_t r, size_t c) : data_(std::move(d)), rows_(r), cols_(c) {}
+    void same(const Matrix& o) const { assert_eq(rows_, o.rows_); assert_eq(cols_, o.cols_); }
+    Vector<T> data_; size_t rows_, cols_;
+    template <typename U> friend class Vector;
+    template <typename U> friend Vector<U> mul_transpose_mat(const Vector<U>&, const Matrix<U>&);
+};
+
+template <typename T>
+Vector<T> Vector<T>::operator*(const Matrix<T>& m) const {          // vector.rs:508-539
+    assert_eq(len_, m.get_row_count());
+    Vector r = uninitialized(m.get_col_count());
+    check(la_mul_vec_mat(D, r.ptr_, ptr_, m.data_.ptr_, m.rows_, m.cols_, nullptr)); sync(); return r;
+}
+template <typename T>
+Vector<T> mul_transpose_mat(const Vector<T>& v, const Matrix<T>& m) {   // vector.rs:542-569
+    assert_eq(v.len(), m.get_col_count());
+    Vector<T> r = Vector<T>::uninitialized(m.get_row_count());
+    check(la_mul_vec_transpose_mat(Parameter<T>::DTYPE, r.ptr_, v.ptr_, m.data_.ptr_, m.rows_, m.cols_, nullptr));
+    check(la_stream_sync(nullptr)); return r;
+}
+template <typename T>
+Matrix<T> mul_column_row(const Vector<T>& column, const Vector<T>& row) {   // matrix.rs:236-238
+    return Matrix<T>::mul_helper(column.ptr_, row.ptr_, column.len(), 1, row.len());
+}
+
+}  // namespace linalg

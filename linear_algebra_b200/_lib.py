@@ -88,6 +88,10 @@ lib.la_dtype_size.restype = ctypes.c_size_t
 # tuning hook (not declared in the public header)
 lib.la_gemm_set_variant.argtypes = [_I]
 lib.la_gemm_set_variant.restype = ctypes.c_int
+lib.la_gemm_tc_set_variant.argtypes = [_I]
+lib.la_gemm_tc_set_variant.restype = ctypes.c_int
+lib.la_gemm_last_engine.argtypes = []
+lib.la_gemm_last_engine.restype = ctypes.c_int
 
 
 def check(status):

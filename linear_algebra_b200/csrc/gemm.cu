@@ -392,6 +392,7 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
 }
 
 int g_gemm_mode = LA_GEMM_SIMT;
+int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32 (la_gemm_last_engine: test hook)
 
 }  // namespace
 
@@ -410,6 +411,7 @@ extern "C" la_status la_get_gemm_mode(int* mode) {
 // Tuning hook used by tools/ and bench.py --sweep: picks the tile shape of the TMA engine
 // (0 = default).  -1 forces the generic engine.
 extern "C" la_status la_gemm_set_variant(int v) { g_gemm_variant = v; return LA_OK; }
+extern "C" int la_gemm_last_engine(void) { return g_last_engine; }
 
 extern "C" la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: unknown dtype %d", dtype);
@@ -426,12 +428,14 @@ extern "C" la_status la_mul_mat_mat(int dtype, void* C, const void* A, const voi
     if (dtype == LA_F32 && g_gemm_mode == LA_GEMM_3XTF32) {
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
-        if (handled) return LA_OK;
+        if (handled) { g_last_engine = 2; return LA_OK; }
     }
     if (tma_ok) {
+        g_last_engine = 1;
         if (dtype == LA_F32) return gemm_tma<float>((float*)C, (const float*)A, (const float*)B, M, K, N, st);
         return gemm_tma<uint32_t>((uint32_t*)C, (const uint32_t*)A, (const uint32_t*)B, M, K, N, st);   // i32 == u32 mod 2^32
     }
+    g_last_engine = 0;
     LA_DISPATCH_DTYPE(dtype, T, return gemm_generic<T>((T*)C, (const T*)A, (const T*)B, M, K, N, st));
     return LA_OK;
 }

@@ -1,9 +1,539 @@
-// csrc/gemm_tc.cu -- optional 3xTF32 tcgen05 engine for f32 GEMM (placeholder until it passes
-// the tolerance gate; reports "not handled" so la_mul_mat_mat uses the SIMT engine).
+// csrc/gemm_tc.cu -- optional 3xTF32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32).
+//
+// Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other
+// arithmetic: every f32 operand is split x = hi + lo with hi = tf32(x) (round to nearest) and
+// lo = tf32(x - hi), and each product is formed as hi*hi + hi*lo + lo*hi on the 5th-generation
+// tensor cores (tcgen05.mma kind::tf32) with FP32 accumulation in tensor memory.  The dropped
+// lo*lo term is below 2^-22 relative, so results stay inside the f32 bar of DESIGN.md section 4;
+// the mode is opt-in (la_set_gemm_mode) and tests/test_gpu_parity.py gates it on that bar.
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads):
+//   pre-pass   split_kernel        A  -> A_hi, A_lo              (scratch)
+//              transpose + split   B  -> Bt_hi, Bt_lo  (N x K)   (scratch) so both operands are K-major
+//   warp 4     TMA producer: cp.async.bulk.tensor.2d (128-byte swizzle) of the four slabs of a
+//              32-wide k-block into a STAGES-deep ring, full/empty mbarriers
+//   warp 5     allocates tensor memory; one elected lane issues 3 tcgen05.mma per 8-wide k-step
+//              (hi*lo, lo*hi, hi*hi) and tcgen05.commit's the stage back to the producer
+//   warps 0-3  epilogue: tcgen05.ld the FP32 accumulator (lane = row, column = column), 16-byte
+//              streaming stores to C
+// Roofline: tensor pipe (tf32), 3 MMAs per useful product.
 #include "common.cuh"
+#include <cuda.h>
+#include <mutex>
+
+la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st);   // transpose.cu
+
+namespace {
+
+constexpr int TC_BM = 128;          // UMMA M (cta_group::1)
+constexpr int TC_BK = 32;           // 32 f32 = 128 bytes = one swizzle row
+constexpr int TC_UMMA_K = 8;        // tf32: 32 bytes of K per instruction
+constexpr int TC_THREADS = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {     // bounded: traps instead of hanging
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (!done && spin > (1u << 22)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
+// K-major operand tile, 128-byte rows, SWIZZLE_128B: 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);      // start address
+    d |= (uint64_t)1 << 16;                           // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                 // stride byte offset between 8-row groups
+    d |= (uint64_t)1 << 46;                           // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                           // SWIZZLE_128B
+    return d;
+}
+// kind::tf32, FP32 accumulate, both operands K-major.
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int BN, int STAGES>
+struct TcShape {
+    static constexpr int A_TILE = TC_BM * TC_BK * 4;          // bytes
+    static constexpr int B_TILE = BN * TC_BK * 4;
+    static constexpr int STAGE_BYTES = 2 * A_TILE + 2 * B_TILE;
+    static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024;   // + alignment slack
+    static constexpr int TMEM_COLS = BN;                       // power of two >= 32
+    static_assert(BN == 128 || BN == 256, "accumulator columns");
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_3xtf32_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                   const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
+                   int M, int N, int K, int tiles_m) {
+    using S = TcShape<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ alignas(8) uint64_t full_bar[STAGES];
+    __shared__ alignas(8) uint64_t empty_bar[STAGES];
+    __shared__ alignas(8) uint64_t tmem_full_bar;
+    __shared__ uint32_t tmem_base_slot;
+
+    // 1024-byte aligned ring (the swizzle pattern is a function of the absolute address)
+    const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = (blockIdx.x % tiles_m) * TC_BM, n0 = (blockIdx.x / tiles_m) * BN;
+    const int num_kb = (K + TC_BK - 1) / TC_BK;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&tmem_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 5) {    // one warp allocates tensor memory and later frees it
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(S::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_slot;
+
+    if (warp == 4) {
+        // ---------------- TMA producer
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                mbar_wait(&empty_bar[s], ph ^ 1u);
+                uint8_t* st = ring_ptr + (size_t)s * S::STAGE_BYTES;
+                mbar_expect_tx(&full_bar[s], (uint32_t)S::STAGE_BYTES);
+                tma_load_2d(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
+                tma_load_2d(st + S::A_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
+                tma_load_2d(st + 2 * S::A_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0);
+                tma_load_2d(st + 2 * S::A_TILE + S::B_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0);
+            }
+        }
+    } else if (warp == 5) {
+        // ---------------- MMA issuer (one elected lane)
+        constexpr uint32_t idesc = umma_idesc_tf32(TC_BM, BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+            const int s = kb % STAGES;
+            const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+            mbar_wait(&full_bar[s], ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (elect_one()) {
+                const uint32_t st = ring + (uint32_t)s * S::STAGE_BYTES;
+                const uint64_t a_hi = umma_desc_k_sw128(st), a_lo = umma_desc_k_sw128(st + S::A_TILE);
+                const uint64_t b_hi = umma_desc_k_sw128(st + 2 * S::A_TILE), b_lo = umma_desc_k_sw128(st + 2 * S::A_TILE + S::B_TILE);
+#pragma unroll
+                for (int kk = 0; kk < TC_BK / TC_UMMA_K; ++kk) {
+                    const uint64_t adv = (uint64_t)((kk * TC_UMMA_K * 4) >> 4);     // 32 bytes of K per step
+                    // small cross terms first, then the leading term
+                    umma_tf32(tmem_d, a_hi + adv, b_lo + adv, idesc, (kb | kk) != 0);
+                    umma_tf32(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                    umma_tf32(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                }
+                umma_commit(&empty_bar[s]);                                         // frees the stage when the MMAs retire
+                if (kb == num_kb - 1) umma_commit(&tmem_full_bar);                  // accumulator complete
+            }
+            __syncwarp();
+        }
+    } else {
+        // ---------------- epilogue warps 0..3: TMEM lane quadrant = warp index
+        mbar_wait(&tmem_full_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int row = m0 + warp * 32 + lane;
+        float* crow = C + (size_t)row * N + n0;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            uint32_t v[32];
+            const uint32_t taddr = tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr) : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (row < M) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const int n = n0 + c0 + q * 4;
+                    if (n < N)      // N % 4 == 0: a 4-column chunk is wholly inside or outside
+                        __stcs(reinterpret_cast<uint4*>(crow + c0 + q * 4), make_uint4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]));
+                }
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 5) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(S::TMEM_COLS) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ accurate variant
+// The tensor core adds into its FP32 accumulator with truncation, so a long accumulation chain
+// drifts (measured: 2e-6 of sum|a||b| at K = 8192, 50x the SIMT engine).  This kernel therefore
+// lets the tensor core accumulate only TC_CHUNK_K = 64 of K at a time into one of two 256-column
+// accumulators in tensor memory; 8 epilogue warps drain the finished chunk with tcgen05.ld and add
+// it to FP32 register accumulators with ordinary round-to-nearest FADDs while the MMA warp is
+// already filling the other accumulator.  384 threads: warps 0-7 epilogue (lane quadrant =
+// warp % 4, column half = warp / 4, 128 accumulators per thread, setmaxnreg 232), warp 8 TMA
+// producer, warp 9 MMA issuer + tensor-memory owner.
+constexpr int TC_CHUNK_KB = 2;                    // k-blocks of 32 per tensor-core accumulation chain
+constexpr int TC2_BN = 256;
+constexpr int TC2_STAGES = 2;
+constexpr int TC2_THREADS = 384;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// The same box lands at the same shared-memory offset of every CTA in `mask`, and completes
+// bytes on the barrier at the same offset in each of them.
+__device__ __forceinline__ void tma_load_2d_mcast(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void umma_commit_mcast(uint64_t* bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+
+// CLUSTER == 2: the two CTAs of a cluster own vertically adjacent 128-row tiles of the same 256
+// columns; each loads half of the B slabs and TMA-multicasts it to both, which cuts L2 -> SM
+// traffic per tile by a third (the single-CTA version is L2-bandwidth bound, not tensor bound).
+template <int CLUSTER>
+__global__ void __launch_bounds__(TC2_THREADS, 1)
+gemm_3xtf32_chunked_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                           const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
+                           int M, int N, int K, int tiles_m) {
+    using S = TcShape<TC2_BN, TC2_STAGES>;
+    constexpr int BN = TC2_BN, STAGES = TC2_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ alignas(8) uint64_t full_bar[STAGES];
+    __shared__ alignas(8) uint64_t empty_bar[STAGES];
+    __shared__ alignas(8) uint64_t acc_full_bar[2];      // MMA -> epilogue: chunk finished in accumulator b
+    __shared__ alignas(8) uint64_t acc_empty_bar[2];     // epilogue -> MMA: accumulator b drained
+    __shared__ uint32_t tmem_base_slot;
+
+    const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = (blockIdx.x % tiles_m) * TC_BM, n0 = (blockIdx.x / tiles_m) * BN;
+    const int num_kb = (K + TC_BK - 1) / TC_BK;
+    const int num_chunks = (num_kb + TC_CHUNK_KB - 1) / TC_CHUNK_KB;
+    const uint32_t crank = (CLUSTER > 1) ? cluster_ctarank() : 0u;
+    constexpr uint16_t cmask = (uint16_t)((1u << CLUSTER) - 1u);
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CLUSTER); }   // a slot is free when every CTA writing into it has consumed it
+#pragma unroll
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full_bar[b], 1); mbar_init(&acc_empty_bar[b], 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 9) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (CLUSTER > 1) cluster_sync_all();          // peers' barriers are initialised before anyone signals them
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 8) {
+            // ---------------- TMA producer
+            if (lane == 0) {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int s = kb % STAGES;
+                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                    mbar_wait(&empty_bar[s], ph ^ 1u);
+                    uint8_t* st = ring_ptr + (size_t)s * S::STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[s], (uint32_t)S::STAGE_BYTES);
+                    tma_load_2d(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
+                    tma_load_2d(st + S::A_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
+                    if (CLUSTER == 1) {
+                        tma_load_2d(st + 2 * S::A_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0);
+                        tma_load_2d(st + 2 * S::A_TILE + S::B_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0);
+                    } else {
+                        // my half of the B rows, delivered to both CTAs (box = BN / 2 rows)
+                        const int half_rows = BN / CLUSTER, half_bytes = half_rows * TC_BK * 4;
+                        const int y = n0 + (int)crank * half_rows;
+                        tma_load_2d_mcast(st + 2 * S::A_TILE + crank * half_bytes, &map_b_hi, &full_bar[s], kb * TC_BK, y, cmask);
+                        tma_load_2d_mcast(st + 2 * S::A_TILE + S::B_TILE + crank * half_bytes, &map_b_lo, &full_bar[s], kb * TC_BK, y, cmask);
+                    }
+                }
+            }
+        } else if (warp == 9) {
+            // ---------------- MMA issuer
+            constexpr uint32_t idesc = umma_idesc_tf32(TC_BM, BN);
+            int kb = 0;
+            for (int c = 0; c < num_chunks; ++c) {
+                const int b = c & 1;
+                const uint32_t use = (uint32_t)(c >> 1);
+                mbar_wait(&acc_empty_bar[b], (use & 1u) ^ 1u);          // first use of each accumulator passes at once
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + (uint32_t)(b * BN);
+                const int kb_end = (kb + TC_CHUNK_KB < num_kb) ? kb + TC_CHUNK_KB : num_kb;
+                for (int first = 1; kb < kb_end; ++kb) {
+                    const int s = kb % STAGES;
+                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                    mbar_wait(&full_bar[s], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    if (elect_one()) {
+                        const uint32_t st = ring + (uint32_t)s * S::STAGE_BYTES;
+                        const uint64_t a_hi = umma_desc_k_sw128(st), a_lo = umma_desc_k_sw128(st + S::A_TILE);
+                        const uint64_t b_hi = umma_desc_k_sw128(st + 2 * S::A_TILE), b_lo = umma_desc_k_sw128(st + 2 * S::A_TILE + S::B_TILE);
+#pragma unroll
+                        for (int kk = 0; kk < TC_BK / TC_UMMA_K; ++kk) {
+                            const uint64_t adv = (uint64_t)((kk * TC_UMMA_K * 4) >> 4);
+                            umma_tf32(tmem_d, a_hi + adv, b_lo + adv, idesc, (first && kk == 0) ? 0u : 1u);
+                            umma_tf32(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                            umma_tf32(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                        }
+                        if (CLUSTER == 1) umma_commit(&empty_bar[s]);
+                        else umma_commit_mcast(&empty_bar[s], cmask);      // frees the slot in both CTAs
+                        if (kb == kb_end - 1) umma_commit(&acc_full_bar[b]);
+                    }
+                    __syncwarp();
+                    first = 0;
+                }
+            }
+        }
+    } else {
+        // ---------------- epilogue warps 0..7
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int quad = warp & 3, half = warp >> 2;
+        float acc[128];
+#pragma unroll
+        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+        for (int c = 0; c < num_chunks; ++c) {
+            const int b = c & 1;
+            const uint32_t use = (uint32_t)(c >> 1);
+            mbar_wait(&acc_full_bar[b], use & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * BN + half * 128);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t v0[32], v1[32];
+                tmem_ld32(taddr + j * 64, v0);
+                tmem_ld32(taddr + j * 64 + 32, v1);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    acc[j * 64 + i] += __uint_as_float(v0[i]);
+                    acc[j * 64 + 32 + i] += __uint_as_float(v1[i]);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty_bar[b]);
+        }
+        const int row = m0 + quad * 32 + lane;
+        if (row < M) {
+            float* crow = C + (size_t)row * N + n0 + half * 128;
+#pragma unroll
+            for (int q = 0; q < 32; ++q) {
+                const int n = n0 + half * 128 + q * 4;
+                if (n < N) __stcs(reinterpret_cast<float4*>(crow + q * 4), make_float4(acc[q * 4], acc[q * 4 + 1], acc[q * 4 + 2], acc[q * 4 + 3]));
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (CLUSTER > 1) cluster_sync_all();          // nobody leaves while a peer may still write into it
+    if (warp == 9) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+    }
+}
+
+// x -> hi = tf32(x) (round to nearest), lo = tf32(x - hi); 16-byte packets, streaming.
+__global__ void __launch_bounds__(256)
+split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4) {
+    const size_t stride = (size_t)gridDim.x * 256;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
+        float4 h, l;
+        const float in[4] = {v.x, v.y, v.z, v.w};
+        float ho[4], lo_[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            uint32_t hb, lb;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(in[e]));
+            ho[e] = __uint_as_float(hb);
+            const float d = in[e] - ho[e];
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(d));
+            lo_[e] = __uint_as_float(lb);
+        }
+        h = make_float4(ho[0], ho[1], ho[2], ho[3]); l = make_float4(lo_[0], lo_[1], lo_[2], lo_[3]);
+        __stcs(reinterpret_cast<float4*>(hi) + i, h);
+        __stcs(reinterpret_cast<float4*>(lo) + i, l);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+la_status tc_get_encode(EncodeTiledFn* out) {
+    static EncodeTiledFn fn = nullptr;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        LA_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (q != cudaDriverEntryPointSuccess || !p) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+        fn = (EncodeTiledFn)p;
+    }
+    *out = fn;
+    return LA_OK;
+}
+
+// rows x K row-major f32, box = box_rows x 32 (128 bytes), 128-byte swizzle
+la_status tc_make_map(CUtensorMap* map, const float* base, size_t rows, size_t K, int box_rows) {
+    EncodeTiledFn enc; LA_TRY(tc_get_encode(&enc));
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 4};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled (3xTF32) failed with CUresult %d", (int)r);
+    return LA_OK;
+}
+
+template <int BN, int STAGES>
+la_status tc_launch(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
+    using S = TcShape<BN, STAGES>;
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128));
+    // a TMA box is at most 256 rows: B_TILE of BN rows in one request
+    LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, BN));
+    auto kern = gemm_3xtf32_kernel<BN, STAGES>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM_BYTES));
+    const size_t tm = (M + TC_BM - 1) / TC_BM, tn = (N + BN - 1) / BN;
+    kern<<<(unsigned)(tm * tn), TC_THREADS, S::SMEM_BYTES, st>>>(C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, (int)K, (int)tm);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
+template <int CLUSTER>
+la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
+    using S = TcShape<TC2_BN, TC2_STAGES>;
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128));
+    LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, TC2_BN / CLUSTER)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, TC2_BN / CLUSTER));
+    auto kern = gemm_3xtf32_chunked_kernel<CLUSTER>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM_BYTES));
+    size_t tm = (M + TC_BM - 1) / TC_BM;
+    const size_t tn = (N + TC2_BN - 1) / TC2_BN;
+    tm = (tm + CLUSTER - 1) / CLUSTER * CLUSTER;      // whole clusters along M; surplus tiles are all out of bounds
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(tm * tn)); cfg.blockDim = dim3(TC2_THREADS); cfg.dynamicSmemBytes = S::SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CLUSTER; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, (int)K, (int)tm));
+    return LA_OK;
+}
+
+int g_tc_variant = 0;
+
+}  // namespace
+
+extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA_OK; }     // tuning hook
 
 la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled) {
-    (void)C; (void)A; (void)B; (void)M; (void)K; (void)N; (void)st;
     *handled = false;
-    return LA_OK;
+    if (M < 128 || N < 128 || K < 32 || K % 4 != 0 || N % 4 != 0 || M % 4 != 0 || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C) ||
+        M >= (1u << 31) || N >= (1u << 31) || K >= (1u << 31))
+        return LA_OK;                              // the SIMT engine takes it
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    const size_t a_elems = M * K, b_elems = K * N;
+    void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 3 * b_elems) * sizeof(float), &scratch));
+    float* a_hi = (float*)((char*)scratch + LA_SCRATCH_ZEROED);
+    float* a_lo = a_hi + a_elems;
+    float* bt = a_lo + a_elems;                    // B^T (N x K)
+    float* b_hi = bt + b_elems;
+    float* b_lo = b_hi + b_elems;
+    const unsigned blocks = (unsigned)info->sm_count * 8;
+    split_tf32_kernel<<<blocks, 256, 0, st>>>(a_hi, a_lo, A, a_elems / 4);
+    LA_LAUNCH_CHECK();
+    LA_TRY(la_transpose_raw32((uint32_t*)bt, (const uint32_t*)B, K, N, st));
+    split_tf32_kernel<<<blocks, 256, 0, st>>>(b_hi, b_lo, bt, b_elems / 4);
+    LA_LAUNCH_CHECK();
+    la_status s;
+    switch (g_tc_variant) {
+    default:
+    case 0: s = tc_launch_chunked<2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // meets the f32 bar; B multicast over CTA pairs
+    case 3: s = tc_launch_chunked<1>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // same, no clusters
+    case 1: s = tc_launch<256, 2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;      // single chain (tuning reference; less accurate)
+    case 2: s = tc_launch<128, 3>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;
+    }
+    if (s == LA_OK) *handled = true;
+    return s;
 }

@@ -248,6 +248,25 @@ def test_matmat_every_engine_variant(la, variant):
         lib.la_gemm_set_variant(0)
 
 
+@pytest.mark.parametrize("tc_variant", [0, 3])
+def test_matmat_3xtf32_engine_meets_the_f32_bar(la, tc_variant):
+    """LA_GEMM_3XTF32 (tcgen05 tensor cores, hi/lo split) must pass the SAME gate as the SIMT
+    engine, and must really be the engine that ran."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    lib.la_gemm_tc_set_variant(tc_variant)
+    try:
+        for M, K, N in ((128, 32, 128), (256, 256, 256), (512, 1000, 384), (388, 1004, 260), (1024, 2048, 512)):
+            check_f32_gemm(la, gen.values("f32", M * K, 41), gen.values("f32", K * N, 42), M, K, N, ("3xtf32", tc_variant, M, K, N))
+            assert lib.la_gemm_last_engine() == 2, "3xTF32 engine did not take %dx%dx%d" % (M, K, N)
+        # shapes it does not cover fall through to the SIMT / generic engines
+        check_f32_gemm(la, gen.values("f32", 33 * 17, 43), gen.values("f32", 17 * 29, 44), 33, 17, 29, "fallthrough")
+        assert lib.la_gemm_last_engine() == 0
+    finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_SIMT)
+        lib.la_gemm_tc_set_variant(0)
+
+
 def test_matmat_f64(la):
     M, K, N = 70, 33, 65
     a = gen.values("f64", M * K, 29); b = gen.values("f64", K * N, 30)

@@ -50,6 +50,29 @@ def main():
                 except Exception as e:  # noqa: BLE001
                     print("n=%d %s variant %d FAILED: %s" % (n, label, v, e), flush=True)
         lib.lib.la_gemm_set_variant(0)
+        # tensor-core engine
+        lib.call("la_set_gemm_mode", 1)
+        for tv, desc in ((0, "3xTF32 chunked 128x256 cluster2 B-multicast"), (3, "3xTF32 chunked 128x256"), (1, "3xTF32 single-chain 128x256")):
+            lib.lib.la_gemm_tc_set_variant(tv)
+            try:
+                def f():
+                    lib.call("la_mul_mat_mat", 8, C.data.ptr, A.data.ptr, B.data.ptr, n, n, n, None)
+                for _ in range(2):
+                    f()
+                la.synchronize()
+                e0, e1 = la.Event(), la.Event()
+                e0.record()
+                for _ in range(5):
+                    f()
+                e1.record()
+                ms = e0.elapsed_ms(e1) / 5
+                c = C.to_vec()
+                got = np.array([c[r * n + cc] for r, cc in zip(rows, cols)])
+                print("n=%d f32 tc variant %d (%s): %.3f ms  %.2f TFLOP/s  maxerr %.2e  engine %d" % (n, tv, desc, ms, 2.0 * n ** 3 / ms / 1e9, float(np.max(np.abs(got - truth))), lib.lib.la_gemm_last_engine()), flush=True)
+            except Exception as e:  # noqa: BLE001
+                print("n=%d tc variant %d FAILED: %s" % (n, tv, e), flush=True)
+        lib.call("la_set_gemm_mode", 0)
+        lib.lib.la_gemm_tc_set_variant(0)
 
 
 if __name__ == "__main__":

@@ -150,7 +150,7 @@ def extras(la, hbm_peak, peak_src):
     n = 1 << 28
     A = la.Vector.uninitialized(n, "f32"); B = la.Vector.uninitialized(n, "f32"); C = la.Vector.uninitialized(n, "f32")
     one = np.array([1.0], np.float32); two = np.array([1.0000001], np.float32)
-    lib.call("la_fill", 8, A.ptr, one.ctypes.data, n, None); lib.call("la_fill", 8, B.ptr, two.ctypes.data, n, None)
+    lib.call("la_synth", 8, A.ptr, 0x5EED0001, n, None); lib.call("la_synth", 8, B.ptr, 0x5EED1001, n, None)
 
     def rec(name, ms, nbytes):
         gbs = nbytes / ms / 1e6
@@ -167,7 +167,7 @@ def extras(la, hbm_peak, peak_src):
     # Matrix x Vector at 32768^2 (4 GiB): reuse A's storage? allocate a fresh matrix
     r = 32768
     M = la.Vector.uninitialized(r * r, "f32"); v = la.Vector.uninitialized(r, "f32"); y = la.Vector.uninitialized(r, "f32")
-    lib.call("la_fill", 8, M.ptr, one.ctypes.data, r * r, None); lib.call("la_fill", 8, v.ptr, two.ctypes.data, r, None)
+    lib.call("la_synth", 8, M.ptr, 0x5EED0002, r * r, None); lib.call("la_synth", 8, v.ptr, 0x5EED1002, r, None)
     rec("mat_x_vec_f32_32768^2", timed(la, lambda: lib.call("la_mul_vec_transpose_mat", 8, y.ptr, v.ptr, M.ptr, r, r, None), 5, 2), 4 * (r * r + 2 * r))
     rec("vec_x_mat_f32_32768^2", timed(la, lambda: lib.call("la_mul_vec_mat", 8, y.ptr, v.ptr, M.ptr, r, r, None), 5, 2), 4 * (r * r + 2 * r))
     del M, v, y, A
@@ -175,10 +175,36 @@ def extras(la, hbm_peak, peak_src):
     k = 8192
     X = la.Vector.uninitialized(k * k, "i32"); Y = la.Vector.uninitialized(k * k, "i32"); Z = la.Vector.uninitialized(k * k, "i32")
     three = np.array([3], np.int32)
-    lib.call("la_fill", 5, X.ptr, three.ctypes.data, k * k, None); lib.call("la_fill", 5, Y.ptr, three.ctypes.data, k * k, None)
+    lib.call("la_synth", 5, X.ptr, 0x5EED0004, k * k, None); lib.call("la_synth", 5, Y.ptr, 0x5EED1004, k * k, None)
     rec("transpose_i32_8192^2", timed(la, lambda: lib.call("la_transpose", 5, Z.ptr, X.ptr, k, k, None), 10), 8 * k * k)
     ms = timed(la, lambda: lib.call("la_mul_mat_mat", 5, Z.ptr, X.ptr, Y.ptr, k, k, k, None), 3, 1)
-    out["gemm_i32_8192^2"] = {"ms": round(ms, 3), "Gop/s": round(2.0 * k ** 3 / ms / 1e6, 1)}
+    sm = __import__("ctypes").c_int(); lib.call("la_sm_count", __import__("ctypes").byref(sm))
+    imad_peak = sm.value * 64 * 2 * 1965e6 / 1e12
+    out["gemm_i32_8192^2"] = {"ms": round(ms, 3), "Top/s": round(2.0 * k ** 3 / ms / 1e9, 2),
+                              "frac_of_nominal_int32_mad_peak": round(2.0 * k ** 3 / ms / 1e9 / imad_peak, 3),
+                              "peak_note": "nominal: %d SMs x 64 IMAD lanes x 2 x 1965 MHz = %.1f Top/s" % (sm.value, imad_peak)}
+    del X, Y, Z
+    # f32 GEMM sweep (BASELINE.json configs[3]) on both engines; the tensor-core engine is opt-in
+    # (LA_GEMM_3XTF32: tf32 hi/lo split, 3 tcgen05 MMAs per product, FP32 accumulate, same f32 bar)
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    tf32_peak = peaks.get("bf16_tflops", 1590.0) / 2.0          # tf32 runs at half the bf16 rate
+    sweep = {}
+    for nn in (2048, 4096, 8192, 16384):
+        P = la.Vector.uninitialized(nn * nn, "f32"); Q = la.Vector.uninitialized(nn * nn, "f32"); R = la.Vector.uninitialized(nn * nn, "f32")
+        lib.call("la_synth", 8, P.ptr, 0x5EED0003, nn * nn, None); lib.call("la_synth", 8, Q.ptr, 0x5EED1003, nn * nn, None)   # U[-1,1), generated on the device
+        row = {}
+        for mode, label in ((0, "simt"), (1, "3xtf32")):
+            lib.call("la_set_gemm_mode", mode)
+            it = 3 if nn >= 8192 else 10
+            ms = timed(la, lambda: lib.call("la_mul_mat_mat", 8, R.ptr, P.ptr, Q.ptr, nn, nn, nn, None), it, 2)
+            row[label] = {"ms": round(ms, 4), "TFLOP/s": round(2.0 * nn ** 3 / ms / 1e9, 2)}
+        lib.call("la_set_gemm_mode", 0)
+        row["3xtf32"]["roofline"] = {"bound": "tensor", "achieved": round(3 * row["3xtf32"]["TFLOP/s"], 1), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
+                                      "frac": round(3 * row["3xtf32"]["TFLOP/s"] / tf32_peak, 3),
+                                      "note": "achieved = tf32 MMA flops issued (3 per useful f32 product, pre-pass included in the time); peak = measured bf16 / 2"}
+        sweep[str(nn)] = row
+        del P, Q, R
+    out["gemm_f32_sweep"] = sweep
     out["_hbm_peak_GB/s"] = hbm_peak
     out["_hbm_peak_source"] = peak_src
     return out

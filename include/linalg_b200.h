@@ -88,6 +88,10 @@ la_status la_upload(void* dst_dev, const void* src_host, size_t bytes, void* str
 la_status la_download(void* dst_host, const void* src_dev, size_t bytes, void* stream); /* returns after the copy */
 la_status la_copy(void* dst_dev, const void* src_dev, size_t bytes, void* stream);
 la_status la_fill(int dtype, void* dst_dev, const void* value_host, size_t n, void* stream);
+/* Synthetic data generated on the device (no counterpart in the reference; bench / test utility):
+ * element i = f(splitmix64(seed ^ i)): floats uniform in [-1,1) from the top 24 (f32) / 53 (f64)
+ * bits, integers the top 8*sizeof(T) bits.  Reproducible on the host (linear_algebra_b200.synth). */
+la_status la_synth(int dtype, void* dst_dev, uint64_t seed, size_t n, void* stream);
 la_status la_host_alloc(void** host_ptr, size_t bytes);            /* pinned host memory */
 la_status la_host_free(void* host_ptr);
 la_status la_stream_create(void** stream);

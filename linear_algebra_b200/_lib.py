@@ -47,6 +47,7 @@ SIGNATURES = {
     "la_download": [_V, _V, _Z, _V],
     "la_copy": [_V, _V, _Z, _V],
     "la_fill": [_I, _V, _V, _Z, _V],
+    "la_synth": [_I, _V, ctypes.c_uint64, _Z, _V],
     "la_host_alloc": [_PV, _Z],
     "la_host_free": [_V],
     "la_stream_create": [_PV],

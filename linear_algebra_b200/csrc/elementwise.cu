@@ -148,6 +148,27 @@ __global__ void __launch_bounds__(EW_THREADS) fill_kernel(T* dst, T value, size_
     for (size_t i = (size_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) dst[i] = value;
 }
 
+// Synthetic operands generated on the device: counter-based, element i
+// depends only on (seed, i), so the host can reproduce any element without moving the array.
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+template <typename T> __device__ __forceinline__ T synth_value(uint64_t bits);
+template <> __device__ __forceinline__ float synth_value<float>(uint64_t bits) { return (float)(bits >> 40) * (2.0f / 16777216.0f) - 1.0f; }       // U[-1,1), 24 bits
+template <> __device__ __forceinline__ double synth_value<double>(uint64_t bits) { return (double)(bits >> 11) * (2.0 / 9007199254740992.0) - 1.0; }
+#define LA_SYNTH_INT(T) template <> __device__ __forceinline__ T synth_value<T>(uint64_t bits) { return (T)(bits >> (64 - 8 * sizeof(T))); }
+LA_SYNTH_INT(uint8_t) LA_SYNTH_INT(int8_t) LA_SYNTH_INT(uint16_t) LA_SYNTH_INT(int16_t)
+LA_SYNTH_INT(uint32_t) LA_SYNTH_INT(int32_t) LA_SYNTH_INT(uint64_t) LA_SYNTH_INT(int64_t)
+
+template <typename T>
+__global__ void __launch_bounds__(EW_THREADS) synth_kernel(T* dst, uint64_t seed, size_t n) {
+    const size_t stride = (size_t)gridDim.x * EW_THREADS;
+    for (size_t i = (size_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) dst[i] = synth_value<T>(splitmix64(seed ^ (uint64_t)i));
+}
+
 la_status check_common(int dtype, size_t n) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "unknown dtype %d", dtype);
     (void)n;
@@ -212,6 +233,21 @@ extern "C" la_status la_fill(int dtype, void* dst_dev, const void* value_host, s
         const size_t cap = (size_t)info->sm_count * 16;
         if (blocks > cap) blocks = cap;
         fill_kernel<T><<<(unsigned)blocks, EW_THREADS, 0, (cudaStream_t)stream>>>((T*)dst_dev, *(const T*)value_host, n);
+    });
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
+extern "C" la_status la_synth(int dtype, void* dst_dev, uint64_t seed, size_t n, void* stream) {
+    LA_TRY(check_common(dtype, n));
+    if (n && !dst_dev) return la_fail(LA_ERR_ARG, "la_synth: NULL operand");
+    if (n == 0) return LA_OK;
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    LA_DISPATCH_DTYPE(dtype, T, {
+        size_t blocks = (n + EW_THREADS - 1) / EW_THREADS;
+        const size_t cap = (size_t)info->sm_count * 16;
+        if (blocks > cap) blocks = cap;
+        synth_kernel<T><<<(unsigned)blocks, EW_THREADS, 0, (cudaStream_t)stream>>>((T*)dst_dev, seed, n);
     });
     LA_LAUNCH_CHECK();
     return LA_OK;

@@ -22,6 +22,7 @@
 // Roofline: FP32 FMA pipe (f32), integer multiply-add pipe (i32/u32).  Work: 2*M*N*K flop.
 #include "common.cuh"
 #include <cuda.h>
+#include <cstdlib>
 #include <mutex>
 
 la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st);   // transpose.cu
@@ -391,7 +392,12 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
     }
 }
 
-int g_gemm_mode = LA_GEMM_SIMT;
+// LA_GEMM_MODE=3xtf32 in the environment selects the tensor-core engine at load time.
+int initial_gemm_mode() {
+    const char* e = getenv("LA_GEMM_MODE");
+    return (e && (e[0] == '3' || e[0] == 't' || e[0] == 'T')) ? LA_GEMM_3XTF32 : LA_GEMM_SIMT;
+}
+int g_gemm_mode = initial_gemm_mode();
 int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32 (la_gemm_last_engine: test hook)
 
 }  // namespace

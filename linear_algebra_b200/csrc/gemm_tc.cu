@@ -7,15 +7,22 @@
 // lo*lo term is below 2^-22 relative, so results stay inside the f32 bar of DESIGN.md section 4;
 // the mode is opt-in (la_set_gemm_mode) and tests/test_gpu_parity.py gates it on that bar.
 //
-// Structure (one 128 x BN output tile per CTA, 192 threads):
-//   pre-pass   split_kernel        A  -> A_hi, A_lo              (scratch)
+// Kernels in this file (la_gemm_tc_set_variant picks one; 0 is the default):
+//   0  gemm_3xtf32_2cta_kernel      CTA pairs (tcgen05 cta_group::2), 256x256 tile per pair, 3-stage
+//                                   TMA ring, chunked accumulation              <- meets the f32 bar
+//   5/3 gemm_3xtf32_chunked_kernel  one CTA per 128x256 tile (with / without B multicast), chunked
+//   1/2 gemm_3xtf32_kernel          single accumulation chain (tuning reference; drifts, see below)
+// Common structure:
+//   pre-pass   split_tf32_kernel   A  -> A_hi, A_lo              (scratch)
 //              transpose + split   B  -> Bt_hi, Bt_lo  (N x K)   (scratch) so both operands are K-major
-//   warp 4     TMA producer: cp.async.bulk.tensor.2d (128-byte swizzle) of the four slabs of a
-//              32-wide k-block into a STAGES-deep ring, full/empty mbarriers
-//   warp 5     allocates tensor memory; one elected lane issues 3 tcgen05.mma per 8-wide k-step
+//   TMA warp   cp.async.bulk.tensor.2d (128-byte swizzle) of the four slabs of a 32-wide k-block
+//              into a ring guarded by full/empty mbarriers
+//   MMA warp   owns tensor memory; one elected lane issues 3 tcgen05.mma per 8-wide k-step
 //              (hi*lo, lo*hi, hi*hi) and tcgen05.commit's the stage back to the producer
-//   warps 0-3  epilogue: tcgen05.ld the FP32 accumulator (lane = row, column = column), 16-byte
-//              streaming stores to C
+//   epilogue   tcgen05.ld of the FP32 accumulator (lane = row, column = column), FP32 adds in
+//              registers, 16-byte streaming stores to C
+// Non-finite inputs: inf * (lo == 0) is NaN, so infinities do not propagate as in plain f32
+// arithmetic; that is one reason the mode is opt-in.
 // Roofline: tensor pipe (tf32), 3 MMAs per useful product.
 #include "common.cuh"
 #include <cuda.h>
@@ -409,6 +416,183 @@ gemm_3xtf32_chunked_kernel(float* __restrict__ C, const __grid_constant__ CUtens
     }
 }
 
+// ------------------------------------------------------------------ CTA-pair variant (cta_group::2)
+// Two CTAs on the SMs of one TPC share one 256 x 256 output tile: CTA r owns rows r*128.. of it
+// (its own tensor memory holds those 128 accumulator rows) and loads its 128 rows of A plus HALF
+// of the B slabs (128 of the 256 columns); tcgen05.mma.cta_group::2, issued by the leader CTA
+// only, reads both CTAs' shared memory.  Per CTA and 32-wide k-block only 64 KB enter shared
+// memory (the single-CTA kernel needs 96 KB, which runs into the SM's ingest rate), and the ring
+// gets 3 stages.  Accumulation is chunked exactly as above; the leader's MMA warp waits for the
+// epilogue warps of BOTH CTAs before it reuses an accumulator.
+constexpr int TC3_STAGES = 3;
+constexpr int TC3_THREADS = 384;
+constexpr int TC3_TILE = 128 * TC_BK * 4;                         // one 128-row slab: 16 KB
+constexpr int TC3_STAGE_BYTES = 4 * TC3_TILE;                     // A_hi, A_lo, Bhalf_hi, Bhalf_lo
+constexpr size_t TC3_SMEM_BYTES = (size_t)TC3_STAGES * TC3_STAGE_BYTES + 1024;
+
+__device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y) {
+    // the transaction bytes are counted on the LEADER CTA's barrier (peer bit of the address cleared)
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_2sm(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {   // arrives on the barrier at this offset in BOTH CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_on_leader(uint64_t* bar) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(smem_u32(bar)));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+
+__global__ void __launch_bounds__(TC3_THREADS, 1)
+gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                        const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
+                        int M, int N, int K, int pair_tiles_m) {
+    constexpr int STAGES = TC3_STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ alignas(8) uint64_t full_bar[STAGES];     // used in the leader: both CTAs' slabs have landed
+    __shared__ alignas(8) uint64_t empty_bar[STAGES];    // per CTA: the pair's MMAs are done with this slot
+    __shared__ alignas(8) uint64_t acc_full_bar[2];      // per CTA: chunk finished in accumulator b
+    __shared__ alignas(8) uint64_t acc_empty_bar[2];     // used in the leader: 16 epilogue warps drained accumulator b
+    __shared__ uint32_t tmem_base_slot;
+
+    const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1;
+    const int m0 = (pair % pair_tiles_m) * 256 + (int)crank * 128;
+    const int n0 = (pair / pair_tiles_m) * 256;
+    const int num_kb = (K + TC_BK - 1) / TC_BK;
+    const int num_chunks = (num_kb + TC_CHUNK_KB - 1) / TC_CHUNK_KB;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+#pragma unroll
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full_bar[b], 1); mbar_init(&acc_empty_bar[b], 16); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 9) {    // the same warp of both CTAs allocates the pair's tensor memory
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 8) {
+            // ---------------- TMA producer (both CTAs)
+            if (lane == 0) {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int s = kb % STAGES;
+                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                    mbar_wait(&empty_bar[s], ph ^ 1u);
+                    uint8_t* st = ring_ptr + (size_t)s * TC3_STAGE_BYTES;
+                    if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * TC3_STAGE_BYTES);     // my slabs + the peer's
+                    tma_load_2d_2sm(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
+                    tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
+                    tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
+                    tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
+                }
+            }
+        } else if (warp == 9 && crank == 0) {
+            // ---------------- MMA issuer (leader CTA only)
+            constexpr uint32_t idesc = umma_idesc_tf32(256, 256);
+            int kb = 0;
+            for (int c = 0; c < num_chunks; ++c) {
+                const int b = c & 1;
+                const uint32_t use = (uint32_t)(c >> 1);
+                mbar_wait(&acc_empty_bar[b], (use & 1u) ^ 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + (uint32_t)(b * 256);
+                const int kb_end = (kb + TC_CHUNK_KB < num_kb) ? kb + TC_CHUNK_KB : num_kb;
+                for (int first = 1; kb < kb_end; ++kb) {
+                    const int s = kb % STAGES;
+                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                    mbar_wait(&full_bar[s], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    if (elect_one()) {
+                        const uint32_t st = ring + (uint32_t)s * TC3_STAGE_BYTES;
+                        const uint64_t a_hi = umma_desc_k_sw128(st), a_lo = umma_desc_k_sw128(st + TC3_TILE);
+                        const uint64_t b_hi = umma_desc_k_sw128(st + 2 * TC3_TILE), b_lo = umma_desc_k_sw128(st + 3 * TC3_TILE);
+#pragma unroll
+                        for (int kk = 0; kk < TC_BK / TC_UMMA_K; ++kk) {
+                            const uint64_t adv = (uint64_t)((kk * TC_UMMA_K * 4) >> 4);
+                            umma_tf32_2sm(tmem_d, a_hi + adv, b_lo + adv, idesc, (first && kk == 0) ? 0u : 1u);
+                            umma_tf32_2sm(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                            umma_tf32_2sm(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                        }
+                        umma_commit_2sm(&empty_bar[s]);
+                        if (kb == kb_end - 1) umma_commit_2sm(&acc_full_bar[b]);
+                    }
+                    __syncwarp();
+                    first = 0;
+                }
+            }
+        }
+    } else {
+        // ---------------- epilogue warps 0..7 (both CTAs; each drains its own tensor memory)
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int quad = warp & 3, half = warp >> 2;
+        float acc[128];
+#pragma unroll
+        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+        for (int c = 0; c < num_chunks; ++c) {
+            const int b = c & 1;
+            const uint32_t use = (uint32_t)(c >> 1);
+            mbar_wait(&acc_full_bar[b], use & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * 256 + half * 128);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t v0[32], v1[32];
+                tmem_ld32(taddr + j * 64, v0);
+                tmem_ld32(taddr + j * 64 + 32, v1);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    acc[j * 64 + i] += __uint_as_float(v0[i]);
+                    acc[j * 64 + 32 + i] += __uint_as_float(v1[i]);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive_on_leader(&acc_empty_bar[b]);
+        }
+        const int row = m0 + quad * 32 + lane;
+        if (row < M) {
+            float* crow = C + (size_t)row * N + n0 + half * 128;
+#pragma unroll
+            for (int q = 0; q < 32; ++q) {
+                const int n = n0 + half * 128 + q * 4;
+                if (n < N) __stcs(reinterpret_cast<float4*>(crow + q * 4), make_float4(acc[q * 4], acc[q * 4 + 1], acc[q * 4 + 2], acc[q * 4 + 3]));
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 9) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+    }
+}
+
 // x -> hi = tf32(x) (round to nearest), lo = tf32(x - hi); 16-byte packets, streaming.
 __global__ void __launch_bounds__(256)
 split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4) {
@@ -501,6 +685,22 @@ la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, cons
     return LA_OK;
 }
 
+la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
+    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128));
+    LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, 128)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, 128));
+    LA_CUDA(cudaFuncSetAttribute(gemm_3xtf32_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
+    const size_t ptm = (M + 255) / 256, tn = (N + 255) / 256;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * ptm * tn)); cfg.blockDim = dim3(TC3_THREADS); cfg.dynamicSmemBytes = TC3_SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LA_CUDA(cudaLaunchKernelEx(&cfg, gemm_3xtf32_2cta_kernel, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, (int)K, (int)ptm));
+    return LA_OK;
+}
+
 int g_tc_variant = 0;
 
 }  // namespace
@@ -529,7 +729,8 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
     la_status s;
     switch (g_tc_variant) {
     default:
-    case 0: s = tc_launch_chunked<2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // meets the f32 bar; B multicast over CTA pairs
+    case 0: s = tc_launch_2cta(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;         // CTA pairs, tcgen05 cta_group::2 (default)
+    case 5: s = tc_launch_chunked<2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // one CTA per tile, B multicast over CTA pairs
     case 3: s = tc_launch_chunked<1>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // same, no clusters
     case 1: s = tc_launch<256, 2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;      // single chain (tuning reference; less accurate)
     case 2: s = tc_launch<128, 3>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;

@@ -104,6 +104,14 @@ class Vector:
         return res
 
     @staticmethod
+    def synth(seed, size, dtype):
+        """Device-generated synthetic data (la_synth); see linear_algebra_b200.synth for the host mirror."""
+        res = Vector.uninitialized(size, dtype)
+        call("la_synth", res.dtype.code, res._ptr, int(seed), res._len, _STREAM)
+        _done()
+        return res
+
+    @staticmethod
     def from_vec(v, dtype=None):
         host = np.ascontiguousarray(v, dtype=None if dtype is None else parameter(dtype).np).reshape(-1)
         dt = parameter(dtype if dtype is not None else host.dtype)

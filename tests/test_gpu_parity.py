@@ -248,7 +248,7 @@ def test_matmat_every_engine_variant(la, variant):
         lib.la_gemm_set_variant(0)
 
 
-@pytest.mark.parametrize("tc_variant", [0, 3])
+@pytest.mark.parametrize("tc_variant", [0, 3, 5])
 def test_matmat_3xtf32_engine_meets_the_f32_bar(la, tc_variant):
     """LA_GEMM_3XTF32 (tcgen05 tensor cores, hi/lo split) must pass the SAME gate as the SIMT
     engine, and must really be the engine that ran."""
@@ -300,3 +300,14 @@ def test_transpose(la, name):
         T = la.Matrix.from_vec(a, R, C, dt(la, name)).transpose()
         assert T.len() == (C, R)
         assert same(T.to_vec(), P.transpose(a, R, C)), (name, R, C)
+
+
+# ------------------------------------------------------------------ device-side synthetic data
+@pytest.mark.parametrize("name", gen.ALL_NAMES)
+def test_synth_matches_host_mirror(la, name):
+    from linear_algebra_b200 import synth
+    n = 100003
+    got = la.Vector.synth(0x5EED0001, n, dt(la, name)).to_vec()
+    assert same(got, synth.values(dt(la, name), 0x5EED0001, 0, n)), name
+    if np.dtype(got.dtype).kind == "f":
+        assert got.min() >= -1.0 and got.max() < 1.0 and abs(float(got.mean())) < 0.02

@@ -52,7 +52,7 @@ def main():
         lib.lib.la_gemm_set_variant(0)
         # tensor-core engine
         lib.call("la_set_gemm_mode", 1)
-        for tv, desc in ((0, "3xTF32 chunked 128x256 cluster2 B-multicast"), (3, "3xTF32 chunked 128x256"), (1, "3xTF32 single-chain 128x256")):
+        for tv, desc in ((0, "3xTF32 chunked 2-CTA 256x256 cta_group::2"), (5, "3xTF32 chunked 128x256 cluster2 B-multicast"), (3, "3xTF32 chunked 128x256"), (1, "3xTF32 single-chain 128x256")):
             lib.lib.la_gemm_tc_set_variant(tv)
             try:
                 def f():

@@ -11,9 +11,7 @@ import linear_algebra_b200 as la  # noqa: E402
 la.init(0)
 lib = la._lib
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
-one = np.array([0.5], np.float32)
-A = la.Vector.uninitialized(n * n, "f32"); B = la.Vector.uninitialized(n * n, "f32"); C = la.Vector.uninitialized(n * n, "f32")
-lib.call("la_fill", 8, A.ptr, one.ctypes.data, n * n, None); lib.call("la_fill", 8, B.ptr, one.ctypes.data, n * n, None)
+A = la.Vector.synth(0x5EED0003, n * n, "f32"); B = la.Vector.synth(0x5EED1003, n * n, "f32"); C = la.Vector.uninitialized(n * n, "f32")   # U[-1,1)
 lib.call("la_set_gemm_mode", 1)
 for _ in range(3):
     lib.call("la_mul_mat_mat", 8, C.ptr, A.ptr, B.ptr, n, n, n, None)

@@ -2,11 +2,14 @@
 """bench.py -- the hot path's headline metric on B200.
 
 Headline (BASELINE.json `metric`): f32 GEMM GFLOP/s at 8192^2.  A "step" is one
-C = A x B of 8192 x 8192 f32 matrices through la_mul_mat_mat (A^T staging + TMA SIMT kernel),
-operands resident in HBM.  With N GPUs the 8192^2 problem is row-block sharded (A and C split by
+C = A x B of 8192 x 8192 f32 matrices through la_mul_mat_mat with the library's default engine
+selection (LA_GEMM_AUTO: the tcgen05 3xTF32 engine, which meets the same f32 tolerance gate as
+the FP32 SIMT engine; `--engine simt` times the SIMT engine instead, and `extra.gemm_f32_sweep`
+always carries both), operands resident in HBM.  With N GPUs the 8192^2 problem is row-block sharded (A and C split by
 rows, B replicated, no data-path collective): strong scaling, value = total flop / max-over-ranks
-time.  `e2e` is the same GEMM through the public Matrix API with pinned HOST buffers (upload A, B;
-multiply; download C inside the timed region).  `extra` carries the vector-op HBM GB/s figures
+time.  `e2e` is the same GEMM on pinned HOST buffers through the public streamed call mul_host /
+la_mul_mat_mat_host (upload A and B, multiply, download C, all inside the timed region);
+`e2e.three_call` is the reference-style from_vec, from_vec, `*`, to_vec sequence.  `extra` carries the vector-op HBM GB/s figures
 the metric also names (elementwise 2^28 f32, dot/sum, Matrix x Vector at 32768^2, i32 8192^2).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-extra]
@@ -198,7 +201,7 @@ def extras(la, hbm_peak, peak_src):
             it = 3 if nn >= 8192 else 10
             ms = timed(la, lambda: lib.call("la_mul_mat_mat", 8, R.ptr, P.ptr, Q.ptr, nn, nn, nn, None), it, 2)
             row[label] = {"ms": round(ms, 4), "TFLOP/s": round(2.0 * nn ** 3 / ms / 1e9, 2)}
-        lib.call("la_set_gemm_mode", 0)
+        lib.call("la_set_gemm_mode", 2)
         row["3xtf32"]["roofline"] = {"bound": "tensor", "achieved": round(3 * row["3xtf32"]["TFLOP/s"], 1), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
                                       "frac": round(3 * row["3xtf32"]["TFLOP/s"] / tf32_peak, 3),
                                       "note": "achieved = tf32 MMA flops issued (3 per useful f32 product, pre-pass included in the time); peak = measured bf16 / 2"}
@@ -208,6 +211,25 @@ def extras(la, hbm_peak, peak_src):
     out["_hbm_peak_GB/s"] = hbm_peak
     out["_hbm_peak_source"] = peak_src
     return out
+
+
+def ncu_traffic(path, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of `kernel` per launch, from the committed ncu summary."""
+    try:
+        rd = wr = None
+        hit = False
+        for ln in open(os.path.join(ROOT, path)):
+            if ln.startswith("== "):
+                if hit:
+                    break
+                hit = kernel in ln
+            elif hit and "dram__bytes_read.sum " in ln:
+                v, u = ln.split()[1:3]; rd = float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[u]
+            elif hit and "dram__bytes_write.sum " in ln:
+                v, u = ln.split()[1:3]; wr = float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[u]
+        return None if rd is None or wr is None else {"dram_bytes_per_launch": int(rd + wr), "source": path}
+    except OSError:
+        return None
 
 
 def run_ours(args):
@@ -233,6 +255,9 @@ def run_ours(args):
     A = la.Matrix.from_vec(hA, rows, n); B = la.Matrix.from_vec(hB, n, n)
     C = la.Matrix.uninitialized(rows, n, "f32")
 
+    mode = {"auto": lib.GEMM_AUTO, "simt": lib.GEMM_SIMT, "3xtf32": lib.GEMM_3XTF32}[args.engine]
+    lib.call("la_set_gemm_mode", mode)
+
     def step():
         lib.call("la_mul_mat_mat", 8, C.data.ptr, A.data.ptr, B.data.ptr, rows, n, n, None)
 
@@ -257,54 +282,78 @@ def run_ours(args):
     t1 = time.time()
     clocks = sampler.window(t0, t1)
 
-    # e2e: public API, host buffers, H2D of A and B and D2H of C inside the timed region
-    def e2e_step():
+    engine_used = lib.lib.la_gemm_last_engine()     # 1 = TMA SIMT, 2 = tcgen05 3xTF32
+
+    # e2e: public API on HOST buffers; H2D of A and B and D2H of C inside the timed region.
+    def e2e_step():                                 # one streamed call
+        la.mul_host(hA, hB, rows, n, n, out=hC)
+
+    def three_call_step():                          # the reference user's sequence
         a = la.Matrix.from_vec(hA, rows, n); b = la.Matrix.from_vec(hB, n, n)
         (a * b).to_vec(out=hC)
 
-    for _ in range(2):
-        e2e_step()
-    barrier()
+    def wall(fn, iters):
+        for _ in range(2):
+            fn()
+        barrier()
+        w0 = time.perf_counter()
+        for _ in range(iters):
+            fn()
+        la.synchronize()
+        return (time.perf_counter() - w0) * 1e3    # host-blocking calls: the wall clock is the honest timer
+
     e2e_steps = max(3, min(args.steps, 10))
-    w0 = time.perf_counter()
-    f0, f1 = la.Event(), la.Event()
-    f0.record()
-    for _ in range(e2e_steps):
-        e2e_step()
-    f1.record()
-    e2e_ms = f0.elapsed_ms(f1)
+    e2e_ms = wall(e2e_step, e2e_steps)
+    three_ms = wall(three_call_step, e2e_steps)
     barrier()
-    e2e_wall_ms = (time.perf_counter() - w0) * 1e3
-    e2e_ms = max(e2e_ms, e2e_wall_ms)              # host-blocking copies: the wall clock is the honest one
     sampler.stop()
 
     if dist is not None:
         import torch
-        t = torch.tensor([ms_total, e2e_ms], device="cuda", dtype=torch.float64)
+        t = torch.tensor([ms_total, e2e_ms, three_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, e2e_ms = float(t[0]), float(t[1])
+        ms_total, e2e_ms, three_ms = float(t[0]), float(t[1]), float(t[2])
     ms_step = ms_total / args.steps
     flop = 2.0 * n * n * n                         # whole job: all ranks' row blocks together
     value = flop / ms_step / 1e6
     e2e_value = flop / (e2e_ms / e2e_steps) / 1e6
+    three_value = flop / (three_ms / e2e_steps) / 1e6
 
     if rank == 0:
         simt_peak = sm_count.value * 128 * 2 * sm_max_mhz * 1e6 / 1e12        # TFLOP/s at max clock
         per_gpu_tflops = value / world / 1e3
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        if engine_used == 2:
+            tf32_peak = peaks.get("bf16_tflops", 1590.0) / 2.0
+            tf32_sustained = peaks.get("bf16_tflops_sustained", 1400.0) / 2.0
+            roofline = {"bound": "tensor", "achieved": round(3 * per_gpu_tflops, 1), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
+                        "frac": round(3 * per_gpu_tflops / tf32_peak, 4), "frac_of_sustained_peak": round(3 * per_gpu_tflops / tf32_sustained, 4),
+                        "peak_source": "measured (MEASURED_PEAKS.json): bf16 burst %.1f / 2 (tf32 runs at half the bf16 rate)" % peaks.get("bf16_tflops", 1590.0),
+                        "achieved_note": "tf32 tensor-core work per second = 3 MMAs per useful f32 product; the split pre-pass is inside the time",
+                        "traffic": ncu_traffic("profiles/r1_gemm_3xtf32_8192_ncu_full.txt", "gemm_3xtf32_2cta_kernel")}
+            engine_name = "tcgen05 3xTF32 (cta_group::2 CTA pairs, TMA, chunked FP32 accumulation; same f32 gate as SIMT)"
+            launches = 3
+        else:
+            roofline = {"bound": "fp32-fma (SIMT; MEASURED_PEAKS.json has no FP32 figure)", "achieved": round(per_gpu_tflops, 2),
+                        "peak": round(simt_peak, 2), "unit": "TFLOP/s", "frac": round(per_gpu_tflops / simt_peak, 4),
+                        "peak_source": "nominal: %d SMs x 128 lanes x 2 x %.0f MHz" % (sm_count.value, sm_max_mhz),
+                        "traffic": ncu_traffic("profiles/r1_gemm_f32_8192_ncu_full.txt", "gemm_tma_kernel")}
+            engine_name = "TMA-fed FP32 SIMT (FFMA2), A^T staged per call"
+            launches = 2
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32" if engine_used != 2 else "f32 (products as 3 tf32 tensor-core MMAs on hi/lo splits, FP32 accumulate; passes the f32 tolerance gate)",
+            "data": "synthetic",
             "config": {"workload": "f32 GEMM 8192x8192x8192, C = A x B, A/C row-block sharded over %d GPU(s), B replicated" % world,
                        "M": n, "K": n, "N": n, "rows_per_gpu": rows, "l2": "operands 768 MB >> 126 MB L2 (no flush needed)",
-                       "engine": "TMA-fed FP32 SIMT (FFMA2), A^T staged per call"},
+                       "engine": engine_name, "engine_flag": args.engine},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int((rows * n + n * n) * 4), "d2h_bytes_per_step": int(rows * n * 4),
-                    "steps": e2e_steps, "api": "Matrix.from_vec(pinned) x2 -> A * B -> to_vec(pinned)"},
-            "gpu_launches": 2 * args.steps,
-            "roofline": {"bound": "fp32-fma (SIMT; MEASURED_PEAKS.json has no FP32 figure)", "achieved": round(per_gpu_tflops, 2),
-                         "peak": round(simt_peak, 2), "unit": "TFLOP/s", "frac": round(per_gpu_tflops / simt_peak, 4),
-                         "peak_source": "nominal: %d SMs x 128 lanes x 2 x %.0f MHz" % (sm_count.value, sm_max_mhz), "traffic": None,
-                         "frac_at_observed_clock": (round(per_gpu_tflops / (sm_count.value * 256 * clocks["sm_mhz"] * 1e6 / 1e12), 4) if clocks.get("sm_mhz") else None)},
+                    "steps": e2e_steps, "api": "mul_host(pinned A, pinned B) -> pinned C  (la_mul_mat_mat_host: row-block streaming, copies overlap the multiply)",
+                    "three_call": {"value": round(three_value, 1), "api": "Matrix.from_vec(pinned) x2 -> A * B -> to_vec(pinned)"}},
+            "gpu_launches": launches * args.steps,
+            "roofline": roofline,
         }
         if world == 1:
             if not args.no_extra:
@@ -325,6 +374,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--engine", default="auto", choices=["auto", "simt", "3xtf32"], help="f32 GEMM engine for the timed steps (auto = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

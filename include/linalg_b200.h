@@ -165,10 +165,25 @@ la_status la_mul_vec_mat_noalloc(int dtype, void* C, const void* A, const void* 
  *   C[M x N] = A[M x K] * B[K x N].  C must not alias A or B. */
 la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream);
 
-/* f32 GEMM engine: LA_GEMM_SIMT (default; FP32 FMA pipe, k-ascending per element like the
- * reference) or LA_GEMM_3XTF32 (tcgen05 tensor cores, 3-term TF32 split with FP32 accumulate;
- * falls back to SIMT for shapes it does not cover).  Process-wide. */
-enum { LA_GEMM_SIMT = 0, LA_GEMM_3XTF32 = 1 };
+/* The reference user's whole sequence -- Matrix::from_vec(a) * Matrix::from_vec(b), then to_vec()
+ * (src/matrix.rs:39-46, 221-265, src/vector.rs:53-78) -- as one call on HOST buffers: B is uploaded
+ * once, A and C stream through in row blocks on separate copy streams so uploads, multiplies and
+ * downloads overlap.  Same results as la_mul_mat_mat.  Blocks until C_host is complete; pinned host
+ * buffers (la_host_alloc) give full PCIe rate, pageable ones work. */
+la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N);
+
+/* f32 GEMM engine.
+ *  LA_GEMM_SIMT    FP32 FMA pipe, each element accumulated k-ascending with one fused multiply-add
+ *                  per k: the reference's own order (src/kernels.cl:136-138).
+ *  LA_GEMM_3XTF32  tcgen05 tensor cores: every operand split into two tf32 parts, 3 MMAs per product,
+ *                  FP32 accumulation in 64-wide chunks (meets the same f32 tolerance as the SIMT
+ *                  engine).  Falls back to SIMT for shapes it does not cover
+ *                  (M, N >= 128, K >= 32, all multiples of 4) and whenever an operand holds a NaN, an
+ *                  infinity or a magnitude outside [2^-100, 2^100] (the call reads one flag back, so it
+ *                  blocks for the length of the pre-pass).
+ *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 from 512^3 multiply-adds up, LA_GEMM_SIMT below.
+ * Process-wide; LA_GEMM_MODE=simt|3xtf32|auto in the environment sets the initial value. */
+enum { LA_GEMM_SIMT = 0, LA_GEMM_3XTF32 = 1, LA_GEMM_AUTO = 2 };
 la_status la_set_gemm_mode(int mode);
 la_status la_get_gemm_mode(int* mode);
 

@@ -7,7 +7,7 @@ from . import _lib
 from ._lib import LaError, lib
 from .traits import Parameter, parameter, U8, I8, I8_CHAR, U16, I16, U32, I32, U64, I64, USIZE, ISIZE, F32, F64
 from .vector import Vector, dot, mul_transpose_mat, set_sync, synchronize, pinned, Event
-from .matrix import Matrix, mul_column_row
+from .matrix import Matrix, mul_column_row, mul_host
 
 
 def init(device=0):

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "liblinalg_b200.so")
 
 LA_OK, LA_ERR_ARG, LA_ERR_SHAPE, LA_ERR_DTYPE, LA_ERR_OOM, LA_ERR_CUDA, LA_ERR_UNSUPPORTED = range(7)
 ADD, SUB, MUL, DIV = 0, 1, 2, 3
-GEMM_SIMT, GEMM_3XTF32 = 0, 1
+GEMM_SIMT, GEMM_3XTF32, GEMM_AUTO = 0, 1, 2
 
 
 class LaError(RuntimeError):
@@ -70,6 +70,7 @@ SIGNATURES = {
     "la_mul_vec_transpose_mat": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_vec_mat_noalloc": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_mat_mat": [_I, _V, _V, _V, _Z, _Z, _Z, _V],
+    "la_mul_mat_mat_host": [_I, _V, _V, _V, _Z, _Z, _Z],
     "la_set_gemm_mode": [_I],
     "la_get_gemm_mode": [_PI],
     "la_transpose": [_I, _V, _V, _Z, _Z, _V],

@@ -40,6 +40,9 @@ la_status la_ensure_init(LaDeviceInfo** info);   // lazily binds the current dev
 // (tickets / flags).
 enum { LA_SCRATCH_ZEROED = 256 };
 la_status la_scratch(cudaStream_t stream, size_t bytes, void** ptr);
+// One zero-copy flag word per (device, stream): kernels store into *dev_ptr, the host reads
+// *host_ptr after waiting for them (no device-to-host copy involved).
+la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsigned** dev_ptr);
 
 // ---------------------------------------------------------------- dtype traits
 template <typename T> struct Arith {                       // wrap-safe arithmetic

@@ -392,10 +392,12 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
     }
 }
 
-// LA_GEMM_MODE=3xtf32 in the environment selects the tensor-core engine at load time.
+// LA_GEMM_MODE=simt|3xtf32|auto in the environment selects the f32 engine at load time.
 int initial_gemm_mode() {
     const char* e = getenv("LA_GEMM_MODE");
-    return (e && (e[0] == '3' || e[0] == 't' || e[0] == 'T')) ? LA_GEMM_3XTF32 : LA_GEMM_SIMT;
+    if (e && (e[0] == 's' || e[0] == 'S')) return LA_GEMM_SIMT;
+    if (e && (e[0] == '3' || e[0] == 't' || e[0] == 'T')) return LA_GEMM_3XTF32;
+    return LA_GEMM_AUTO;
 }
 int g_gemm_mode = initial_gemm_mode();
 int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32 (la_gemm_last_engine: test hook)
@@ -405,7 +407,7 @@ int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32 (la_gemm_last_e
 la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled);   // gemm_tc.cu
 
 extern "C" la_status la_set_gemm_mode(int mode) {
-    if (mode != LA_GEMM_SIMT && mode != LA_GEMM_3XTF32) return la_fail(LA_ERR_ARG, "unknown GEMM mode %d", mode);
+    if (mode != LA_GEMM_SIMT && mode != LA_GEMM_3XTF32 && mode != LA_GEMM_AUTO) return la_fail(LA_ERR_ARG, "unknown GEMM mode %d", mode);
     g_gemm_mode = mode;
     return LA_OK;
 }
@@ -419,7 +421,16 @@ extern "C" la_status la_get_gemm_mode(int* mode) {
 extern "C" la_status la_gemm_set_variant(int v) { g_gemm_variant = v; return LA_OK; }
 extern "C" int la_gemm_last_engine(void) { return g_last_engine; }
 
+la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode);
+
 extern "C" la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream) {
+    return la_mul_mat_mat_impl(dtype, C, A, B, M, K, N, stream, g_gemm_mode);
+}
+
+int la_gemm_current_mode() { return g_gemm_mode; }
+
+// `mode`: LA_GEMM_SIMT / LA_GEMM_3XTF32 / LA_GEMM_AUTO for this call (gemm_host.cu forces SIMT per block).
+la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: unknown dtype %d", dtype);
     if (M == 0 || N == 0) return LA_OK;
     if (!C || !A || !B) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: NULL operand");
@@ -431,7 +442,8 @@ extern "C" la_status la_mul_mat_mat(int dtype, void* C, const void* A, const voi
     const bool four_byte = (dtype == LA_F32 || dtype == LA_U32 || dtype == LA_I32);
     const bool tma_ok = four_byte && g_gemm_variant >= 0 && M % 4 == 0 && N % 4 == 0 && la_aligned16(A) && la_aligned16(B) && la_aligned16(C) &&
                         M >= 64 && N >= 64 && K >= 16 && M < (1u << 31) && N < (1u << 31) && K < (1u << 31);
-    if (dtype == LA_F32 && g_gemm_mode == LA_GEMM_3XTF32) {
+    // AUTO: the tensor engine for problems big enough to amortise its pre-pass (>= 512^3 multiply-adds)
+    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && (double)M * (double)N * (double)K >= 134217728.0))) {
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 2; return LA_OK; }

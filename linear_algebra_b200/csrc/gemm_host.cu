@@ -1,0 +1,151 @@
+// csrc/gemm_host.cu -- Matrix x Matrix on HOST buffers, streamed.
+//
+// The reference's user writes  Matrix::from_vec(a) * Matrix::from_vec(b)  and then to_vec():
+// upload, upload, multiply, download, one after the other (src/matrix.rs:39-46, 221-265,
+// src/vector.rs:53-78).  la_mul_mat_mat_host is that whole sequence as ONE call that overlaps its
+// parts: B goes up once (and is pre-processed once for the tensor engine); A and C move in row
+// blocks on their own copy streams, so block i+1 uploads and block i-1 downloads while block i
+// multiplies (PCIe is full duplex).  Results are those of la_mul_mat_mat on the same operands.
+#include "common.cuh"
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+
+la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode);
+int la_gemm_current_mode();
+la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size_t K, unsigned* flag, cudaStream_t st);
+la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st);
+la_status la_tc_run(float* C, const float* a_hi, const float* a_lo, const float* bt_hi, const float* bt_lo, size_t M, size_t K, size_t N, cudaStream_t st);
+bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_t K, size_t N);
+
+namespace {
+
+struct HostGemmStreams {
+    cudaStream_t in = nullptr, cmp = nullptr, out = nullptr;
+    cudaEvent_t b_up = nullptr, in_done[2] = {nullptr, nullptr}, cmp_done[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
+};
+std::mutex g_hs_mu;
+std::map<int, HostGemmStreams*> g_hs;
+
+la_status host_streams(HostGemmStreams** out) {
+    int dev = -1;
+    LA_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_hs_mu);
+    auto it = g_hs.find(dev);
+    if (it != g_hs.end()) { *out = it->second; return LA_OK; }
+    HostGemmStreams* s = new HostGemmStreams();
+    LA_CUDA(cudaStreamCreateWithFlags(&s->in, cudaStreamNonBlocking));
+    LA_CUDA(cudaStreamCreateWithFlags(&s->cmp, cudaStreamNonBlocking));
+    LA_CUDA(cudaStreamCreateWithFlags(&s->out, cudaStreamNonBlocking));
+    LA_CUDA(cudaEventCreateWithFlags(&s->b_up, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) {
+        LA_CUDA(cudaEventCreateWithFlags(&s->in_done[i], cudaEventDisableTiming));
+        LA_CUDA(cudaEventCreateWithFlags(&s->cmp_done[i], cudaEventDisableTiming));
+        LA_CUDA(cudaEventCreateWithFlags(&s->out_done[i], cudaEventDisableTiming));
+    }
+    g_hs[dev] = s;
+    *out = s;
+    return LA_OK;
+}
+
+struct DevBuf {       // stream-ordered pool allocation, freed on scope exit
+    void* p = nullptr; cudaStream_t st;
+    explicit DevBuf(cudaStream_t s) : st(s) {}
+    la_status alloc(size_t bytes) { LA_CUDA(cudaMallocAsync(&p, bytes ? bytes : 16, st)); return LA_OK; }
+    ~DevBuf() { if (p) cudaFreeAsync(p, st); }
+};
+
+}  // namespace
+
+static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N, bool allow_tensor, bool* redo) {
+    *redo = false;
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    HostGemmStreams* hs; LA_TRY(host_streams(&hs));
+    const size_t es = la_dtype_size(dtype);
+    const int mode = la_gemm_current_mode();
+    static const bool dbg = getenv("LA_DEBUG_HOSTGEMM") != nullptr;
+    auto t0 = std::chrono::steady_clock::now();
+    auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+
+    // row block: about a sixteenth of M (short pipeline tail), a multiple of 128 rows, 256 .. 2048
+    size_t rb = ((M / 16 + 127) / 128) * 128;
+    if (rb < 256) rb = 256;
+    if (rb > 2048) rb = 2048;
+    if (rb > M) rb = M;
+    const size_t nblocks = (M + rb - 1) / rb;
+
+    DevBuf B(hs->cmp), Abuf0(hs->cmp), Abuf1(hs->cmp), Cbuf0(hs->cmp), Cbuf1(hs->cmp), bt_hi(hs->cmp), bt_lo(hs->cmp), a_hi0(hs->cmp), a_lo0(hs->cmp), a_hi1(hs->cmp), a_lo1(hs->cmp);
+    LA_TRY(B.alloc(K * N * es));
+    LA_TRY(Abuf0.alloc(rb * K * es)); LA_TRY(Abuf1.alloc(rb * K * es));
+    LA_TRY(Cbuf0.alloc(rb * N * es)); LA_TRY(Cbuf1.alloc(rb * N * es));
+    void* Ab[2] = {Abuf0.p, Abuf1.p}; void* Cb[2] = {Cbuf0.p, Cbuf1.p};
+
+    // tensor engine for f32 when the mode and the shapes allow: B is split once, up front
+    bool tensor = allow_tensor && dtype == LA_F32 && mode != LA_GEMM_SIMT && K > 0 && la_tc_shape_ok(Ab[0], B.p, Cb[0], rb, K, N) &&
+                  (mode == LA_GEMM_3XTF32 || (double)M * (double)N * (double)K >= 134217728.0);
+    float* ah[2] = {nullptr, nullptr}; float* al[2] = {nullptr, nullptr};
+    volatile unsigned* flag_host = nullptr; unsigned* flag = nullptr;
+    if (tensor) {
+        LA_TRY(la_host_flag(hs->cmp, &flag_host, &flag));
+        *flag_host = 0u;
+        LA_TRY(bt_hi.alloc(K * N * 4)); LA_TRY(bt_lo.alloc(K * N * 4));
+        LA_TRY(a_hi0.alloc(rb * K * 4)); LA_TRY(a_lo0.alloc(rb * K * 4)); LA_TRY(a_hi1.alloc(rb * K * 4)); LA_TRY(a_lo1.alloc(rb * K * 4));
+        ah[0] = (float*)a_hi0.p; al[0] = (float*)a_lo0.p; ah[1] = (float*)a_hi1.p; al[1] = (float*)a_lo1.p;
+    }
+    // the copy streams may touch the buffers only after the (stream-ordered) allocations exist
+    LA_CUDA(cudaEventRecord(hs->b_up, hs->cmp));
+    LA_CUDA(cudaStreamWaitEvent(hs->in, hs->b_up, 0));
+    LA_CUDA(cudaStreamWaitEvent(hs->out, hs->b_up, 0));
+
+    LA_CUDA(cudaMemcpyAsync(B.p, B_host, K * N * es, cudaMemcpyHostToDevice, hs->in));
+    LA_CUDA(cudaEventRecord(hs->b_up, hs->in));
+    LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->b_up, 0));
+    if (tensor) LA_TRY(la_tc_split_bt((float*)bt_hi.p, (float*)bt_lo.p, (const float*)B.p, K, N, flag, hs->cmp));
+    if (dbg) fprintf(stderr, "[hostgemm] setup enqueued at %.3f ms (tensor=%d rb=%zu nblocks=%zu)\n", ms_since(), (int)tensor, rb, nblocks);
+
+    for (size_t i = 0; i < nblocks; ++i) {
+        const int b = (int)(i & 1);
+        const size_t r0 = i * rb, rows = (r0 + rb <= M) ? rb : M - r0;
+        // upload block i once the multiply that last read this A buffer is done
+        if (i >= 2) LA_CUDA(cudaStreamWaitEvent(hs->in, hs->cmp_done[b], 0));
+        LA_CUDA(cudaMemcpyAsync(Ab[b], (const char*)A_host + r0 * K * es, rows * K * es, cudaMemcpyHostToDevice, hs->in));
+        LA_CUDA(cudaEventRecord(hs->in_done[b], hs->in));
+        // multiply once the block is up and the download that last read this C buffer is done
+        LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->in_done[b], 0));
+        if (i >= 2) LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->out_done[b], 0));
+        // The range check of the split is read back once, after everything is queued: no host
+        // wait inside the pipeline.  (If it trips, the whole product is redone in plain f32.)
+        if (tensor && rows >= 128 && rows % 4 == 0) {
+            LA_TRY(la_tc_split_a(ah[b], al[b], (const float*)Ab[b], rows, K, flag, hs->cmp));
+            LA_TRY(la_tc_run((float*)Cb[b], ah[b], al[b], (const float*)bt_hi.p, (const float*)bt_lo.p, rows, K, N, hs->cmp));
+        } else {
+            // (a ragged tail block of a tensor-engine product goes to the SIMT engine: la_gemm_3xtf32 would
+            //  reset the range flag this pass is still collecting)
+            LA_TRY(la_mul_mat_mat_impl(dtype, Cb[b], Ab[b], B.p, rows, K, N, hs->cmp, (tensor || !allow_tensor) ? LA_GEMM_SIMT : mode));
+        }
+        LA_CUDA(cudaEventRecord(hs->cmp_done[b], hs->cmp));
+        // download
+        LA_CUDA(cudaStreamWaitEvent(hs->out, hs->cmp_done[b], 0));
+        LA_CUDA(cudaMemcpyAsync((char*)C_host + r0 * N * es, Cb[b], rows * N * es, cudaMemcpyDeviceToHost, hs->out));
+        LA_CUDA(cudaEventRecord(hs->out_done[b], hs->out));
+    }
+    if (dbg) fprintf(stderr, "[hostgemm] all enqueued at %.3f ms\n", ms_since());
+    LA_CUDA(cudaStreamSynchronize(hs->out));
+    if (dbg) fprintf(stderr, "[hostgemm] out drained at %.3f ms\n", ms_since());
+    LA_CUDA(cudaStreamSynchronize(hs->in));
+    LA_CUDA(cudaStreamSynchronize(hs->cmp));
+    if (tensor && *flag_host) *redo = true;      // an operand the tf32 split cannot represent (inf, NaN, extreme exponent)
+    return LA_OK;
+}
+
+extern "C" la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N) {
+    if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_mul_mat_mat_host: unknown dtype %d", dtype);
+    if (M == 0 || N == 0) return LA_OK;
+    if (!C_host || !A_host || !B_host) return la_fail(LA_ERR_ARG, "la_mul_mat_mat_host: NULL operand");
+    bool redo = false;
+    LA_TRY(host_gemm_pass(dtype, C_host, A_host, B_host, M, K, N, true, &redo));
+    if (redo) LA_TRY(host_gemm_pass(dtype, C_host, A_host, B_host, M, K, N, false, &redo));
+    return LA_OK;
+}

@@ -13,16 +13,17 @@
 //   5/3 gemm_3xtf32_chunked_kernel  one CTA per 128x256 tile (with / without B multicast), chunked
 //   1/2 gemm_3xtf32_kernel          single accumulation chain (tuning reference; drifts, see below)
 // Common structure:
-//   pre-pass   split_tf32_kernel   A  -> A_hi, A_lo              (scratch)
-//              transpose + split   B  -> Bt_hi, Bt_lo  (N x K)   (scratch) so both operands are K-major
+//   pre-pass   split_tf32_kernel       A -> A_hi, A_lo             (scratch)
+//              split_transpose_kernel  B -> Bt_hi, Bt_lo (N x K)   (scratch) so both operands are K-major
 //   TMA warp   cp.async.bulk.tensor.2d (128-byte swizzle) of the four slabs of a 32-wide k-block
 //              into a ring guarded by full/empty mbarriers
 //   MMA warp   owns tensor memory; one elected lane issues 3 tcgen05.mma per 8-wide k-step
 //              (hi*lo, lo*hi, hi*hi) and tcgen05.commit's the stage back to the producer
 //   epilogue   tcgen05.ld of the FP32 accumulator (lane = row, column = column), FP32 adds in
 //              registers, 16-byte streaming stores to C
-// Non-finite inputs: inf * (lo == 0) is NaN, so infinities do not propagate as in plain f32
-// arithmetic; that is one reason the mode is opt-in.
+// Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-pass
+// detects anything outside [2^-100, 2^100] (or NaN) and the call then falls back to the SIMT engine,
+// so the tensor engine never changes the result class of a product.
 // Roofline: tensor pipe (tf32), 3 MMAs per useful product.
 #include "common.cuh"
 #include <cuda.h>
@@ -593,28 +594,68 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
     }
 }
 
-// x -> hi = tf32(x) (round to nearest), lo = tf32(x - hi); 16-byte packets, streaming.
+// ------------------------------------------------------------------ pre-pass
+// x -> hi = tf32(x) (round to nearest), lo = tf32(x - hi).  The split is only faithful for finite
+// values away from the ends of the exponent range (an infinity would turn into NaN through
+// inf * 0, a tiny value would lose its lo part to underflow), so the pre-pass also raises *flag
+// when it sees anything else and the caller then leaves the problem to the SIMT engine.
+__device__ __forceinline__ void split_one(float x, float& hi, float& lo, bool& bad) {
+    uint32_t hb, lb;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(x));
+    hi = __uint_as_float(hb);
+    const float d = x - hi;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(d));
+    lo = __uint_as_float(lb);
+    const float ax = fabsf(x);
+    bad |= !(ax <= 1.2676506e30f) || (ax < 7.8886091e-31f && ax != 0.0f);      // outside [2^-100, 2^100] (or NaN)
+}
+
 __global__ void __launch_bounds__(256)
-split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4) {
+split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4, unsigned* flag) {
     const size_t stride = (size_t)gridDim.x * 256;
+    bool bad = false;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
         const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
         float4 h, l;
-        const float in[4] = {v.x, v.y, v.z, v.w};
-        float ho[4], lo_[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            uint32_t hb, lb;
-            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(in[e]));
-            ho[e] = __uint_as_float(hb);
-            const float d = in[e] - ho[e];
-            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(d));
-            lo_[e] = __uint_as_float(lb);
-        }
-        h = make_float4(ho[0], ho[1], ho[2], ho[3]); l = make_float4(lo_[0], lo_[1], lo_[2], lo_[3]);
+        split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
         __stcs(reinterpret_cast<float4*>(hi) + i, h);
         __stcs(reinterpret_cast<float4*>(lo) + i, l);
     }
+    if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;     // flag may live in mapped host memory: plain store
+}
+
+// B (K x N) -> Bt_hi, Bt_lo (N x K) in one pass: 64 x 64 tile through shared memory, 16-byte
+// loads along B's rows, 16-byte stores along Bt's rows.  K % 4 == 0 and N % 4 == 0.
+__global__ void __launch_bounds__(256)
+split_transpose_kernel(float* __restrict__ bt_hi, float* __restrict__ bt_lo, const float* __restrict__ B, size_t K, size_t N,
+                       unsigned tiles_n, unsigned* flag) {
+    __shared__ float tile[64][65];
+    const size_t k0 = (size_t)(blockIdx.x / tiles_n) * 64, n0 = (size_t)(blockIdx.x % tiles_n) * 64;
+    float4 in[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
+        in[j] = (k0 + r < K && n0 + q * 4 < N) ? __ldcs(reinterpret_cast<const float4*>(B + (k0 + r) * N + n0 + q * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
+        tile[r][q * 4 + 0] = in[j].x; tile[r][q * 4 + 1] = in[j].y; tile[r][q * 4 + 2] = in[j].z; tile[r][q * 4 + 3] = in[j].w;
+    }
+    __syncthreads();
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int idx = threadIdx.x + j * 256, cc = idx / 16, q = idx % 16;      // Bt row n0+cc, columns k0 + q*4 ..
+        float4 h, l;
+        split_one(tile[q * 4 + 0][cc], h.x, l.x, bad); split_one(tile[q * 4 + 1][cc], h.y, l.y, bad);
+        split_one(tile[q * 4 + 2][cc], h.z, l.z, bad); split_one(tile[q * 4 + 3][cc], h.w, l.w, bad);
+        if (n0 + cc < N && k0 + q * 4 < K) {
+            __stcs(reinterpret_cast<float4*>(bt_hi + (n0 + cc) * K + k0 + q * 4), h);
+            __stcs(reinterpret_cast<float4*>(bt_lo + (n0 + cc) * K + k0 + q * 4), l);
+        }
+    }
+    if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;     // flag may live in mapped host memory: plain store
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -707,34 +748,53 @@ int g_tc_variant = 0;
 
 extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA_OK; }     // tuning hook
 
-la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled) {
-    *handled = false;
-    if (M < 128 || N < 128 || K < 32 || K % 4 != 0 || N % 4 != 0 || M % 4 != 0 || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C) ||
-        M >= (1u << 31) || N >= (1u << 31) || K >= (1u << 31))
-        return LA_OK;                              // the SIMT engine takes it
+// Pieces shared by la_gemm_3xtf32 and the host-streaming GEMM (gemm_host.cu).
+la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size_t K, unsigned* flag, cudaStream_t st) {
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
-    const size_t a_elems = M * K, b_elems = K * N;
-    void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 3 * b_elems) * sizeof(float), &scratch));
-    float* a_hi = (float*)((char*)scratch + LA_SCRATCH_ZEROED);
-    float* a_lo = a_hi + a_elems;
-    float* bt = a_lo + a_elems;                    // B^T (N x K)
-    float* b_hi = bt + b_elems;
-    float* b_lo = b_hi + b_elems;
-    const unsigned blocks = (unsigned)info->sm_count * 8;
-    split_tf32_kernel<<<blocks, 256, 0, st>>>(a_hi, a_lo, A, a_elems / 4);
+    split_tf32_kernel<<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag);
     LA_LAUNCH_CHECK();
-    LA_TRY(la_transpose_raw32((uint32_t*)bt, (const uint32_t*)B, K, N, st));
-    split_tf32_kernel<<<blocks, 256, 0, st>>>(b_hi, b_lo, bt, b_elems / 4);
+    return LA_OK;
+}
+la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st) {
+    const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
+    if (tk * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "3xTF32 pre-pass: B is too large");
+    split_transpose_kernel<<<(unsigned)(tk * tn), 256, 0, st>>>(bt_hi, bt_lo, B, K, N, (unsigned)tn, flag);
     LA_LAUNCH_CHECK();
-    la_status s;
+    return LA_OK;
+}
+la_status la_tc_run(float* C, const float* a_hi, const float* a_lo, const float* bt_hi, const float* bt_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
     switch (g_tc_variant) {
     default:
-    case 0: s = tc_launch_2cta(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;         // CTA pairs, tcgen05 cta_group::2 (default)
-    case 5: s = tc_launch_chunked<2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // one CTA per tile, B multicast over CTA pairs
-    case 3: s = tc_launch_chunked<1>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;   // same, no clusters
-    case 1: s = tc_launch<256, 2>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;      // single chain (tuning reference; less accurate)
-    case 2: s = tc_launch<128, 3>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st); break;
+    case 0: return tc_launch_2cta(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);         // CTA pairs, tcgen05 cta_group::2 (default)
+    case 5: return tc_launch_chunked<2>(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);   // one CTA per tile, B multicast over CTA pairs
+    case 3: return tc_launch_chunked<1>(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);   // same, no clusters
+    case 1: return tc_launch<256, 2>(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);      // single chain (tuning reference; less accurate)
+    case 2: return tc_launch<128, 3>(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);
     }
-    if (s == LA_OK) *handled = true;
-    return s;
+}
+bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_t K, size_t N) {
+    return !(M < 128 || N < 128 || K < 32 || K % 4 != 0 || N % 4 != 0 || M % 4 != 0 || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C) ||
+             M >= (1u << 31) || N >= (1u << 31) || K >= (1u << 31));
+}
+
+la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled) {
+    *handled = false;
+    if (!la_tc_shape_ok(A, B, C, M, K, N)) return LA_OK;      // the SIMT engine takes it
+    const size_t a_elems = M * K, b_elems = K * N;
+    void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 2 * b_elems) * sizeof(float), &scratch));
+    volatile unsigned* flag_host; unsigned* flag;               // zero-copy flag word of this stream
+    LA_TRY(la_host_flag(st, &flag_host, &flag));
+    float* a_hi = (float*)((char*)scratch + LA_SCRATCH_ZEROED);
+    float* a_lo = a_hi + a_elems;
+    float* b_hi = a_lo + a_elems;                               // B^T (N x K), split
+    float* b_lo = b_hi + b_elems;
+    *flag_host = 0u;                                            // no kernel of this stream that writes it is in flight (each call waits below)
+    LA_TRY(la_tc_split_a(a_hi, a_lo, A, M, K, flag, st));
+    LA_TRY(la_tc_split_bt(b_hi, b_lo, B, K, N, flag, st));
+    // Were all operands inside the range the split is faithful for?  (wait for the pre-pass, read the word)
+    LA_CUDA(cudaStreamSynchronize(st));
+    if (*flag_host) return LA_OK;                               // inf / NaN / extreme exponents: plain f32 arithmetic instead
+    LA_TRY(la_tc_run(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st));
+    *handled = true;
+    return LA_OK;
 }

@@ -44,6 +44,7 @@ namespace {
 struct DeviceState {
     LaDeviceInfo info;
     std::map<cudaStream_t, std::pair<void*, size_t>> scratch;   // per stream: block, capacity
+    std::map<cudaStream_t, unsigned*> host_flags;                // per stream: one mapped, page-locked word
 };
 std::mutex g_mu;
 std::map<int, DeviceState*> g_devices;
@@ -102,6 +103,26 @@ la_status la_scratch(cudaStream_t stream, size_t bytes, void** ptr) {
         slot = {p, cap};
     }
     *ptr = slot.first;
+    return LA_OK;
+}
+
+// A 4-byte flag in page-locked host memory that kernels on `stream` can set directly (zero-copy),
+// so the host can read it after an event wait without queueing a device-to-host copy behind
+// whatever bulk transfer a copy engine is busy with.
+la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsigned** dev_ptr) {
+    DeviceState* st = nullptr;
+    LA_TRY(device_state(&st));
+    std::lock_guard<std::mutex> lk(g_mu);
+    unsigned*& slot = st->host_flags[stream];
+    if (!slot) {
+        void* p = nullptr;
+        LA_CUDA(cudaHostAlloc(&p, 64, cudaHostAllocMapped));
+        *(volatile unsigned*)p = 0u;
+        slot = (unsigned*)p;
+    }
+    void* d = nullptr;
+    LA_CUDA(cudaHostGetDevicePointer(&d, slot, 0));
+    *host_ptr = slot; *dev_ptr = (unsigned*)d;
     return LA_OK;
 }
 

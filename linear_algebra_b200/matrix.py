@@ -120,3 +120,21 @@ def _mul_helper(a, b, a_row_count, a_col_count, b_col_count):     # matrix.rs:24
 def mul_column_row(column, row):                  # matrix.rs:236-238
     """Outer product: column (as an n x 1 matrix) times row (as a 1 x m matrix)."""
     return _mul_helper(column, row, column.len(), 1, row.len())
+
+
+def mul_host(a_host, b_host, a_row_count, a_col_count, b_col_count, out=None):
+    """C = A x B on HOST arrays in one streamed call (la_mul_mat_mat_host): what
+    `Matrix.from_vec(a) * Matrix.from_vec(b)` followed by `to_vec()` computes, with the uploads,
+    the multiply and the download overlapped.  Pass page-locked arrays (linear_algebra_b200.pinned)
+    for full PCIe rate.  Returns the host array of a_row_count * b_col_count elements."""
+    import numpy as np
+    from .traits import parameter
+    a = np.ascontiguousarray(a_host).reshape(-1); b = np.ascontiguousarray(b_host, dtype=a.dtype).reshape(-1)
+    assert a.size == a_row_count * a_col_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (a.size, a_row_count * a_col_count)
+    assert b.size == a_col_count * b_col_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (b.size, a_col_count * b_col_count)
+    dt = parameter(a.dtype)
+    if out is None:
+        out = np.empty(a_row_count * b_col_count, dtype=a.dtype)
+    assert out.size == a_row_count * b_col_count and out.dtype == a.dtype and out.flags.c_contiguous
+    call("la_mul_mat_mat_host", dt.code, out.ctypes.data, a.ctypes.data, b.ctypes.data, a_row_count, a_col_count, b_col_count)
+    return out

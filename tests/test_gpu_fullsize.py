@@ -69,11 +69,17 @@ def test_integer_8192_square(la):              # configs[4]: i32 elementwise + G
         assert int(np.uint32(c[r * n + col])) == expect
 
 
-def test_f32_gemm_8192(la):                    # the headline config
+@pytest.mark.parametrize("mode", ["simt", "3xtf32"])
+def test_f32_gemm_8192(la, mode):              # the headline config, on both f32 engines
     n = 8192
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_SIMT if mode == "simt" else la._lib.GEMM_3XTF32)
     rng = np.random.default_rng(102)
     a = rng.random(n * n, dtype=np.float32) * np.float32(2) - np.float32(1); b = rng.random(n * n, dtype=np.float32) * np.float32(2) - np.float32(1)
-    C = (la.Matrix.from_vec(a, n, n) * la.Matrix.from_vec(b, n, n)).to_vec()
+    try:
+        C = (la.Matrix.from_vec(a, n, n) * la.Matrix.from_vec(b, n, n)).to_vec()
+        assert la._lib.lib.la_gemm_last_engine() == (1 if mode == "simt" else 2)
+    finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
     A2 = a.reshape(n, n).astype(np.float64); B2 = b.reshape(n, n)
     worst = 0.0
     for r, col in rng.integers(0, n, (256, 2)):

@@ -238,6 +238,7 @@ def test_matmat_every_engine_variant(la, variant):
     edge tiles and a K tail."""
     P = oracle.port(); lib = la._lib.lib
     lib.la_gemm_set_variant(variant)
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_SIMT)
     try:
         for M, K, N in ((512, 256, 384), (388, 1001, 260)):
             check_f32_gemm(la, gen.values("f32", M * K, 25), gen.values("f32", K * N, 26), M, K, N, (variant, M, K, N))
@@ -246,6 +247,7 @@ def test_matmat_every_engine_variant(la, variant):
             assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (variant, M, K, N)
     finally:
         lib.la_gemm_set_variant(0)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
 @pytest.mark.parametrize("tc_variant", [0, 3, 5])
@@ -263,8 +265,44 @@ def test_matmat_3xtf32_engine_meets_the_f32_bar(la, tc_variant):
         check_f32_gemm(la, gen.values("f32", 33 * 17, 43), gen.values("f32", 17 * 29, 44), 33, 17, 29, "fallthrough")
         assert lib.la_gemm_last_engine() == 0
     finally:
-        la._lib.call("la_set_gemm_mode", la._lib.GEMM_SIMT)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
         lib.la_gemm_tc_set_variant(0)
+
+
+def test_matmat_3xtf32_leaves_non_finite_and_extreme_operands_to_simt(la):
+    """inf / NaN / magnitudes outside [2^-100, 2^100] cannot be split faithfully: the pre-pass
+    spots them and the SIMT engine computes the product, so infinities propagate as in f32."""
+    lib = la._lib.lib
+    M = K = N = 512
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    try:
+        for poison, where in ((np.inf, "a"), (np.nan, "b"), (1e-35, "a"), (3e33, "b")):
+            a = gen.values("f32", M * K, 45).copy(); b = gen.values("f32", K * N, 46).copy()
+            (a if where == "a" else b)[777] = poison
+            C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+            assert lib.la_gemm_last_engine() == 1, (poison, "tensor engine should have declined")
+            with np.errstate(invalid="ignore", over="ignore"):
+                ref = (a.reshape(M, K).astype(np.float64) @ b.reshape(K, N).astype(np.float64)).reshape(-1)
+            assert np.array_equal(np.isnan(C), np.isnan(ref)) and np.array_equal(np.isinf(C), np.isinf(ref)), poison
+        a = gen.values("f32", M * K, 47); b = gen.values("f32", K * N, 48)      # clean data: tensor engine again
+        la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)
+        assert lib.la_gemm_last_engine() == 2
+    finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
+def test_matmat_auto_mode_picks_the_engine_by_size(la):
+    lib = la._lib.lib
+    mode = __import__("ctypes").c_int(-1)
+    la._lib.call("la_get_gemm_mode", __import__("ctypes").byref(mode))
+    assert mode.value == la._lib.GEMM_AUTO
+    check_f32_gemm(la, gen.values("f32", 256 * 256, 49), gen.values("f32", 256 * 256, 50), 256, 256, 256, "auto small")
+    assert lib.la_gemm_last_engine() == 1          # below 512^3: SIMT
+    check_f32_gemm(la, gen.values("f32", 512 * 1024, 51), gen.values("f32", 1024 * 512, 52), 512, 1024, 512, "auto large")
+    assert lib.la_gemm_last_engine() == 2          # tensor cores
+    a = gen.values("i32", 512 * 1024, 53); b = gen.values("i32", 1024 * 512, 54)
+    C = la.Matrix.from_vec(a, 512, 1024) * la.Matrix.from_vec(b, 1024, 512)
+    assert same(C.to_vec(), oracle.port().mul_mat_mat(a, b, 512, 1024, 512)) and lib.la_gemm_last_engine() == 1   # integers never use it
 
 
 def test_matmat_f64(la):
@@ -311,3 +349,36 @@ def test_synth_matches_host_mirror(la, name):
     assert same(got, synth.values(dt(la, name), 0x5EED0001, 0, n)), name
     if np.dtype(got.dtype).kind == "f":
         assert got.min() >= -1.0 and got.max() < 1.0 and abs(float(got.mean())) < 0.02
+
+
+# ------------------------------------------------------------------ streamed host-buffer GEMM
+@pytest.mark.parametrize("name,shape", [("f32", (1000, 512, 768)), ("f32", (2304, 1024, 640)), ("i32", (700, 300, 260)), ("u8", (300, 200, 100)), ("f32", (5, 7, 3))])
+def test_mul_host_equals_the_three_call_sequence(la, name, shape):
+    M, K, N = shape
+    a = gen.values(name, M * K, 60); b = gen.values(name, K * N, 61)
+    expect = (la.Matrix.from_vec(a, M, K, dt(la, name)) * la.Matrix.from_vec(b, K, N, dt(la, name))).to_vec()
+    ha = la.pinned(M * K, dt(la, name)); hb = la.pinned(K * N, dt(la, name)); hc = la.pinned(M * N, dt(la, name))
+    ha[:] = a; hb[:] = b
+    for _ in range(2):                         # twice: stream / event state must be reusable
+        hc[:] = 0
+        got = la.mul_host(ha, hb, M, K, N, out=hc)
+        if np.dtype(NP[name]).kind == "f":
+            P = oracle.port()
+            truth, absab = P.f32_mul_mat_mat_truth(a, b, M, K, N)
+            check_float_dot_like(got, P.mul_mat_mat(a, b, M, K, N), truth, absab, ("mul_host", shape))
+            assert np.linalg.norm(got - expect) <= NORMWISE_TOL * np.linalg.norm(expect)
+        else:
+            assert same(got, expect), (name, shape)
+    assert same(la.mul_host(a, b, M, K, N), got) or np.dtype(NP[name]).kind == "f"      # pageable host memory works too
+
+
+def test_mul_host_redoes_the_product_in_f32_for_non_finite_operands(la):
+    M = K = N = 1024
+    a = gen.values("f32", M * K, 62).copy(); b = gen.values("f32", K * N, 63).copy()
+    a[5 * K + 9] = np.inf
+    got = la.mul_host(a, b, M, K, N)
+    with np.errstate(invalid="ignore", over="ignore"):
+        ref = (a.reshape(M, K).astype(np.float64) @ b.reshape(K, N).astype(np.float64)).reshape(-1)
+    assert np.array_equal(np.isinf(got), np.isinf(ref)) and not np.isnan(got).any()
+    finite = np.isfinite(ref)
+    assert np.linalg.norm(got[finite] - ref[finite]) <= NORMWISE_TOL * np.linalg.norm(ref[finite])

@@ -23,6 +23,7 @@ def main():
         A = la.Matrix.from_vec(a, n, n); B = la.Matrix.from_vec(b, n, n); C = la.Matrix.uninitialized(n, n, "f32")
         rows = rng.integers(0, n, 16); cols = rng.integers(0, n, 16)
         truth = np.array([a[r * n:(r + 1) * n].astype(np.float64) @ b[c::n].astype(np.float64) for r, c in zip(rows, cols)])
+        lib.call("la_set_gemm_mode", 0)      # SIMT engine variants first
         for dtype_code, label in ((8, "f32"), (5, "i32")):
             for v, desc in VARIANTS.items():
                 if label == "i32" and "ffma2" in desc and v not in (0, 2, 4):
@@ -71,7 +72,7 @@ def main():
                 print("n=%d f32 tc variant %d (%s): %.3f ms  %.2f TFLOP/s  maxerr %.2e  engine %d" % (n, tv, desc, ms, 2.0 * n ** 3 / ms / 1e9, float(np.max(np.abs(got - truth))), lib.lib.la_gemm_last_engine()), flush=True)
             except Exception as e:  # noqa: BLE001
                 print("n=%d tc variant %d FAILED: %s" % (n, tv, e), flush=True)
-        lib.call("la_set_gemm_mode", 0)
+        lib.call("la_set_gemm_mode", 2)
         lib.lib.la_gemm_tc_set_variant(0)
 
 

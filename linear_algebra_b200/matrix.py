@@ -101,6 +101,32 @@ class Matrix:
         _v._done()
         return res
 
+    # ---- persistence (matrix.rs:76-130): u64 element size, u64 rows, u64 cols, raw row-major data
+    def write_to_file(self, f):
+        import numpy as np
+        f.write(np.array([self.dtype.size, self.row_count, self.col_count], dtype=np.uint64).tobytes())
+        f.write(self.to_vec().tobytes())
+
+    @staticmethod
+    def read_from_file(f, dtype):
+        import numpy as np
+        from .traits import parameter
+        from .vector import _read_exact
+        dt = parameter(dtype)
+        elem_size, rows, cols = (int(x) for x in np.frombuffer(_read_exact(f, 24), dtype=np.uint64))
+        if elem_size != dt.size:       # matrix.rs:97-100
+            raise AssertionError("Elem size from buffer does not seem to match, what was expected!Missmatch in endiannes?")
+        return Matrix.from_vec(np.frombuffer(_read_exact(f, rows * cols * dt.size), dtype=dt.np), rows, cols, dt)
+
+    def save(self, path):
+        with open(path, "wb") as f:
+            self.write_to_file(f)
+
+    @staticmethod
+    def open(path, dtype):
+        with open(path, "rb") as f:
+            return Matrix.read_from_file(f, dtype)
+
     def __repr__(self):                           # matrix.rs:289-317
         v = self.to_vec()
         rows = ["\t " + ", ".join(repr(x.item()) for x in v[r * self.col_count:(r + 1) * self.col_count]) for r in range(self.row_count)]

@@ -255,11 +255,41 @@ class Vector:
         inv = self.dtype.np.type(1.0) / self.length()
         return self * inv
 
+    # ---- persistence (vector.rs:183-245, util.rs:6-21): native-endian u64 element size, u64 element
+    # count, raw data.  Files written by the reference load here and vice versa.
+    def write_to_file(self, f):
+        f.write(np.array([self.dtype.size, self._len], dtype=np.uint64).tobytes())
+        f.write(self.to_vec().tobytes())
+
+    @staticmethod
+    def read_from_file(f, dtype):
+        dt = parameter(dtype)
+        elem_size, count = (int(x) for x in np.frombuffer(_read_exact(f, 16), dtype=np.uint64))
+        if elem_size != dt.size:       # vector.rs:215-220
+            raise AssertionError("Elem size from buffer does not seem to match, what was expected!Missmatch in endiannes?")
+        return Vector.from_vec(np.frombuffer(_read_exact(f, count * dt.size), dtype=dt.np), dt)
+
+    def save(self, path):
+        with open(path, "wb") as f:
+            self.write_to_file(f)
+
+    @staticmethod
+    def open(path, dtype):
+        with open(path, "rb") as f:
+            return Vector.read_from_file(f, dtype)
+
     # ---- formatting (vector.rs:678-698)
     def __repr__(self):
         return "{ " + ", ".join(repr(x.item()) for x in self.to_vec()) + " }"
 
     __str__ = __repr__
+
+
+def _read_exact(f, n):
+    data = f.read(n)
+    if len(data) != n:
+        raise EOFError("Failed to read all data from file")       # vector.rs:244
+    return data
 
 
 def dot(a, b):                                    # vector.rs:326-363

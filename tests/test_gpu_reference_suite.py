@@ -92,6 +92,30 @@ def test_vec_mul_scl(la):                     # tests.rs:195-206
     assert r == a * 2
 
 
+def test_save_load_vec(la, tmp_path):         # tests.rs:208-221
+    path = str(tmp_path / "save_load_vec.tmp")
+    a = la.Vector.from_vec(GOLD["save_load_vec"]["a"], TestType)
+    a.save(path)
+    b = la.Vector.open(path, TestType)
+    assert a == b
+    raw = open(path, "rb").read()              # util.rs:6-21 / vector.rs:202-207: u64 elem size, u64 count, data
+    assert np.frombuffer(raw[:16], np.uint64).tolist() == [4, 4]
+    assert np.frombuffer(raw[16:], np.uint32).tolist() == GOLD["save_load_vec"]["a"]
+    with pytest.raises(AssertionError):       # vector.rs:215-220
+        la.Vector.open(path, "u64")
+
+
+def test_save_load_mat(la, tmp_path):         # tests.rs:223-238
+    path = str(tmp_path / "save_load_mat.tmp")
+    g = GOLD["save_load_mat"]
+    a = la.Matrix.from_vec(g["a"], *g["shape"], TestType)
+    a.save(path)
+    b = la.Matrix.open(path, TestType)
+    assert a == b and b.len() == tuple(g["shape"])
+    raw = open(path, "rb").read()
+    assert np.frombuffer(raw[:24], np.uint64).tolist() == [4] + g["shape"]
+
+
 def test_normalize_vec(la):                   # tests.rs:240-252
     for size in GOLD["normalize_vec"]["sizes"]:
         v = np.arange(1, size + 1, dtype=np.float32)

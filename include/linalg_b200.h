@@ -182,6 +182,8 @@ la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const
  *                  infinity or a magnitude outside [2^-100, 2^100] (the call reads one flag back, so it
  *                  blocks for the length of the pre-pass).
  *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 from 512^3 multiply-adds up, LA_GEMM_SIMT below.
+ * 8/16/32-bit integer products of that size run as exact byte-limb products on the INT8 tensor cores
+ * (bit-identical results, mod 2^n) unless LA_GEMM_SIMT is selected.
  * Process-wide; LA_GEMM_MODE=simt|3xtf32|auto in the environment sets the initial value. */
 enum { LA_GEMM_SIMT = 0, LA_GEMM_3XTF32 = 1, LA_GEMM_AUTO = 2 };
 la_status la_set_gemm_mode(int mode);

@@ -400,11 +400,12 @@ int initial_gemm_mode() {
     return LA_GEMM_AUTO;
 }
 int g_gemm_mode = initial_gemm_mode();
-int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32 (la_gemm_last_engine: test hook)
+int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32, 3 int8-limb tensor cores (la_gemm_last_engine: test hook)
 
 }  // namespace
 
 la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled);   // gemm_tc.cu
+la_status la_gemm_limb(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled);  // gemm_limb.cu
 
 extern "C" la_status la_set_gemm_mode(int mode) {
     if (mode != LA_GEMM_SIMT && mode != LA_GEMM_3XTF32 && mode != LA_GEMM_AUTO) return la_fail(LA_ERR_ARG, "unknown GEMM mode %d", mode);
@@ -447,6 +448,12 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 2; return LA_OK; }
+    }
+    // 8/16/32-bit integers: exact limb products on the INT8 tensor cores (mode SIMT keeps the IMAD engines)
+    if (dtype != LA_F32 && dtype != LA_F64 && la_dtype_size(dtype) <= 4 && mode != LA_GEMM_SIMT && (double)M * (double)N * (double)K >= 134217728.0) {
+        bool handled = false;
+        LA_TRY(la_gemm_limb(dtype, C, A, B, M, K, N, st, &handled));
+        if (handled) { g_last_engine = 3; return LA_OK; }
     }
     if (tma_ok) {
         g_last_engine = 1;

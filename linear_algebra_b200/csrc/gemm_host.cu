@@ -69,10 +69,14 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     auto t0 = std::chrono::steady_clock::now();
     auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
 
-    // row block: about a sixteenth of M (short pipeline tail), a multiple of 128 rows, 256 .. 2048
-    size_t rb = ((M / 16 + 127) / 128) * 128;
-    if (rb < 256) rb = 256;
-    if (rb > 2048) rb = 2048;
+    // Row block.  Tensor engine: about a sixteenth of M (short pipeline tail) but at least 512 rows, so that
+    // one block still fills most SM pairs (512 x N / (256 x 256) tiles).  Other engines are compute bound and
+    // tile-quantised: a quarter of M, at least 1024 rows.  Multiples of 128 / 256 rows.
+    const bool want_tensor = allow_tensor && dtype == LA_F32 && mode != LA_GEMM_SIMT && K > 0 &&
+                             (mode == LA_GEMM_3XTF32 || (double)M * (double)N * (double)K >= 134217728.0);
+    size_t rb;
+    if (want_tensor) { rb = ((M / 16 + 127) / 128) * 128; if (rb < 512) rb = 512; if (rb > 2048) rb = 2048; }
+    else             { rb = ((M / 4 + 255) / 256) * 256;  if (rb < 1024) rb = 1024; if (rb > 4096) rb = 4096; }
     if (rb > M) rb = M;
     const size_t nblocks = (M + rb - 1) / rb;
 
@@ -83,8 +87,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     void* Ab[2] = {Abuf0.p, Abuf1.p}; void* Cb[2] = {Cbuf0.p, Cbuf1.p};
 
     // tensor engine for f32 when the mode and the shapes allow: B is split once, up front
-    bool tensor = allow_tensor && dtype == LA_F32 && mode != LA_GEMM_SIMT && K > 0 && la_tc_shape_ok(Ab[0], B.p, Cb[0], rb, K, N) &&
-                  (mode == LA_GEMM_3XTF32 || (double)M * (double)N * (double)K >= 134217728.0);
+    bool tensor = want_tensor && la_tc_shape_ok(Ab[0], B.p, Cb[0], rb, K, N);
     float* ah[2] = {nullptr, nullptr}; float* al[2] = {nullptr, nullptr};
     volatile unsigned* flag_host = nullptr; unsigned* flag = nullptr;
     if (tensor) {

@@ -1,0 +1,294 @@
+// csrc/gemm_limb.cu -- exact integer Matrix x Matrix on the INT8 tensor cores.
+//
+// Same contract as the integer path of gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169: results
+// mod 2^n, any summation order gives the same bits), other arithmetic.  An n-bit element
+// (n = 8 L, L = 1, 2, 4 for 8-, 16-, 32-bit types, signed or unsigned: two's complement) is the sum
+// of L unsigned byte "limbs", x = sum_i x_i 2^(8 i).  Modulo 2^n
+//     x * y  =  sum over i + j < L of  2^(8 (i + j)) x_i y_j ,
+// so C = A x B mod 2^n needs L (L + 1) / 2 byte-matrix products A_i x B_j, accumulated per shift
+// class s = i + j.  Each is a tcgen05.mma kind::i8 (u8 x u8 -> s32).  The s32 accumulators may wrap:
+// only bits below 2^n of  P_0 + 2^8 P_1 + 2^16 P_2 + 2^24 P_3  survive, and wrapping keeps exactly
+// those.  10 MMAs per 32-bit product still run ~8x faster than the half-rate IMAD pipe.
+//
+//   pre-pass   limb_split_kernel            A (M x K)  -> A_0 .. A_{L-1}   (M x K bytes each)
+//              limb_split_transpose_kernel  B (K x N)  -> Bt_0 .. Bt_{L-1} (N x K bytes each), K-major
+//   kernel     CTA pairs (cta_group::2) own a 256 x 128 tile; per 128-byte k-block each CTA TMA-loads
+//              its 128 rows of every A limb and 64 of the 128 rows of every Bt limb (128-byte swizzle);
+//              the leader's MMA warp issues the L(L+1)/2 MMAs per 32-wide k-step into L accumulators of
+//              128 columns in tensor memory; 8 epilogue warps per CTA combine them with shifts and store.
+// Shapes: K % 16 == 0 (TMA row pitch), N * sizeof(T) % 16 == 0, 16-byte aligned bases; anything else
+// (and 64-bit types) stays on the SIMT / generic engines.  Roofline: tensor pipe (int8).
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int LB_BK = 128;            // bytes of K per k-block = one 128-byte swizzle row = 128 byte-limbs
+constexpr int LB_UMMA_K = 32;         // 8-bit operands: 32 elements (32 bytes) of K per instruction
+constexpr int LB_BN = 128;            // tile columns (accumulator columns per shift class)
+constexpr int LB_THREADS = 384;
+constexpr int LB_A_TILE = 128 * LB_BK;        // 16 KB: 128 rows of one A limb
+constexpr int LB_B_TILE = 64 * LB_BK;         // 8 KB:  this CTA's 64 of the 128 Bt rows of one limb
+
+template <int L> struct LimbShape {
+    static constexpr int STAGE_BYTES = L * (LB_A_TILE + LB_B_TILE);
+    static constexpr int STAGES = (L == 4) ? 2 : (L == 2 ? 4 : 6);
+    static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024;
+    static constexpr int TMEM_COLS = L * LB_BN;            // 128, 256, 512: powers of two
+};
+
+// kind::i8: unsigned 8-bit A and B, s32 accumulator, both operands K-major, no saturation.
+__host__ __device__ constexpr uint32_t umma_idesc_u8(int M, int N) {
+    return (2u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_i8_2sm(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+template <typename OutT, int L>
+__global__ void __launch_bounds__(LB_THREADS, 1)
+gemm_limb_2cta_kernel(OutT* __restrict__ C, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                      int M, int N, int K, int pair_tiles_m) {
+    using S = LimbShape<L>;
+    constexpr int STAGES = S::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ alignas(8) uint64_t full_bar[STAGES];     // leader: both CTAs' slabs have landed
+    __shared__ alignas(8) uint64_t empty_bar[STAGES];    // per CTA: the pair's MMAs are done with this slot
+    __shared__ alignas(8) uint64_t acc_full_bar;         // per CTA: all accumulators complete
+    __shared__ uint32_t tmem_base_slot;
+
+    const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1;
+    const int m0 = (pair % pair_tiles_m) * 256 + (int)crank * 128;
+    const int n0 = (pair / pair_tiles_m) * LB_BN;
+    const int num_kb = (K + LB_BK - 1) / LB_BK;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&acc_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 9) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(S::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 8) {
+            // ---------------- TMA producer (both CTAs).  The limb planes are stacked along the row
+            // coordinate of one tensor map: limb i of A starts at row i * M, of Bt at row i * N.
+            if (lane == 0) {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int s = kb % STAGES;
+                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                    mbar_wait(&empty_bar[s], ph ^ 1u);
+                    uint8_t* st = ring_ptr + (size_t)s * S::STAGE_BYTES;
+                    if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * S::STAGE_BYTES);
+#pragma unroll
+                    for (int i = 0; i < L; ++i) {
+                        tma_load_2d_2sm(st + i * LB_A_TILE, &map_a, &full_bar[s], kb * LB_BK, i * M + m0);
+                        tma_load_2d_2sm(st + L * LB_A_TILE + i * LB_B_TILE, &map_b, &full_bar[s], kb * LB_BK, i * N + n0 + (int)crank * 64);
+                    }
+                }
+            }
+        } else if (warp == 9 && crank == 0) {
+            // ---------------- MMA issuer (leader CTA only)
+            constexpr uint32_t idesc = umma_idesc_u8(256, LB_BN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                mbar_wait(&full_bar[s], ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (elect_one()) {
+                    const uint32_t st = ring + (uint32_t)s * S::STAGE_BYTES;
+#pragma unroll
+                    for (int kk = 0; kk < LB_BK / LB_UMMA_K; ++kk) {
+                        const uint64_t adv = (uint64_t)((kk * LB_UMMA_K) >> 4);      // 32 bytes of K per step
+#pragma unroll
+                        for (int i = 0; i < L; ++i)
+#pragma unroll
+                            for (int j = 0; j + i < L; ++j) {
+                                // shift class i + j accumulates in columns (i + j) * 128 ..; the first product of a
+                                // class at the very first k-step overwrites (j == 0 or i == 0 comes first per class)
+                                const uint32_t first = (kb == 0 && kk == 0 && i == 0) ? 0u : 1u;
+                                umma_i8_2sm(tmem_base + (uint32_t)((i + j) * LB_BN),
+                                            umma_desc_k_sw128(st + i * LB_A_TILE) + adv,
+                                            umma_desc_k_sw128(st + L * LB_A_TILE + j * LB_B_TILE) + adv, idesc, first);
+                            }
+                    }
+                    umma_commit_2sm(&empty_bar[s]);
+                    if (kb == num_kb - 1) umma_commit_2sm(&acc_full_bar);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // ---------------- epilogue warps 0..7: lane quadrant = warp % 4, column half = warp / 4
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int quad = warp & 3, half = warp >> 2;
+        mbar_wait(&acc_full_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int row = m0 + quad * 32 + lane;
+        constexpr int PER16 = 16 / (int)sizeof(OutT);       // elements per 16-byte store
+#pragma unroll 1
+        for (int c0 = half * 64; c0 < half * 64 + 64; c0 += 32) {
+            uint32_t p[L][32];
+#pragma unroll
+            for (int s = 0; s < L; ++s) tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(s * LB_BN + c0), p[s]);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            OutT out[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+                uint32_t v = p[0][e];
+#pragma unroll
+                for (int s = 1; s < L; ++s) v += p[s][e] << (8 * s);
+                out[e] = (OutT)v;
+            }
+            if (row < M) {
+                OutT* crow = C + (size_t)row * N + n0 + c0;
+#pragma unroll
+                for (int q = 0; q < 32 / PER16; ++q) {
+                    const int n = n0 + c0 + q * PER16;
+                    if (n < N) {        // N * sizeof(T) % 16 == 0: a 16-byte chunk is wholly inside or outside
+                        uint4 v;
+                        memcpy(&v, &out[q * PER16], 16);
+                        __stcs(reinterpret_cast<uint4*>(crow + q * PER16), v);
+                    }
+                }
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 9) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(S::TMEM_COLS) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ pre-pass
+// A (rows x K elements of U) -> L byte planes, plane i at planes + i * rows * K.  Each thread turns 16
+// consecutive elements into one 16-byte store per plane.  K % 16 == 0.
+template <typename U, int L>
+__global__ void __launch_bounds__(256)
+limb_split_kernel(uint8_t* __restrict__ planes, const U* __restrict__ x, size_t n16, size_t plane_bytes) {
+    const size_t stride = (size_t)gridDim.x * 256;
+    for (size_t g = (size_t)blockIdx.x * 256 + threadIdx.x; g < n16; g += stride) {
+        U v[16];
+        constexpr int PACKS = (int)sizeof(U);          // 16 elements = sizeof(U) packets of 16 bytes
+#pragma unroll
+        for (int p = 0; p < PACKS; ++p) *reinterpret_cast<uint4*>(&v[p * (16 / sizeof(U))]) = __ldcs(reinterpret_cast<const uint4*>(x + g * 16) + p);
+#pragma unroll
+        for (int i = 0; i < L; ++i) {
+            alignas(16) uint8_t b[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) b[e] = (uint8_t)(v[e] >> (8 * i));
+            __stcs(reinterpret_cast<uint4*>(planes + (size_t)i * plane_bytes + g * 16), *reinterpret_cast<const uint4*>(b));
+        }
+    }
+}
+
+// B (K x N elements of U) -> L byte planes of B^T (N x K bytes each).  64 x 64 tile through shared memory.
+// K % 16 == 0; N arbitrary (guards).
+template <typename U, int L>
+__global__ void __launch_bounds__(256)
+limb_split_transpose_kernel(uint8_t* __restrict__ planes, const U* __restrict__ B, size_t K, size_t N, unsigned tiles_n, size_t plane_bytes) {
+    __shared__ U tile[64][65];
+    const size_t k0 = (size_t)(blockIdx.x / tiles_n) * 64, n0 = (size_t)(blockIdx.x % tiles_n) * 64;
+    for (int idx = threadIdx.x; idx < 64 * 64; idx += 256) {        // coalesced along n
+        const int r = idx / 64, c = idx % 64;
+        tile[r][c] = (k0 + r < K && n0 + c < N) ? B[(k0 + r) * N + n0 + c] : U(0);
+    }
+    __syncthreads();
+    // thread -> (Bt row n0+cc, 16 consecutive k): 64 rows x 4 groups = 256 threads
+    const int cc = threadIdx.x / 4, q = threadIdx.x % 4;
+    if (n0 + cc < N && k0 + (size_t)q * 16 < K) {
+#pragma unroll
+        for (int i = 0; i < L; ++i) {
+            alignas(16) uint8_t b[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) b[e] = (uint8_t)(tile[q * 16 + e][cc] >> (8 * i));
+            __stcs(reinterpret_cast<uint4*>(planes + (size_t)i * plane_bytes + (n0 + cc) * K + k0 + (size_t)q * 16), *reinterpret_cast<const uint4*>(b));
+        }
+    }
+}
+
+// All L planes of an operand as ONE 2-D byte tensor: (L * rows) x K, box = box_rows x 128 bytes, 128-byte swizzle.
+la_status limb_make_map(CUtensorMap* map, const uint8_t* base, size_t total_rows, size_t K, int box_rows) {
+    EncodeTiledFn enc; LA_TRY(tc_get_encode(&enc));
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)total_rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K};
+    cuuint32_t box[2] = {(cuuint32_t)LB_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled (limb engine) failed with CUresult %d", (int)r);
+    return LA_OK;
+}
+
+template <typename U, int L>
+la_status limb_gemm(U* C, const U* A, const U* B, size_t M, size_t K, size_t N, cudaStream_t st, int sm_count) {
+    using S = LimbShape<L>;
+    const size_t a_plane = M * K, b_plane = N * K;
+    void* scratch; LA_TRY(la_scratch(st, (size_t)L * (a_plane + b_plane), &scratch));
+    uint8_t* a_planes = (uint8_t*)scratch + LA_SCRATCH_ZEROED;
+    uint8_t* b_planes = a_planes + (size_t)L * a_plane;          // a_plane % 16 == 0 keeps this 16-byte aligned
+    limb_split_kernel<U, L><<<(unsigned)sm_count * 8, 256, 0, st>>>(a_planes, A, a_plane / 16, a_plane);
+    LA_LAUNCH_CHECK();
+    const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
+    if (tk * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "limb engine pre-pass: B is too large");
+    limb_split_transpose_kernel<U, L><<<(unsigned)(tk * tn), 256, 0, st>>>(b_planes, B, K, N, (unsigned)tn, b_plane);
+    LA_LAUNCH_CHECK();
+    // Within a plane, rows past M (or N) would run into the next plane instead of reading zeros; they only
+    // feed output rows / columns the epilogue never stores, so that is harmless.
+    CUtensorMap map_a, map_b;
+    LA_TRY(limb_make_map(&map_a, a_planes, (size_t)L * M, K, 128));
+    LA_TRY(limb_make_map(&map_b, b_planes, (size_t)L * N, K, 64));
+    auto kern = gemm_limb_2cta_kernel<U, L>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM_BYTES));
+    const size_t ptm = (M + 255) / 256, tnn = (N + LB_BN - 1) / LB_BN;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * ptm * tnn)); cfg.blockDim = dim3(LB_THREADS); cfg.dynamicSmemBytes = S::SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, map_a, map_b, (int)M, (int)N, (int)K, (int)ptm));
+    return LA_OK;
+}
+
+}  // namespace
+
+// Integer GEMM on the INT8 tensor cores when the shape allows; *handled says whether it ran.
+la_status la_gemm_limb(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled) {
+    *handled = false;
+    const size_t es = la_dtype_size(dtype);
+    if (es > 4 || dtype == LA_F32) return LA_OK;
+    if (M < 128 || N < 64 || K < 128 || K % 16 != 0 || (N * es) % 16 != 0 || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C) ||
+        4 * M >= (1u << 31) || 4 * N >= (1u << 31) || K >= (1u << 31))
+        return LA_OK;
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    la_status s;
+    switch (es) {
+    case 1: s = limb_gemm<uint8_t, 1>((uint8_t*)C, (const uint8_t*)A, (const uint8_t*)B, M, K, N, st, info->sm_count); break;
+    case 2: s = limb_gemm<uint16_t, 2>((uint16_t*)C, (const uint16_t*)A, (const uint16_t*)B, M, K, N, st, info->sm_count); break;
+    default: s = limb_gemm<uint32_t, 4>((uint32_t*)C, (const uint32_t*)A, (const uint32_t*)B, M, K, N, st, info->sm_count); break;
+    }
+    if (s == LA_OK) *handled = true;
+    return s;
+}

@@ -302,7 +302,7 @@ def test_matmat_auto_mode_picks_the_engine_by_size(la):
     assert lib.la_gemm_last_engine() == 2          # tensor cores
     a = gen.values("i32", 512 * 1024, 53); b = gen.values("i32", 1024 * 512, 54)
     C = la.Matrix.from_vec(a, 512, 1024) * la.Matrix.from_vec(b, 1024, 512)
-    assert same(C.to_vec(), oracle.port().mul_mat_mat(a, b, 512, 1024, 512)) and lib.la_gemm_last_engine() == 1   # integers never use it
+    assert same(C.to_vec(), oracle.port().mul_mat_mat(a, b, 512, 1024, 512)) and lib.la_gemm_last_engine() == 3   # integers: INT8-limb tensor engine
 
 
 def test_matmat_f64(la):
@@ -382,3 +382,30 @@ def test_mul_host_redoes_the_product_in_f32_for_non_finite_operands(la):
     assert np.array_equal(np.isinf(got), np.isinf(ref)) and not np.isnan(got).any()
     finite = np.isfinite(ref)
     assert np.linalg.norm(got[finite] - ref[finite]) <= NORMWISE_TOL * np.linalg.norm(ref[finite])
+
+
+# ------------------------------------------------------------------ integer GEMM on the INT8 tensor cores
+@pytest.mark.parametrize("name", ["u8", "i8", "u16", "i16", "u32", "i32"])
+def test_matmat_limb_engine_is_bit_exact(la, name):
+    """The limb engine (byte-limb products on tcgen05 kind::i8, s32 accumulators that may wrap) must give
+    the reference's bits: integers are exact mod 2^n whatever the order or the machinery."""
+    P = oracle.port(); lib = la._lib.lib
+    for M, K, N in ((512, 1024, 512), (388, 2048, 272), (1024, 4096, 128)):
+        a = gen.values(name, M * K, 70); b = gen.values(name, K * N, 71)
+        C = la.Matrix.from_vec(a, M, K, dt(la, name)) * la.Matrix.from_vec(b, K, N, dt(la, name))
+        assert lib.la_gemm_last_engine() == 3, "limb engine did not take %s %dx%dx%d" % (name, M, K, N)
+        assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (name, M, K, N)
+    # all-ones bytes: every limb product is 255*255 and the s32 accumulators overflow for 32-bit types
+    M, K, N = 256, 32768, 128
+    a = np.full(M * K, -1, NP[name]) if np.dtype(NP[name]).kind == "i" else np.full(M * K, np.iinfo(NP[name]).max, NP[name])
+    C = la.Matrix.from_vec(a, M, K, dt(la, name)) * la.Matrix.from_vec(a[:K * N], K, N, dt(la, name))
+    assert lib.la_gemm_last_engine() == 3
+    assert same(C.to_vec(), P.mul_mat_mat(a, a[:K * N], M, K, N)), (name, "wrap")
+    # SIMT mode keeps the IMAD engines
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_SIMT)
+    try:
+        a = gen.values(name, 512 * 1024, 72); b = gen.values(name, 1024 * 512, 73)
+        C = la.Matrix.from_vec(a, 512, 1024, dt(la, name)) * la.Matrix.from_vec(b, 1024, 512, dt(la, name))
+        assert lib.la_gemm_last_engine() in (0, 1) and same(C.to_vec(), P.mul_mat_mat(a, b, 512, 1024, 512))
+    finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)

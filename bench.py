@@ -294,8 +294,16 @@ def run_ours(args):
     engine_used = lib.lib.la_gemm_last_engine()     # 1 = TMA SIMT, 2 = tcgen05 3xTF32
 
     # e2e: public API on HOST buffers; H2D of A and B and D2H of C inside the timed region.
-    def e2e_step():                                 # one streamed call
-        la.mul_host(hA, hB, rows, n, n, out=hC)
+    comm = None
+    if dist is not None:
+        from linear_algebra_b200 import dist as ladist
+        comm = ladist.Comm()
+
+    def e2e_step():                                 # one streamed call (N > 1: each rank uploads 1/N of B, NVLink all_gather)
+        if comm is None:
+            la.mul_host(hA, hB, rows, n, n, out=hC)
+        else:
+            ladist.mul_host(comm, hA, hB, n, n, n, out=hC)
 
     def three_call_step():                          # the reference user's sequence
         a = la.Matrix.from_vec(hA, rows, n); b = la.Matrix.from_vec(hB, n, n)
@@ -346,6 +354,7 @@ def run_ours(args):
             roofline = {"bound": "fp32-fma (SIMT; MEASURED_PEAKS.json has no FP32 figure)", "achieved": round(per_gpu_tflops, 2),
                         "peak": round(simt_peak, 2), "unit": "TFLOP/s", "frac": round(per_gpu_tflops / simt_peak, 4),
                         "peak_source": "nominal: %d SMs x 128 lanes x 2 x %.0f MHz" % (sm_count.value, sm_max_mhz),
+                        "frac_at_observed_clock": (round(per_gpu_tflops / (sm_count.value * 256 * clocks["sm_mhz"] * 1e6 / 1e12), 4) if clocks.get("sm_mhz") else None),
                         "traffic": ncu_traffic("profiles/r1_gemm_f32_8192_ncu_full.txt", "gemm_tma_kernel")}
             engine_name = "TMA-fed FP32 SIMT (FFMA2), A^T staged per call"
             launches = 2

@@ -87,6 +87,9 @@ la_status la_free(void* dev_ptr);
 la_status la_upload(void* dst_dev, const void* src_host, size_t bytes, void* stream);   /* async if src is pinned */
 la_status la_download(void* dst_host, const void* src_dev, size_t bytes, void* stream); /* returns after the copy */
 la_status la_copy(void* dst_dev, const void* src_dev, size_t bytes, void* stream);
+/* `height` rows of `width_bytes`, rows `*_pitch` bytes apart (device to device; used to place the
+ * blocks of a multi-GPU transpose). */
+la_status la_copy_2d(void* dst_dev, size_t dst_pitch, const void* src_dev, size_t src_pitch, size_t width_bytes, size_t height, void* stream);
 la_status la_fill(int dtype, void* dst_dev, const void* value_host, size_t n, void* stream);
 /* Synthetic data generated on the device (no counterpart in the reference; bench / test utility):
  * element i = f(splitmix64(seed ^ i)): floats uniform in [-1,1) from the top 24 (f32) / 53 (f64)
@@ -169,7 +172,8 @@ la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_
  * (src/matrix.rs:39-46, 221-265, src/vector.rs:53-78) -- as one call on HOST buffers: B is uploaded
  * once, A and C stream through in row blocks on separate copy streams so uploads, multiplies and
  * downloads overlap.  Same results as la_mul_mat_mat.  Blocks until C_host is complete; pinned host
- * buffers (la_host_alloc) give full PCIe rate, pageable ones work. */
+ * buffers (la_host_alloc) give full PCIe rate, pageable ones work; any of the three may also be a
+ * device pointer (e.g. a B that is already resident). */
 la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N);
 
 /* f32 GEMM engine.

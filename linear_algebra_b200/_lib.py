@@ -46,6 +46,7 @@ SIGNATURES = {
     "la_upload": [_V, _V, _Z, _V],
     "la_download": [_V, _V, _Z, _V],
     "la_copy": [_V, _V, _Z, _V],
+    "la_copy_2d": [_V, _Z, _V, _Z, _Z, _Z, _V],
     "la_fill": [_I, _V, _V, _Z, _V],
     "la_synth": [_I, _V, ctypes.c_uint64, _Z, _V],
     "la_host_alloc": [_PV, _Z],

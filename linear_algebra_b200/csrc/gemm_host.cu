@@ -6,6 +6,8 @@
 // parts: B goes up once (and is pre-processed once for the tensor engine); A and C move in row
 // blocks on their own copy streams, so block i+1 uploads and block i-1 downloads while block i
 // multiplies (PCIe is full duplex).  Results are those of la_mul_mat_mat on the same operands.
+// Any of the three pointers may also be a device pointer (the copies use cudaMemcpyDefault): the
+// multi-GPU path passes a B that ranks have gathered over NVLink instead of each uploading all of it.
 #include "common.cuh"
 #include <chrono>
 #include <cstdio>
@@ -102,7 +104,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     LA_CUDA(cudaStreamWaitEvent(hs->in, hs->b_up, 0));
     LA_CUDA(cudaStreamWaitEvent(hs->out, hs->b_up, 0));
 
-    LA_CUDA(cudaMemcpyAsync(B.p, B_host, K * N * es, cudaMemcpyHostToDevice, hs->in));
+    LA_CUDA(cudaMemcpyAsync(B.p, B_host, K * N * es, cudaMemcpyDefault, hs->in));
     LA_CUDA(cudaEventRecord(hs->b_up, hs->in));
     LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->b_up, 0));
     if (tensor) LA_TRY(la_tc_split_bt((float*)bt_hi.p, (float*)bt_lo.p, (const float*)B.p, K, N, flag, hs->cmp));
@@ -113,7 +115,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
         const size_t r0 = i * rb, rows = (r0 + rb <= M) ? rb : M - r0;
         // upload block i once the multiply that last read this A buffer is done
         if (i >= 2) LA_CUDA(cudaStreamWaitEvent(hs->in, hs->cmp_done[b], 0));
-        LA_CUDA(cudaMemcpyAsync(Ab[b], (const char*)A_host + r0 * K * es, rows * K * es, cudaMemcpyHostToDevice, hs->in));
+        LA_CUDA(cudaMemcpyAsync(Ab[b], (const char*)A_host + r0 * K * es, rows * K * es, cudaMemcpyDefault, hs->in));
         LA_CUDA(cudaEventRecord(hs->in_done[b], hs->in));
         // multiply once the block is up and the download that last read this C buffer is done
         LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->in_done[b], 0));
@@ -131,7 +133,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
         LA_CUDA(cudaEventRecord(hs->cmp_done[b], hs->cmp));
         // download
         LA_CUDA(cudaStreamWaitEvent(hs->out, hs->cmp_done[b], 0));
-        LA_CUDA(cudaMemcpyAsync((char*)C_host + r0 * N * es, Cb[b], rows * N * es, cudaMemcpyDeviceToHost, hs->out));
+        LA_CUDA(cudaMemcpyAsync((char*)C_host + r0 * N * es, Cb[b], rows * N * es, cudaMemcpyDefault, hs->out));
         LA_CUDA(cudaEventRecord(hs->out_done[b], hs->out));
     }
     if (dbg) fprintf(stderr, "[hostgemm] all enqueued at %.3f ms\n", ms_since());

@@ -193,6 +193,13 @@ extern "C" la_status la_copy(void* dst_dev, const void* src_dev, size_t bytes, v
     LA_CUDA(cudaMemcpyAsync(dst_dev, src_dev, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return LA_OK;
 }
+extern "C" la_status la_copy_2d(void* dst_dev, size_t dst_pitch, const void* src_dev, size_t src_pitch, size_t width_bytes, size_t height, void* stream) {
+    if (width_bytes == 0 || height == 0) return LA_OK;
+    if (!dst_dev || !src_dev) return la_fail(LA_ERR_ARG, "la_copy_2d: NULL pointer");
+    if (dst_pitch < width_bytes || src_pitch < width_bytes) return la_fail(LA_ERR_ARG, "la_copy_2d: pitch smaller than the row width");
+    LA_CUDA(cudaMemcpy2DAsync(dst_dev, dst_pitch, src_dev, src_pitch, width_bytes, height, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return LA_OK;
+}
 extern "C" la_status la_host_alloc(void** host_ptr, size_t bytes) {
     if (!host_ptr) return la_fail(LA_ERR_ARG, "host_ptr is NULL");
     LA_CUDA(cudaMallocHost(host_ptr, bytes ? bytes : 16));

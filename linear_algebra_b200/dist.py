@@ -13,6 +13,9 @@ need no NCCL support for the element type (NCCL has no 16-bit integers).
   v x M                      v and M by rows -> full-length partial all_gather of `cols` elements,
                                                                     rank-ordered adds (la_ew_assign_vec_vec)
   M x M                      A, C by rows, B replicated             none
+  M x M on host buffers      A, C by rows; every rank uploads 1/world all_gather of B over NVLink (mul_host)
+                             of B over its own PCIe link
+  transpose                  rows in -> rows of the transpose out   all_to_all of (rows_q x cols_p) blocks
 
 `Comm` wraps the process group; `local` is the module providing Vector/Matrix (the real one by
 default; the CPU tests inject a numpy stand-in to exercise this file's logic under gloo)."""
@@ -57,6 +60,11 @@ class Comm:
         """dst (world * nbytes device bytes, rank order) <- every rank's src (nbytes device bytes)."""
         out = self._tensor(dst_ptr, nbytes * self.world)
         self.dist.all_gather_into_tensor(out, self._tensor(src_ptr, nbytes), group=self.group)
+
+    def all_to_all_device(self, dst_ptr, dst_counts, src_ptr, src_counts):
+        """Byte counts per rank; chunks are contiguous and in rank order on both sides."""
+        out = self._tensor(dst_ptr, sum(dst_counts)); inp = self._tensor(src_ptr, sum(src_counts))
+        self.dist.all_to_all_single(out, inp, output_split_sizes=list(dst_counts), input_split_sizes=list(src_counts), group=self.group)
 
     def barrier(self):
         self.dist.barrier(group=self.group)
@@ -207,6 +215,67 @@ class ShardedMatrix:
             lo, hi = partition(self.global_rows, self.comm.world, r)
             out.append(np.frombuffer(p, dtype=self.local.dtype.np, count=(hi - lo) * self.col_count))
         return np.concatenate(out)
+
+
+def transpose(sm):
+    """Transpose of a row-sharded matrix, row-sharded again (rank p ends up with rows [p_lo, p_hi) of
+    the transpose = columns of the input).  Local transpose, one all_to_all of contiguous
+    (cols_p x rows_q) blocks over NVLink, then strided placement of the received blocks."""
+    comm, m = sm.comm, sm._mod()
+    rows_g, cols_g = sm.global_rows, sm.col_count
+    if comm.world == 1:
+        return ShardedMatrix(comm, sm.local.transpose(), cols_g, sm._m)
+    assert comm.backend == "nccl", "the sharded transpose exchanges device buffers (NCCL)"
+    dt = sm.local.dtype
+    my_rows = sm.hi - sm.lo
+    local_t = sm.local.transpose()                          # cols_g x my_rows: rows [p_lo, p_hi) are rank p's block
+    spans = [partition(cols_g, comm.world, p) for p in range(comm.world)]
+    row_spans = [partition(rows_g, comm.world, q) for q in range(comm.world)]
+    my_lo, my_hi = spans[comm.rank]
+    my_cols = my_hi - my_lo
+    send_counts = [(hi - lo) * my_rows * dt.size for lo, hi in spans]
+    recv_counts = [my_cols * (hi - lo) * dt.size for lo, hi in row_spans]
+    recv = m.Vector.uninitialized(sum(recv_counts) // dt.size, dt)
+    m.synchronize()
+    comm.all_to_all_device(recv.ptr, recv_counts, local_t.data.ptr, send_counts)
+    import torch
+    torch.cuda.current_stream().synchronize()
+    out = m.Matrix.uninitialized(my_cols, rows_g, dt)
+    off = 0
+    for q, (lo, hi) in enumerate(row_spans):                # block from rank q: my_cols x (hi - lo), goes to columns [lo, hi)
+        m._lib.call("la_copy_2d", out.data.ptr + lo * dt.size, rows_g * dt.size, recv.ptr + off, (hi - lo) * dt.size, (hi - lo) * dt.size, my_cols, None)
+        off += recv_counts[q]
+    m.synchronize()
+    return ShardedMatrix(comm, out, cols_g, sm._m)
+
+
+def mul_host(comm, a_shard_host, b_host, a_rows_global, k, n, out=None, local_mod=None):
+    """C = A x B on HOST buffers over all ranks: A and C are row-block sharded (each rank passes its
+    own rows of A and gets its rows of C), every rank holds all of B on the host.  Each rank uploads
+    only its 1/world slice of B over its own PCIe link and the slices are all_gathered over NVLink;
+    then the streamed host-buffer GEMM (la_mul_mat_mat_host) runs on the local rows with the gathered,
+    device-resident B."""
+    m = local_mod or _default_local()
+    from .traits import parameter
+    a = np.ascontiguousarray(a_shard_host).reshape(-1); b = np.ascontiguousarray(b_host, dtype=a.dtype).reshape(-1)
+    dt = parameter(a.dtype)
+    lo, hi = partition(a_rows_global, comm.world, comm.rank)
+    rows = hi - lo
+    assert a.size == rows * k and b.size == k * n
+    if out is None:
+        out = np.empty(rows * n, dtype=a.dtype)
+    if comm.world == 1 or comm.backend != "nccl" or (k % comm.world) != 0:
+        m._lib.call("la_mul_mat_mat_host", dt.code, out.ctypes.data, a.ctypes.data, b.ctypes.data, rows, k, n)
+        return out
+    import torch
+    bdev = m.Vector.uninitialized(k * n, dt)
+    slice_elems = (k // comm.world) * n
+    m._lib.call("la_upload", bdev.ptr + comm.rank * slice_elems * dt.size, b.ctypes.data + comm.rank * slice_elems * dt.size, slice_elems * dt.size, None)
+    m.synchronize()
+    comm.all_gather_device(bdev.ptr, bdev.ptr + comm.rank * slice_elems * dt.size, slice_elems * dt.size)     # in place
+    torch.cuda.current_stream().synchronize()
+    m._lib.call("la_mul_mat_mat_host", dt.code, out.ctypes.data, a.ctypes.data, bdev.ptr, rows, k, n)
+    return out
 
 
 def mul_transpose_mat(vector, sharded_m):

@@ -55,6 +55,22 @@ def main():
         else:
             for got, ref in ((mv, P.mul_vec_transpose_mat(vc, m, rows, cols)), (vm, P.mul_vec_mat(vr, m, rows, cols)), (mm, P.mul_mat_mat(m, bm, rows, cols, 256))):
                 assert np.linalg.norm(got - ref) / np.linalg.norm(ref) <= 1e-5
+        # sharded transpose (all_to_all over NVLink) and the NVLink-gathered host GEMM
+        T = dist.transpose(M)
+        assert T.len() == (cols, rows)
+        assert T.gather().tobytes() == P.transpose(m, rows, cols).tobytes()
+        Mh, Kh, Nh = 1024, 512 * world, 384
+        if np.dtype(np_dt).kind == "f":
+            ah = rng.uniform(-1, 1, Mh * Kh).astype(np_dt); bh = rng.uniform(-1, 1, Kh * Nh).astype(np_dt)
+        else:
+            ah = rng.integers(info.min, info.max, Mh * Kh, dtype=np_dt, endpoint=True); bh = rng.integers(info.min, info.max, Kh * Nh, dtype=np_dt, endpoint=True)
+        lo, hi = dist.partition(Mh, world, rank)
+        ch = dist.mul_host(comm, ah[lo * Kh:hi * Kh], bh, Mh, Kh, Nh)
+        ref = P.mul_mat_mat(ah, bh, Mh, Kh, Nh)[lo * Nh:hi * Nh]
+        if np.dtype(np_dt).kind != "f":
+            assert ch.tobytes() == ref.tobytes()
+        else:
+            assert np.linalg.norm(ch - ref) / np.linalg.norm(ref) <= 1e-5
     comm.barrier()
     td.destroy_process_group()
     print("rank %d/%d ok" % (rank, world))

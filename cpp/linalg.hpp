@@ -10,6 +10,7 @@
 #pragma once
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -95,6 +96,26 @@ class Vector {                              // vector.rs:23-27
     bool operator!=(const Vector& o) const { return !(*this == o); }
 
     T sum() const { T out{}; check(la_sum_vec(D, ptr_, len_, &out, nullptr)); return out; }      // vector.rs:256-293
+
+    // persistence (vector.rs:183-245, util.rs:6-21): native-endian u64 element size, u64 count, raw data
+    void write_to_file(std::FILE* f) const {
+        const uint64_t hdr[2] = {sizeof(T), (uint64_t)len_};
+        const std::vector<T> v = to_vec();
+        if (std::fwrite(hdr, 8, 2, f) != 2 || std::fwrite(v.data(), sizeof(T), v.size(), f) != v.size()) throw Panic("write failed");
+    }
+    static Vector read_from_file(std::FILE* f) {
+        uint64_t hdr[2];
+        if (std::fread(hdr, 8, 2, f) != 2) throw Panic("Failed to read all data from file");
+        if (hdr[0] != sizeof(T)) throw Panic("Elem size from buffer does not seem to match, what was expected!Missmatch in endiannes?");   // vector.rs:215-220
+        std::vector<T> v(hdr[1]);
+        if (std::fread(v.data(), sizeof(T), v.size(), f) != v.size()) throw Panic("Failed to read all data from file");
+        return from_vec(v);
+    }
+    void save(const std::string& path) const { std::FILE* f = std::fopen(path.c_str(), "wb"); if (!f) throw Panic("cannot create " + path); write_to_file(f); std::fclose(f); }
+    static Vector open(const std::string& path) {
+        std::FILE* f = std::fopen(path.c_str(), "rb"); if (!f) throw Panic("Failed to open file");
+        Vector v = read_from_file(f); std::fclose(f); return v;
+    }
     T length() const;                                               // vector.rs:303-305
     Vector normalized() const { T inv = T(1) / length(); return *this * inv; }                  // vector.rs:320-323
     Vector normalize() && { T inv = T(1) / length(); *this *= inv; return std::move(*this); }   // vector.rs:313-317
@@ -157,6 +178,26 @@ class Matrix {                                                      // matrix.rs
     }
     bool operator==(const Matrix& o) const { return rows_ == o.rows_ && cols_ == o.cols_ && data_ == o.data_; }   // matrix.rs:279-287
     bool operator!=(const Matrix& o) const { return !(*this == o); }
+    // persistence (matrix.rs:76-130): u64 element size, u64 rows, u64 cols, raw row-major data
+    void save(const std::string& path) const {
+        std::FILE* f = std::fopen(path.c_str(), "wb"); if (!f) throw Panic("cannot create " + path);
+        const uint64_t hdr[3] = {sizeof(T), (uint64_t)rows_, (uint64_t)cols_};
+        const std::vector<T> v = to_vec();
+        const bool ok = std::fwrite(hdr, 8, 3, f) == 3 && std::fwrite(v.data(), sizeof(T), v.size(), f) == v.size();
+        std::fclose(f);
+        if (!ok) throw Panic("write failed");
+    }
+    static Matrix open(const std::string& path) {
+        std::FILE* f = std::fopen(path.c_str(), "rb"); if (!f) throw Panic("Failed to open file");
+        uint64_t hdr[3];
+        if (std::fread(hdr, 8, 3, f) != 3) { std::fclose(f); throw Panic("Failed to read all data from file"); }
+        if (hdr[0] != sizeof(T)) { std::fclose(f); throw Panic("Elem size from buffer does not seem to match, what was expected!Missmatch in endiannes?"); }   // matrix.rs:97-100
+        std::vector<T> v(hdr[1] * hdr[2]);
+        const bool ok = std::fread(v.data(), sizeof(T), v.size(), f) == v.size();
+        std::fclose(f);
+        if (!ok) throw Panic("Failed to read all data from file");
+        return from_vec(v, hdr[1], hdr[2]);
+    }
     Matrix transpose() const {                                      // not in the reference (north star)
         Matrix r = uninitialized(cols_, rows_);
         check(la_transpose(Parameter<T>::DTYPE, r.data_.ptr_, data_.ptr_, rows_, cols_, nullptr)); check(la_stream_sync(nullptr)); return r;
@@ -190,6 +231,16 @@ Vector<T> mul_transpose_mat(const Vector<T>& v, const Matrix<T>& m) {   // vecto
 template <typename T>
 Matrix<T> mul_column_row(const Vector<T>& column, const Vector<T>& row) {   // matrix.rs:236-238
     return Matrix<T>::mul_helper(column.ptr_, row.ptr_, column.len(), 1, row.len());
+}
+
+// C = A x B on host vectors in one streamed call (la_mul_mat_mat_host): from_vec, from_vec, *, to_vec with the
+// copies overlapped with the multiply.
+template <typename T>
+std::vector<T> mul_host(const std::vector<T>& a, const std::vector<T>& b, size_t a_rows, size_t a_cols, size_t b_cols) {
+    assert_eq(a.size(), a_rows * a_cols); assert_eq(b.size(), a_cols * b_cols);
+    std::vector<T> c(a_rows * b_cols);
+    check(la_mul_mat_mat_host(Parameter<T>::DTYPE, c.data(), a.data(), b.data(), a_rows, a_cols, b_cols));
+    return c;
 }
 
 }  // namespace linalg

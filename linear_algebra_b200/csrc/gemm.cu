@@ -400,6 +400,7 @@ int initial_gemm_mode() {
     return LA_GEMM_AUTO;
 }
 int g_gemm_mode = initial_gemm_mode();
+int g_last_padded = 0;        // the last call went through zero-padded temporaries
 int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32, 3 int8-limb tensor cores (la_gemm_last_engine: test hook)
 
 }  // namespace
@@ -421,6 +422,7 @@ extern "C" la_status la_get_gemm_mode(int* mode) {
 // (0 = default).  -1 forces the generic engine.
 extern "C" la_status la_gemm_set_variant(int v) { g_gemm_variant = v; return LA_OK; }
 extern "C" int la_gemm_last_engine(void) { return g_last_engine; }
+extern "C" int la_gemm_last_padded(void) { return g_last_padded; }
 
 la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode);
 
@@ -443,17 +445,40 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     const bool four_byte = (dtype == LA_F32 || dtype == LA_U32 || dtype == LA_I32);
     const bool tma_ok = four_byte && g_gemm_variant >= 0 && M % 4 == 0 && N % 4 == 0 && la_aligned16(A) && la_aligned16(B) && la_aligned16(C) &&
                         M >= 64 && N >= 64 && K >= 16 && M < (1u << 31) && N < (1u << 31) && K < (1u << 31);
-    // AUTO: the tensor engine for problems big enough to amortise its pre-pass (>= 512^3 multiply-adds)
-    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && (double)M * (double)N * (double)K >= 134217728.0))) {
+    g_last_padded = 0;
+    const bool big = (double)M * (double)N * (double)K >= 134217728.0;      // 512^3 multiply-adds
+    // AUTO: the tensor engine for problems big enough to amortise its pre-pass
+    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && big))) {
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 2; return LA_OK; }
     }
     // 8/16/32-bit integers: exact limb products on the INT8 tensor cores (mode SIMT keeps the IMAD engines)
-    if (dtype != LA_F32 && dtype != LA_F64 && la_dtype_size(dtype) <= 4 && mode != LA_GEMM_SIMT && (double)M * (double)N * (double)K >= 134217728.0) {
+    if (dtype != LA_F32 && dtype != LA_F64 && la_dtype_size(dtype) <= 4 && mode != LA_GEMM_SIMT && big) {
         bool handled = false;
         LA_TRY(la_gemm_limb(dtype, C, A, B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 3; return LA_OK; }
+    }
+    // Ragged sizes or unaligned bases of a large product: instead of dropping to the generic kernel (a 30x
+    // cliff), copy the operands into zero-padded, aligned temporaries (every dimension a multiple of 16),
+    // run the fast engines on those and copy C back.  Zero padding adds exact zeros to every dot product.
+    const size_t es = la_dtype_size(dtype);
+    const bool ragged = (M % 16) || (K % 16) || (N % 16) || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C);   // false on the padded call
+    if (ragged && es <= 4 && big && M < (1u << 30) && N < (1u << 30) && K < (1u << 30)) {
+        const size_t Mp = (M + 15) / 16 * 16, Kp = (K + 15) / 16 * 16, Np = (N + 15) / 16 * 16;
+        void *Ap = nullptr, *Bp = nullptr, *Cp = nullptr;
+        LA_CUDA(cudaMallocAsync(&Ap, Mp * Kp * es, st));
+        LA_CUDA(cudaMallocAsync(&Bp, Kp * Np * es, st));
+        LA_CUDA(cudaMallocAsync(&Cp, Mp * Np * es, st));
+        LA_CUDA(cudaMemsetAsync(Ap, 0, Mp * Kp * es, st));
+        LA_CUDA(cudaMemsetAsync(Bp, 0, Kp * Np * es, st));
+        LA_CUDA(cudaMemcpy2DAsync(Ap, Kp * es, A, K * es, K * es, M, cudaMemcpyDeviceToDevice, st));
+        LA_CUDA(cudaMemcpy2DAsync(Bp, Np * es, B, N * es, N * es, K, cudaMemcpyDeviceToDevice, st));
+        const la_status ps = la_mul_mat_mat_impl(dtype, Cp, Ap, Bp, Mp, Kp, Np, stream, mode);
+        if (ps == LA_OK) LA_CUDA(cudaMemcpy2DAsync(C, N * es, Cp, Np * es, N * es, M, cudaMemcpyDeviceToDevice, st));
+        cudaFreeAsync(Ap, st); cudaFreeAsync(Bp, st); cudaFreeAsync(Cp, st);
+        g_last_padded = 1;
+        return ps;
     }
     if (tma_ok) {
         g_last_engine = 1;

@@ -69,6 +69,24 @@ static void vec_mul_scl() {                      // tests.rs:195-206
     auto a = Vector<TestType>::from_vec({1, 2, 3, 4}); auto r = Vector<TestType>::from_vec({2, 4, 6, 8});
     CHECK(r == a * 2u);
 }
+static void save_load_vec() {                    // tests.rs:208-221
+    const char* path = "save_load_vec.tmp";
+    auto a = Vector<TestType>::from_vec({0x01234567u, 0x89ABCDEFu, 0xFEDCBA98u, 0x76543210u});
+    a.save(path);
+    auto b = Vector<TestType>::open(path);
+    std::remove(path);
+    CHECK(a == b);
+}
+static void save_load_mat() {                    // tests.rs:223-238
+    const char* path = "save_load_mat.tmp";
+    auto a = Matrix<TestType>::from_vec({0x01234567u, 0x89ABCDEFu, 0x13579BDFu, 0xFEDCBA98u, 0x76543210u, 0x02468ACEu}, 2, 3);
+    a.save(path);
+    auto b = Matrix<TestType>::open(path);
+    std::remove(path);
+    CHECK(a == b);
+    CHECK(panics([&] { a.save(path); auto w = Matrix<uint64_t>::open(path); }));   // matrix.rs:97-100
+    std::remove(path);
+}
 static void normalize_vec() {                    // tests.rs:240-252
     for (int size : {1, 2, 8, 16, 64, 128}) {
         std::vector<float> v; for (int x = 1; x <= size; ++x) v.push_back((float)x);
@@ -99,6 +117,8 @@ static void panics_like_the_reference() {
     CHECK(panics([&] { Matrix<TestType>::from_vec({1, 2, 3}, 2, 2); }));   // matrix.rs:40
     auto t = m.transpose();
     CHECK(t == Matrix<TestType>::from_vec({1, 4, 2, 5, 3, 6}, 3, 2));
+    auto hc = mul_host<TestType>({1, 2, 3, 4, 5, 6}, {7, 8, 9, 10, 11, 12}, 2, 3, 2);
+    CHECK((hc == std::vector<TestType>{58, 64, 139, 154}));
     auto o = mul_column_row(Vector<TestType>::from_vec({1, 2}), Vector<TestType>::from_vec({3, 4, 5}));
     CHECK(o == Matrix<TestType>::from_vec({3, 4, 5, 6, 8, 10}, 2, 3));
 }
@@ -107,7 +127,7 @@ int main() {
     try {
         check(la_init(0));
         f32_vec_mat_mul(); vec_eq(); vec_sum(); vec_vec_dot(); mat_eq(); vec_mat_mul(); mat_mat_mul(); vec_transpose_mat_mul();
-        vec_add(); vec_mul_scl(); normalize_vec(); length_vec(); vec_clone(); panics_like_the_reference();
+        vec_add(); vec_mul_scl(); save_load_vec(); save_load_mat(); normalize_vec(); length_vec(); vec_clone(); panics_like_the_reference();
     } catch (const std::exception& e) { std::printf("EXCEPTION: %s\n", e.what()); return 2; }
     std::printf(failures ? "%d checks failed\n" : "all reference tests passed (%d failures)\n", failures);
     return failures ? 1 : 0;

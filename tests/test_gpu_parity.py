@@ -409,3 +409,27 @@ def test_matmat_limb_engine_is_bit_exact(la, name):
         assert lib.la_gemm_last_engine() in (0, 1) and same(C.to_vec(), P.mul_mat_mat(a, b, 512, 1024, 512))
     finally:
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
+# ------------------------------------------------------------------ ragged large products: padded onto the fast engines
+def test_matmat_large_ragged_shapes_take_the_fast_engines_through_padding(la):
+    P = oracle.port(); lib = la._lib.lib
+    M, K, N = 517, 1031, 523                       # nothing is a multiple of 4
+    a = gen.values("f32", M * K, 80); b = gen.values("f32", K * N, 81)
+    check_f32_gemm(la, a, b, M, K, N, "padded f32")
+    assert lib.la_gemm_last_padded() == 1 and lib.la_gemm_last_engine() == 2
+    for name in ("i32", "u16", "u8"):
+        ai = gen.values(name, M * K, 82); bi = gen.values(name, K * N, 83)
+        C = la.Matrix.from_vec(ai, M, K, dt(la, name)) * la.Matrix.from_vec(bi, K, N, dt(la, name))
+        assert lib.la_gemm_last_padded() == 1 and lib.la_gemm_last_engine() == 3, name
+        assert same(C.to_vec(), P.mul_mat_mat(ai, bi, M, K, N)), name
+    # unaligned base pointers
+    a = gen.values("i32", 512 * 1024 + 1, 84); b = gen.values("i32", 1024 * 512 + 1, 85)
+    A = la.Vector.from_vec(a); B = la.Vector.from_vec(b); Cv = la.Vector.uninitialized(512 * 512 + 1, "i32")
+    la._lib.call("la_mul_mat_mat", 5, Cv.ptr + 4, A.ptr + 4, B.ptr + 4, 512, 1024, 512, None)
+    la.synchronize()
+    assert lib.la_gemm_last_padded() == 1
+    assert same(Cv.to_vec()[1:], P.mul_mat_mat(a[1:], b[1:], 512, 1024, 512))
+    # small ragged products stay on the generic kernel
+    check_f32_gemm(la, gen.values("f32", 33 * 17, 86), gen.values("f32", 17 * 29, 87), 33, 17, 29, "small ragged")
+    assert lib.la_gemm_last_padded() == 0 and lib.la_gemm_last_engine() == 0

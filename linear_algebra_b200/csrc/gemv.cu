@@ -27,7 +27,7 @@ constexpr int MV_ROWS = 4;      // rows per warp
 constexpr int MV_UNROLL = 2;    // column packets in flight per row per lane
 
 template <typename T>
-__global__ void __launch_bounds__(MV_THREADS)
+__global__ void __launch_bounds__(MV_THREADS, 4)
 matvec_rows_pack_kernel(T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ B, size_t rows, size_t cols) {
     using Acc = typename Arith<T>::Acc;
     using P = Pack<T>;

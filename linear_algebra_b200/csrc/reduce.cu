@@ -18,8 +18,9 @@
 namespace {
 
 constexpr int RED_THREADS = 256;
-constexpr int RED_UNROLL = 4;
-constexpr int RED_BLOCKS_PER_SM = 4;
+// 16-byte packets per operand in flight per thread
+template <bool DOT> struct RedUnroll { static constexpr int value = 4; };
+template <bool DOT> struct RedBlocksPerSm { static constexpr int value = DOT ? 4 : 6; };     // sum needs fewer registers: more blocks in flight
 
 template <typename T, bool DOT>
 __global__ void __launch_bounds__(RED_THREADS)
@@ -28,6 +29,7 @@ reduce_kernel(const T* __restrict__ a, const T* __restrict__ b, size_t n, bool p
     using A = typename Arith<T>::Acc;
     using P = Pack<T>;
     constexpr int N = P::N;
+    constexpr int RED_UNROLL = RedUnroll<DOT>::value;
     __shared__ A smem[32];
     __shared__ bool is_last;
 
@@ -69,6 +71,7 @@ reduce_kernel(const T* __restrict__ a, const T* __restrict__ b, size_t n, bool p
         acc[0] = DOT ? Arith<T>::fma(a[i], b[i], acc[0]) : acc[0] + Arith<T>::widen(a[i]);
 
     A v = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    if (RED_UNROLL == 8) v += (acc[RED_UNROLL - 4] + acc[RED_UNROLL - 3]) + (acc[RED_UNROLL - 2] + acc[RED_UNROLL - 1]);
     v = block_sum(v, smem);
 
     if (gridDim.x == 1) {
@@ -102,8 +105,9 @@ la_status reduce_launch(const T* a, const T* b, size_t n, T* out_dev, cudaStream
     }
     const bool packed = la_aligned16(a) && (!DOT || la_aligned16(b));
     const size_t work = packed ? (n / Pack<T>::N + 1) : n;
+    constexpr int RED_UNROLL = RedUnroll<DOT>::value;
     size_t blocks = (work + (size_t)RED_THREADS * RED_UNROLL - 1) / ((size_t)RED_THREADS * RED_UNROLL);
-    const size_t cap = (size_t)sm_count * RED_BLOCKS_PER_SM;
+    const size_t cap = (size_t)sm_count * RedBlocksPerSm<DOT>::value;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     void* scratch;

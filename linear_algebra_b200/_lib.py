@@ -95,6 +95,8 @@ lib.la_gemm_tc_set_variant.argtypes = [_I]
 lib.la_gemm_tc_set_variant.restype = ctypes.c_int
 lib.la_gemm_last_engine.argtypes = []
 lib.la_gemm_last_engine.restype = ctypes.c_int
+lib.la_transpose_set_variant.argtypes = [_I]
+lib.la_transpose_set_variant.restype = ctypes.c_int
 lib.la_gemm_last_padded.argtypes = []
 lib.la_gemm_last_padded.restype = ctypes.c_int
 

@@ -14,43 +14,47 @@ namespace {
 
 constexpr int TR_THREADS = 256;
 
-template <typename E, int TILE>
+// TROWS x TCOLS input tile (dynamic shared memory, padded rows).
+template <typename E, int TROWS, int TCOLS>
 __global__ void __launch_bounds__(TR_THREADS)
 transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x) {
     using P = Pack<E>;
     constexpr int V = P::N;               // elements per 16-byte packet
-    constexpr int VPR = TILE / V;         // packets per tile row
-    __shared__ E tile[TILE][TILE + 1];
-    const size_t r0 = (size_t)(blockIdx.x / tiles_x) * TILE, c0 = (size_t)(blockIdx.x % tiles_x) * TILE;
+    constexpr int VPR_IN = TCOLS / V;     // packets per input tile row
+    constexpr int VPR_OUT = TROWS / V;    // packets per output tile row
+    constexpr int PITCH = TCOLS + 1;
+    extern __shared__ __align__(16) uint8_t tile_raw[];
+    E* tile = reinterpret_cast<E*>(tile_raw);                  // tile[r * PITCH + c]
+    const size_t r0 = (size_t)(blockIdx.x / tiles_x) * TROWS, c0 = (size_t)(blockIdx.x % tiles_x) * TCOLS;
 
     // R % V == 0 and C % V == 0 on this path: a packet is either wholly inside or wholly outside.
-    constexpr int PER_THREAD = TILE * VPR / TR_THREADS;
-    static_assert(TILE * VPR % TR_THREADS == 0, "whole packets per thread");
-    // all global loads first (PER_THREAD independent 16-byte requests in flight per thread) ...
-    P in_p[PER_THREAD];
+    constexpr int LOADS = TROWS * VPR_IN / TR_THREADS, STORES = TCOLS * VPR_OUT / TR_THREADS;
+    static_assert(TROWS * VPR_IN % TR_THREADS == 0 && TCOLS * VPR_OUT % TR_THREADS == 0, "whole packets per thread");
+    // all global loads first (LOADS independent 16-byte requests in flight per thread) ...
+    P in_p[LOADS];
 #pragma unroll
-    for (int j = 0; j < PER_THREAD; ++j) {
+    for (int j = 0; j < LOADS; ++j) {
         const int idx = threadIdx.x + j * TR_THREADS;
-        const int r = idx / VPR, q = idx % VPR;
+        const int r = idx / VPR_IN, q = idx % VPR_IN;
         if (r0 + r < R && c0 + (size_t)q * V < C)
             in_p[j] = ld_stream(reinterpret_cast<const P*>(in + (r0 + r) * C + c0 + (size_t)q * V));
     }
     // ... then scatter them into the tile
 #pragma unroll
-    for (int j = 0; j < PER_THREAD; ++j) {
+    for (int j = 0; j < LOADS; ++j) {
         const int idx = threadIdx.x + j * TR_THREADS;
-        const int r = idx / VPR, q = idx % VPR;
+        const int r = idx / VPR_IN, q = idx % VPR_IN;
 #pragma unroll
-        for (int e = 0; e < V; ++e) tile[r][q * V + e] = in_p[j].v[e];
+        for (int e = 0; e < V; ++e) tile[r * PITCH + q * V + e] = in_p[j].v[e];
     }
     __syncthreads();
 #pragma unroll
-    for (int j = 0; j < PER_THREAD; ++j) {
+    for (int j = 0; j < STORES; ++j) {
         const int idx = threadIdx.x + j * TR_THREADS;
-        const int cc = idx / VPR, q = idx % VPR;      // output row c0+cc, output columns r0 + q*V ...
+        const int cc = idx / VPR_OUT, q = idx % VPR_OUT;      // output row c0+cc, output columns r0 + q*V ...
         P p;
 #pragma unroll
-        for (int e = 0; e < V; ++e) p.v[e] = tile[q * V + e][cc];
+        for (int e = 0; e < V; ++e) p.v[e] = tile[(q * V + e) * PITCH + cc];
         if (c0 + cc < C && r0 + (size_t)q * V < R)
             st_stream(reinterpret_cast<P*>(out + (c0 + cc) * R + r0 + (size_t)q * V), p);
     }
@@ -72,17 +76,39 @@ transpose_elem_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
         if (c0 + j < C && r0 + tx < R) out[(c0 + j) * R + r0 + tx] = tile[tx][j];
 }
 
+int g_tr_variant = 0;      // la_transpose_set_variant (tuning hook): 4-byte tile shape; measured at i32 8192^2 / 32768^2:
+                           // 64x64 6.06 / 6.51 TB/s (default), 64x32 6.26 / 6.38, 32x64 6.17 / 6.05, 128x128 4.73 / 5.11
+
+template <typename E, int TROWS, int TCOLS>
+la_status transpose_pack_launch(E* out, const E* in, size_t R, size_t C, cudaStream_t st) {
+    const size_t gx = (C + TCOLS - 1) / TCOLS, gy = (R + TROWS - 1) / TROWS;
+    // 1-D grid of tiles (row-major over the input), so neither dimension hits the 65535 limit
+    if (gx * gy > 0x7fffffffull || gx > 0xffffffffull) return la_fail(LA_ERR_UNSUPPORTED, "transpose: %zu x %zu is too large", R, C);
+    auto kern = transpose_pack_kernel<E, TROWS, TCOLS>;
+    constexpr size_t smem = (size_t)TROWS * (TCOLS + 1) * sizeof(E);
+    if (smem > 48 * 1024) LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)(gx * gy), TR_THREADS, smem, st>>>(out, in, R, C, (unsigned)gx);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
 template <typename E, int TILE>
 la_status transpose_launch(E* out, const E* in, size_t R, size_t C, cudaStream_t st) {
     constexpr int V = Pack<E>::N;
     const bool packed = la_aligned16(out) && la_aligned16(in) && R % V == 0 && C % V == 0;
-    const int tile = packed ? TILE : 32;
-    const size_t gx = (C + tile - 1) / tile, gy = (R + tile - 1) / tile;
-    // 1-D grid of tiles (row-major over the input), so neither dimension hits the 65535 limit
+    if (packed) {
+        if constexpr (sizeof(E) == 4) {
+            switch (g_tr_variant) {
+            case 1: return transpose_pack_launch<E, 32, 64>(out, in, R, C, st);
+            case 2: return transpose_pack_launch<E, 64, 32>(out, in, R, C, st);
+            default: break;
+            }
+        }
+        return transpose_pack_launch<E, TILE, TILE>(out, in, R, C, st);
+    }
+    const size_t gx = (C + 31) / 32, gy = (R + 31) / 32;
     if (gx * gy > 0x7fffffffull || gx > 0xffffffffull) return la_fail(LA_ERR_UNSUPPORTED, "transpose: %zu x %zu is too large", R, C);
-    const unsigned grid = (unsigned)(gx * gy);
-    if (packed) transpose_pack_kernel<E, TILE><<<grid, TR_THREADS, 0, st>>>(out, in, R, C, (unsigned)gx);
-    else        transpose_elem_kernel<E><<<grid, TR_THREADS, 0, st>>>(out, in, R, C, (unsigned)gx);
+    transpose_elem_kernel<E><<<(unsigned)(gx * gy), TR_THREADS, 0, st>>>(out, in, R, C, (unsigned)gx);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
@@ -93,6 +119,8 @@ la_status transpose_launch(E* out, const E* in, size_t R, size_t C, cudaStream_t
 la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st) {
     return transpose_launch<uint32_t, 64>(out, in, R, C, st);
 }
+
+extern "C" la_status la_transpose_set_variant(int v) { g_tr_variant = v; return LA_OK; }      // tuning hook
 
 extern "C" la_status la_transpose(int dtype, void* out, const void* in, size_t rows, size_t cols, void* stream) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_transpose: unknown dtype %d", dtype);

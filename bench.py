@@ -222,6 +222,52 @@ def extras(la, hbm_peak, peak_src):
     return out
 
 
+def extras_multi(la, comm, hbm_peak):
+    """BASELINE.json configs[2] on N GPUs: dot/sum over 2^28 f32 and both matrix-vector products at
+    32768^2, row-block sharded (linear_algebra_b200/dist.py).  Times include the exchange and the host
+    round trip of the scalar results; max over ranks; GB/s = whole-job algorithmic bytes / time."""
+    import torch
+    import torch.distributed as td
+    from linear_algebra_b200 import dist as ladist
+    out = {}
+    world, rank = comm.world, comm.rank
+
+    def wall(fn, iters):
+        for _ in range(3):
+            fn()
+        la.synchronize(); comm.barrier()
+        t0 = time.perf_counter()
+        for _ in range(iters):
+            fn()
+        la.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3 / iters
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        return float(t[0])
+
+    def rec(name, ms, nbytes):
+        gbs = nbytes / ms / 1e6
+        out[name] = {"ms": round(ms, 4), "GB/s": round(gbs, 1), "frac_of_measured_hbm_x_n": round(gbs / (hbm_peak * world), 3)}
+
+    n = 1 << 28
+    lo, hi = ladist.partition(n, world, rank)
+    A = ladist.ShardedVector(comm, la.Vector.synth(0x5EED0001 + rank, hi - lo, "f32"), n)
+    B = ladist.ShardedVector(comm, la.Vector.synth(0x5EED1001 + rank, hi - lo, "f32"), n)
+    rec("dot_f32_2^28_sharded", wall(lambda: ladist.dot(A, B), 20), 8 * n)
+    rec("sum_f32_2^28_sharded", wall(lambda: A.sum(), 20), 4 * n)
+    rec("add_f32_2^28_sharded", wall(lambda: A + B, 20), 12 * n)
+    del A, B
+    r = 32768
+    rlo, rhi = ladist.partition(r, world, rank)
+    M = ladist.ShardedMatrix(comm, la.Matrix(la.Vector.synth(0x5EED0002 + rank, (rhi - rlo) * r, "f32"), rhi - rlo, r), r)
+    v = la.Vector.synth(0x5EED1002, r, "f32")
+    sv = ladist.ShardedVector(comm, la.Vector.synth(0x5EED2002 + rank, rhi - rlo, "f32"), r)
+    rec("mat_x_vec_f32_32768^2_sharded", wall(lambda: ladist.mul_transpose_mat(v, M), 10), 4 * (r * r + 2 * r))
+    rec("vec_x_mat_f32_32768^2_sharded", wall(lambda: sv * M, 10), 4 * (r * r + 2 * r))
+    out["_note"] = "exchange: all_gather over NVLink + rank-ordered combination (deterministic); scalar results return to the host"
+    return out
+
+
 def ncu_traffic(path, kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of `kernel` per launch, from the committed ncu summary."""
     try:
@@ -379,6 +425,11 @@ def run_ours(args):
             cb = time_reference_gemm(12.0)
             cb.pop("seconds", None)
             line["cpu_baseline"] = cb
+    if world > 1 and not args.no_extra:
+        em = extras_multi(la, comm, hbm_peak)
+        if rank == 0:
+            line["extra"] = em
+    if rank == 0:
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()

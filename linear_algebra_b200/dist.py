@@ -132,6 +132,8 @@ class ShardedVector:
 
     # one exchange: a single element per rank, combined in rank order
     def sum(self):
+        if self.comm.backend == "nccl":
+            return _device_scalar_exchange(self, None)
         part = self.local.sum()
         return combine_scalars(self.comm.all_gather_host(np.asarray(part).tobytes()), self.local.dtype.np)
 
@@ -163,8 +165,28 @@ def _pad(b, n):
     return b + b"\x00" * (n - len(b))
 
 
+def _device_scalar_exchange(a, b):
+    """NCCL path of sum (b is None) / dot: the local partial stays on the device (la_*_dev writes it into
+    this rank's 8-byte slot of a small gather buffer), one in-place all_gather over NVLink, one download
+    of `world` slots, rank-ordered combination on the host."""
+    m, comm, dt = a._mod(), a.comm, a.local.dtype
+    slots = getattr(comm, "_scalar_slots", None)
+    if slots is None:
+        slots = comm._scalar_slots = m.Vector.uninitialized(8 * comm.world, "u8")
+    mine = slots.ptr + 8 * comm.rank
+    if b is None:
+        m._lib.call("la_sum_vec_dev", dt.code, a.local.ptr, a.local.len(), mine, None)
+    else:
+        m._lib.call("la_dot_vec_vec_dev", dt.code, a.local.ptr, b.local.ptr, a.local.len(), mine, None)
+    comm.all_gather_device(slots.ptr, mine, 8)           # in place; ordered after the kernel on the default stream
+    raw = slots.to_vec().tobytes()
+    return combine_scalars([raw[8 * r:8 * r + dt.size] for r in range(comm.world)], dt.np)
+
+
 def dot(a, b):
     a._co(b)
+    if a.comm.backend == "nccl":
+        return _device_scalar_exchange(a, b)
     part = a._mod().dot(a.local, b.local)
     return combine_scalars(a.comm.all_gather_host(np.asarray(part).tobytes()), a.local.dtype.np)
 

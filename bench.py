@@ -217,6 +217,13 @@ def extras(la, hbm_peak, peak_src):
         sweep[str(nn)] = row
         del P, Q, R
     out["gemm_f32_sweep"] = sweep
+    # the reference's own OpenCL kernels on this very GPU (separate process: its OpenCL context stays apart from ours)
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "cl_bench.py")], capture_output=True, text=True, timeout=240)
+        js = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        out["reference_opencl_on_this_gpu"] = json.loads(js[-1]) if js else {"unavailable": (r.stderr or "no output")[-300:]}
+    except Exception as e:  # noqa: BLE001
+        out["reference_opencl_on_this_gpu"] = {"unavailable": str(e)[:300]}
     out["_hbm_peak_GB/s"] = hbm_peak
     out["_hbm_peak_source"] = peak_src
     return out

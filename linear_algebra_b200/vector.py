@@ -128,6 +128,13 @@ class Vector:
         call("la_download", out.ctypes.data, self._ptr, out.nbytes, _STREAM)
         return out
 
+    def slice_to_vec(self, start, count):
+        """Download elements [start, start+count) only (spot checks of operands too big to bring back whole)."""
+        assert 0 <= start and start + count <= self._len
+        out = np.empty(count, dtype=self.dtype.np)
+        call("la_download", out.ctypes.data, self._ptr + start * self.dtype.size, out.nbytes, _STREAM)
+        return out
+
     def len(self):
         return self._len
 

@@ -52,6 +52,28 @@ def build(reference: str, contract: str = "off", out_name: str = "libref_kernels
     return out
 
 
+def build_cl_source(reference: str) -> str:
+    """oracle/_ref/libref_clsrc.so: the OpenCL program text exactly as lib.rs:337-354 `get_src` assembles it for
+    the default TYPES (lib.rs:84-92), embedded in a binary as one C string (ref_cl_source()).  Used by
+    oracle/cl_ref.py to run the reference's UNMODIFIED kernels through a real OpenCL driver where one exists
+    (the GPU box ships NVIDIA's).  No reference text is written to the repository, only this binary."""
+    path = os.path.join(reference, "src", "kernels.cl")
+    with open(path, "r") as f:
+        kernels_cl = f.read()
+    text = []
+    for ty in TYPES[:9]:                       # the reference's default list: no "double"
+        text.append(("#define IS_%s\n" % ty.upper() + kernels_cl + "\n").replace("{T}", ty))
+        text.append("\n#undef IS_%s\n" % ty.upper())
+    src = "".join(text).encode()
+    c = "static const unsigned char text[] = {" + ",".join(str(b) for b in src) + ",0};\n" \
+        "const char* ref_cl_source(void) { return (const char*)text; }\n"
+    out_dir = os.path.join(HERE, "_ref")
+    os.makedirs(out_dir, exist_ok=True)
+    out = os.path.join(out_dir, "libref_clsrc.so")
+    subprocess.run(["gcc", "-x", "c", "-O1", "-fPIC", "-shared", "-o", out, "-"], input=c.encode(), check=True)
+    return out
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--reference", default="/root/reference")
@@ -62,3 +84,4 @@ if __name__ == "__main__":
         sys.exit(0)
     print(build(args.reference, "off"))
     print(build(args.reference, "fast", "libref_kernels_fma.so"))
+    print(build_cl_source(args.reference))

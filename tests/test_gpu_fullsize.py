@@ -111,3 +111,53 @@ def test_matvec_32768(la):                     # configs[2], one GPU
         col = M2[:, c].astype(np.float64)
         truth = float(col @ v.astype(np.float64)); scale = float(np.abs(col) @ np.abs(v).astype(np.float64))
         assert abs(float(z[c]) - truth) <= 2.0 ** -20 * scale
+
+
+def test_more_than_2_pow_32_elements(la):
+    """Sizes the reference cannot even express (it passes counts as i32, vector.rs:277): 2^32 + 7 one-byte
+    elements.  Operands are generated on the device (la_synth) and spot-checked against the host mirror of
+    the generator, so nothing of that size crosses PCIe.  Exercises 64-bit indexing, the ragged tail and
+    the wrap-around identities of sum/dot."""
+    from linear_algebra_b200 import synth
+    n = (1 << 32) + 7
+    A = la.Vector.synth(0xA, n, "u8"); B = la.Vector.synth(0xB, n, "u8")
+    C = A + B
+    D = A * B
+    spots = [0, (1 << 31) - 64, (1 << 31), (1 << 32) - 64, n - 128]
+    for s in spots:
+        a = synth.values("u8", 0xA, s, 128 if s + 128 <= n else n - s); b = synth.values("u8", 0xB, s, a.size)
+        assert A.slice_to_vec(s, a.size).tobytes() == a.tobytes()
+        with np.errstate(over="ignore"):
+            assert C.slice_to_vec(s, a.size).tobytes() == (a + b).astype(np.uint8).tobytes()
+            assert D.slice_to_vec(s, a.size).tobytes() == (a * b).astype(np.uint8).tobytes()
+    # reductions: exact mod 2^8 whatever the order -> checksum identities across independent kernels
+    sa, sb = int(A.sum()), int(B.sum())
+    assert int(C.sum()) == (sa + sb) & 0xFF
+    assert int(D.sum()) == int(la.dot(A, B))
+    # and one independent anchor: the sum of a 2^24-element slice against the host mirror
+    m = 1 << 24
+    part = la.Vector(A.dtype, A.ptr + ((1 << 32) - m + 7), m, owner=False)       # the last 2^24 elements, unaligned start
+    assert int(part.sum()) == int(synth.values("u8", 0xA, (1 << 32) - m + 7, m).sum(dtype=np.uint64) & 0xFF)
+    assert A == A and not (A == B)
+    del C, D
+    # transpose of a 65536 x 65543 byte matrix (> 2^32 elements, ragged columns -> element kernel)
+    R, Cc = 65536, 65543
+    X = la.Matrix(la.Vector.synth(0xC, R * Cc, "u8"), R, Cc)
+    T = X.transpose()
+    for r, c in ((0, 0), (65535, 65542), (40000, 123), (7, 65000)):
+        assert T.data.slice_to_vec(c * R + r, 1)[0] == synth.values("u8", 0xC, r * Cc + c, 1)[0]
+
+
+def test_empty_operands(la):
+    """Zero-length vectors and matrices are legal in the reference (Vector::from_vec(vec![]))."""
+    for name in ("u8", "i32", "f32", "f64"):
+        e = la.Vector.from_vec([], name)
+        assert (e + e).len() == 0 and (e * 3).len() == 0 and e.sum() == 0 and la.dot(e, e) == 0 and e == e
+        e += e
+        m0 = la.Matrix.from_vec([], 0, 5, name); m1 = la.Matrix.from_vec([], 5, 0, name)
+        assert (m0 * la.Matrix.from_vec(np.zeros(15, la.parameter(name).np), 5, 3, name)).len() == (0, 3)
+        z = (m1 * m0)                                  # 5x0 times 0x5 = 5x5 of zeros
+        assert z.len() == (5, 5) and not z.to_vec().any()
+        assert m0.transpose().len() == (5, 0)
+        assert (la.Vector.from_vec([], name) * m0).to_vec().tolist() == [0] * 5      # v(0) x M(0x5) = zeros(5)
+        assert la.mul_transpose_mat(la.Vector.from_vec([], name), m1).to_vec().tolist() == [0] * 5

@@ -271,7 +271,7 @@ def extras_multi(la, comm, hbm_peak):
     sv = ladist.ShardedVector(comm, la.Vector.synth(0x5EED2002 + rank, rhi - rlo, "f32"), r)
     rec("mat_x_vec_f32_32768^2_sharded", wall(lambda: ladist.mul_transpose_mat(v, M), 10), 4 * (r * r + 2 * r))
     rec("vec_x_mat_f32_32768^2_sharded", wall(lambda: sv * M, 10), 4 * (r * r + 2 * r))
-    out["_note"] = "exchange: all_gather over NVLink + rank-ordered combination (deterministic); scalar results return to the host"
+    out["_note"] = "exchange fused into the kernels: partials stored into / read from the peers' cudaIpc-mapped buffers over NVLink, rank-ordered (deterministic); scalar results return to the host"
     return out
 
 

@@ -139,6 +139,28 @@ la_status la_dot_vec_vec(int dtype, const void* a, const void* b, size_t n, void
 la_status la_sum_vec_dev(int dtype, const void* data, size_t n, void* out_dev, void* stream);
 la_status la_dot_vec_vec_dev(int dtype, const void* a, const void* b, size_t n, void* out_dev, void* stream);
 
+/* ------------------------------------------------------------------ multi-GPU reductions (no counterpart in
+ * the single-device reference).  One process per GPU.  sum / dot over all ranks in ONE
+ * launch per rank: the reduction kernel stores its partial into every peer's mailbox over NVLink peer memory and
+ * adds the `world` partials in rank order (deterministic, same bits on every rank), instead of a separate
+ * collective.  Set-up: every rank creates a mailbox, the 64-byte handles are exchanged by any means (the Python
+ * mirror uses torch.distributed), every rank opens the peers' handles.  `peer_mailboxes[p]` is rank p's mailbox
+ * as mapped in this process (the own one at [rank]); `seq` = 1, 2, 3, ... must advance identically on all ranks.
+ * world <= 16.  A rank that never shows up makes the others trap after a bounded wait. */
+size_t la_p2p_mailbox_bytes(void);
+size_t la_p2p_handle_bytes(void);
+la_status la_p2p_buffer_create(size_t bytes, void** dev, void* ipc_handle_out);    /* exportable, zeroed; a mailbox is one of la_p2p_mailbox_bytes() */
+la_status la_p2p_buffer_open(const void* ipc_handle, void** peer_dev);
+la_status la_p2p_buffer_close(void* peer_dev);
+la_status la_p2p_buffer_destroy(void* dev);
+la_status la_sum_vec_allreduce(int dtype, const void* data, size_t n, void* out_dev, void* const* peer_mailboxes, int world, int rank, uint64_t seq, void* stream);
+la_status la_dot_vec_vec_allreduce(int dtype, const void* a, const void* b, size_t n, void* out_dev, void* const* peer_mailboxes, int world, int rank, uint64_t seq, void* stream);
+/* out[c] = sum over ranks (ascending) of each rank's n-element vector, read from the peers' exported buffers over
+ * NVLink in one launch per rank (used after la_mul_vec_mat on row-sharded operands).  Rank r's contribution must
+ * already be at byte offset (seq & 1) * half_bytes of ITS buffer, written by earlier work on `stream`. */
+la_status la_vec_allreduce(int dtype, void* out_dev, size_t n, void* const* peer_vectors, size_t half_bytes, void* const* peer_mailboxes,
+                           int world, int rank, uint64_t seq, void* stream);
+
 /* ------------------------------------------------------------------ matrix x vector
  * {T}_mul_vec_mat src/kernels.cl:143-147, host `&Vector * &Matrix` src/vector.rs:508-539:
  *   C[col] = sum_j A[j] * B[j*cols + col],  A has `rows` elements, C has `cols`.

@@ -67,6 +67,13 @@ SIGNATURES = {
     "la_dot_vec_vec": [_I, _V, _V, _Z, _V, _V],
     "la_sum_vec_dev": [_I, _V, _Z, _V, _V],
     "la_dot_vec_vec_dev": [_I, _V, _V, _Z, _V, _V],
+    "la_p2p_buffer_create": [_Z, _PV, _V],
+    "la_p2p_buffer_open": [_V, _PV],
+    "la_p2p_buffer_close": [_V],
+    "la_p2p_buffer_destroy": [_V],
+    "la_vec_allreduce": [_I, _V, _Z, _PV, _Z, _PV, _I, _I, ctypes.c_uint64, _V],
+    "la_sum_vec_allreduce": [_I, _V, _Z, _V, _PV, _I, _I, ctypes.c_uint64, _V],
+    "la_dot_vec_vec_allreduce": [_I, _V, _V, _Z, _V, _PV, _I, _I, ctypes.c_uint64, _V],
     "la_mul_vec_mat": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_vec_transpose_mat": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_vec_mat_noalloc": [_I, _V, _V, _V, _Z, _Z, _V],
@@ -76,7 +83,8 @@ SIGNATURES = {
     "la_get_gemm_mode": [_PI],
     "la_transpose": [_I, _V, _V, _Z, _Z, _V],
 }
-NON_STATUS = {"la_last_error": ctypes.c_char_p, "la_version": ctypes.c_char_p, "la_dtype_size": ctypes.c_size_t}
+NON_STATUS = {"la_last_error": ctypes.c_char_p, "la_version": ctypes.c_char_p, "la_dtype_size": ctypes.c_size_t,
+              "la_p2p_mailbox_bytes": ctypes.c_size_t, "la_p2p_handle_bytes": ctypes.c_size_t}
 
 for _name, _args in SIGNATURES.items():
     _f = getattr(lib, _name)
@@ -86,6 +94,10 @@ lib.la_last_error.argtypes = []
 lib.la_last_error.restype = ctypes.c_char_p
 lib.la_version.argtypes = []
 lib.la_version.restype = ctypes.c_char_p
+lib.la_p2p_mailbox_bytes.argtypes = []
+lib.la_p2p_mailbox_bytes.restype = ctypes.c_size_t
+lib.la_p2p_handle_bytes.argtypes = []
+lib.la_p2p_handle_bytes.restype = ctypes.c_size_t
 lib.la_dtype_size.argtypes = [_I]
 lib.la_dtype_size.restype = ctypes.c_size_t
 # tuning hook (not declared in the public header)

@@ -8,10 +8,13 @@ need no NCCL support for the element type (NCCL has no 16-bit integers).
 
   op                         partition                              exchange
   elementwise / scale        co-sharded ranges                      none
-  sum / dot / ==             local partial (la_*_dev)               all_gather of one element
+  sum / dot                  fused: the reduction kernel stores its partial into every peer's mailbox over NVLink
+                             peer memory and adds the partials in rank order (la_*_allreduce, one launch per rank);
+                             fallback / == : local partial + all_gather of one element
   M x v (mul_transpose_mat)  M by rows, v replicated -> rows shard  none
-  v x M                      v and M by rows -> full-length partial all_gather of `cols` elements,
-                                                                    rank-ordered adds (la_ew_assign_vec_vec)
+  v x M                      v and M by rows -> full-length partial fused: partial into an exported buffer, one kernel
+                                                                    adds the peers' partials over NVLink in rank order
+                                                                    (la_vec_allreduce); fallback: all_gather + adds
   M x M                      A, C by rows, B replicated             none
   M x M on host buffers      A, C by rows; every rank uploads 1/world all_gather of B over NVLink (mul_host)
                              of B over its own PCIe link
@@ -68,6 +71,41 @@ class Comm:
 
     def barrier(self):
         self.dist.barrier(group=self.group)
+
+    # ---- NVLink peer-memory mailboxes for the fused reductions (la_*_allreduce)
+    def p2p(self, m):
+        """Lazily: create this rank's mailbox, exchange the IPC handles, map the peers' mailboxes.  Returns
+        (ctypes array of `world` device pointers, next sequence number) or None when unavailable."""
+        import ctypes
+        st = getattr(self, "_p2p", None)
+        if st is None:
+            st = self._p2p = {"ok": False, "seq": 0}
+            if self.backend == "nccl" and self.world <= 16:
+                try:
+                    hb = m._lib.lib.la_p2p_handle_bytes()
+
+                    def exported(nbytes):
+                        mine = ctypes.c_void_p(); handle = ctypes.create_string_buffer(hb)
+                        m._lib.call("la_p2p_buffer_create", nbytes, ctypes.byref(mine), handle)
+                        ptrs = (ctypes.c_void_p * self.world)()
+                        for r, h in enumerate(self.all_gather_host(handle.raw)):
+                            if r == self.rank:
+                                ptrs[r] = mine.value
+                            else:
+                                p = ctypes.c_void_p()
+                                m._lib.call("la_p2p_buffer_open", ctypes.create_string_buffer(h, hb), ctypes.byref(p))
+                                ptrs[r] = p.value
+                        return ptrs
+                    st.update(ok=True, ptrs=exported(m._lib.lib.la_p2p_mailbox_bytes()), vec_half=4 << 20,
+                              vecs=exported(2 * (4 << 20)), out=m.Vector.uninitialized(8, "u8"))
+                except Exception as e:  # noqa: BLE001  (no peer access, IPC refused, ...): keep the NCCL path
+                    st["error"] = str(e)
+                flags = self.all_gather_host(b"\x01" if st["ok"] else b"\x00")       # all ranks or none
+                st["ok"] = all(f == b"\x01" for f in flags)
+        if not st["ok"]:
+            return None
+        st["seq"] += 1
+        return st["ptrs"], st["seq"], st["out"]
 
 
 def combine_scalars(parts, np_dtype):
@@ -170,6 +208,15 @@ def _device_scalar_exchange(a, b):
     this rank's 8-byte slot of a small gather buffer), one in-place all_gather over NVLink, one download
     of `world` slots, rank-ordered combination on the host."""
     m, comm, dt = a._mod(), a.comm, a.local.dtype
+    fused = comm.p2p(m)
+    if fused is not None:
+        # ONE launch per rank: reduce, store the partial into every peer's mailbox over NVLink, add in rank order
+        ptrs, seq, out = fused
+        if b is None:
+            m._lib.call("la_sum_vec_allreduce", dt.code, a.local.ptr, a.local.len(), out.ptr, ptrs, comm.world, comm.rank, seq, None)
+        else:
+            m._lib.call("la_dot_vec_vec_allreduce", dt.code, a.local.ptr, b.local.ptr, a.local.len(), out.ptr, ptrs, comm.world, comm.rank, seq, None)
+        return np.frombuffer(out.to_vec().tobytes()[:dt.size], dtype=dt.np, count=1)[0]
     slots = getattr(comm, "_scalar_slots", None)
     if slots is None:
         slots = comm._scalar_slots = m.Vector.uninitialized(8 * comm.world, "u8")
@@ -313,9 +360,22 @@ def _sharded_vec_mat(sv, sm):
     assert sv.global_len == sm.global_rows, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (sv.global_len, sm.global_rows)
     m = sm._mod()
     comm = sv.comm
-    partial = sv.local * sm.local                  # la_mul_vec_mat on the local rows
     if comm.world == 1:
-        return partial
+        return sv.local * sm.local
+    fused = comm.p2p(m) if comm.backend == "nccl" else None
+    dtp = sv.local.dtype
+    if fused is not None and sm.col_count * dtp.size <= comm._p2p["vec_half"]:
+        # local partial straight into this rank's exported buffer, then ONE kernel reads every peer's partial over
+        # NVLink and adds them in rank order
+        ptrs, seq, _ = fused
+        st = comm._p2p
+        mine = st["vecs"][comm.rank] + (seq & 1) * st["vec_half"]
+        m._lib.call("la_mul_vec_mat", dtp.code, mine, sv.local.ptr, sm.local.data.ptr, sm.local.get_row_count(), sm.col_count, None)
+        out = m.Vector.uninitialized(sm.col_count, dtp)
+        m._lib.call("la_vec_allreduce", dtp.code, out.ptr, sm.col_count, st["vecs"], st["vec_half"], ptrs, comm.world, comm.rank, seq, None)
+        m.synchronize()
+        return out
+    partial = sv.local * sm.local                  # la_mul_vec_mat on the local rows
     if comm.backend == "nccl":
         dt = partial.dtype
         nbytes = partial.len() * dt.size

@@ -23,15 +23,16 @@ namespace {
 
 // ------------------------------------------------------------------ M x v  (row dots)
 constexpr int MV_THREADS = 256;
-constexpr int MV_ROWS = 4;      // rows per warp
-constexpr int MV_UNROLL = 2;    // column packets in flight per row per lane
+constexpr int MV_LOADS = 8;     // 16-byte matrix packets in flight per lane (MV_ROWS x MV_UNROLL)
 
-template <typename T>
+// MV_ROWS rows per warp (4 for tall matrices; 2 or 1 when there are too few rows to fill the SMs otherwise)
+template <typename T, int MV_ROWS>
 __global__ void __launch_bounds__(MV_THREADS, 4)
 matvec_rows_pack_kernel(T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ B, size_t rows, size_t cols) {
     using Acc = typename Arith<T>::Acc;
     using P = Pack<T>;
     constexpr int N = P::N;
+    constexpr int MV_UNROLL = MV_LOADS / MV_ROWS;    // column packets in flight per row per lane
     const int lane = threadIdx.x & 31;
     const size_t warp = ((size_t)blockIdx.x * MV_THREADS + threadIdx.x) >> 5;
     const size_t r0 = warp * MV_ROWS;
@@ -92,6 +93,39 @@ matvec_rows_block_kernel(T* __restrict__ C, const T* __restrict__ A, const T* __
         for (size_t j = threadIdx.x; j < cols; j += MV_THREADS) acc = Arith<T>::fma(A[j], row[j], acc);
         acc = block_sum(acc, smem);
         if (threadIdx.x == 0) C[r] = Arith<T>::from_acc(acc);
+    }
+}
+
+// One block per row, 16-byte packets (aligned rows): matrices with few, long rows.
+template <typename T>
+__global__ void __launch_bounds__(MV_THREADS)
+matvec_rows_block_pack_kernel(T* __restrict__ C, const T* __restrict__ A, const T* __restrict__ B, size_t rows, size_t cols) {
+    using Acc = typename Arith<T>::Acc;
+    using P = Pack<T>;
+    constexpr int N = P::N;
+    __shared__ Acc smem[32];
+    const size_t n_pack = cols / N;
+    const P* vp = reinterpret_cast<const P*>(A);
+    for (size_t r = blockIdx.x; r < rows; r += gridDim.x) {
+        const P* bp = reinterpret_cast<const P*>(B + r * cols);
+        Acc acc[4] = {Acc(0), Acc(0), Acc(0), Acc(0)};
+        size_t p = threadIdx.x;
+        for (; p + 3 * MV_THREADS < n_pack; p += 4 * MV_THREADS) {
+            P v[4], m[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { m[u] = ld_stream(bp + p + u * MV_THREADS); v[u] = ld_cached(vp + p + u * MV_THREADS); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int e = 0; e < N; ++e) acc[u] = Arith<T>::fma(v[u].v[e], m[u].v[e], acc[u]);
+        }
+        for (; p < n_pack; p += MV_THREADS) {
+            P v = ld_cached(vp + p), m = ld_stream(bp + p);
+#pragma unroll
+            for (int e = 0; e < N; ++e) acc[0] = Arith<T>::fma(v.v[e], m.v[e], acc[0]);
+        }
+        Acc s = block_sum((acc[0] + acc[1]) + (acc[2] + acc[3]), smem);
+        if (threadIdx.x == 0) C[r] = Arith<T>::from_acc(s);
     }
 }
 
@@ -173,20 +207,28 @@ vecmat_finish_kernel(T* __restrict__ C, const typename Arith<T>::Acc* __restrict
     C[c] = Arith<T>::from_acc(acc);
 }
 
+template <typename T, int MV_ROWS>
+la_status matvec_rows_launch(T* C, const T* A, const T* B, size_t rows, size_t cols, cudaStream_t st) {
+    const size_t warps = (rows + MV_ROWS - 1) / MV_ROWS;
+    const size_t blocks = (warps + MV_THREADS / 32 - 1) / (MV_THREADS / 32);
+    if (blocks > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "mul_vec_transpose_mat: too many rows");
+    matvec_rows_pack_kernel<T, MV_ROWS><<<(unsigned)blocks, MV_THREADS, 0, st>>>(C, A, B, rows, cols);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
 template <typename T>
 la_status matvec_rows(T* C, const T* A, const T* B, size_t rows, size_t cols, cudaStream_t st, int sm) {
     const bool packed = la_aligned16(A) && la_aligned16(B) && (cols % Pack<T>::N == 0) && cols >= 32 * Pack<T>::N;
-    const size_t warps_needed = (rows + MV_ROWS - 1) / MV_ROWS;
-    if (packed && warps_needed >= (size_t)sm * 8) {
-        const size_t blocks = (warps_needed + MV_THREADS / 32 - 1) / (MV_THREADS / 32);
-        if (blocks > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "mul_vec_transpose_mat: too many rows");
-        matvec_rows_pack_kernel<T><<<(unsigned)blocks, MV_THREADS, 0, st>>>(C, A, B, rows, cols);
-    } else {
-        size_t blocks = rows;
-        const size_t cap = (size_t)sm * 16;
-        if (blocks > cap) blocks = cap;
-        matvec_rows_block_kernel<T><<<(unsigned)blocks, MV_THREADS, 0, st>>>(C, A, B, rows, cols);
-    }
+    const size_t fill = (size_t)sm * 16;                        // warps that keep every SM busy
+    if (packed && rows / 4 >= fill) return matvec_rows_launch<T, 4>(C, A, B, rows, cols, st);
+    if (packed && rows / 2 >= fill) return matvec_rows_launch<T, 2>(C, A, B, rows, cols, st);
+    if (packed && rows >= fill)     return matvec_rows_launch<T, 1>(C, A, B, rows, cols, st);
+    size_t blocks = rows;
+    const size_t cap = (size_t)sm * 16;
+    if (blocks > cap) blocks = cap;
+    if (packed) matvec_rows_block_pack_kernel<T><<<(unsigned)blocks, MV_THREADS, 0, st>>>(C, A, B, rows, cols);
+    else        matvec_rows_block_kernel<T><<<(unsigned)blocks, MV_THREADS, 0, st>>>(C, A, B, rows, cols);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }

@@ -40,3 +40,7 @@ for name, fn in (("M*v", lambda: lib.call("la_mul_vec_transpose_mat", 8, y.ptr, 
                  ("v*M", lambda: lib.call("la_mul_vec_mat", 8, y.ptr, v.ptr, M.ptr, r, r, None))):
     ms = timed(fn, 10, 2)
     print("%-8s %.4f ms  %.0f GB/s" % (name, ms, 4 * (r * r + 2 * r) / ms / 1e6), flush=True)
+for rr in (4096, 8192, 1024, 256):
+    Ms = la.Vector(M.dtype, M.ptr, rr * r, owner=False)
+    ms = timed(lambda: lib.call("la_mul_vec_transpose_mat", 8, y.ptr, v.ptr, Ms.ptr, rr, r, None), 10, 2)
+    print("M*v %dx%d  %.4f ms  %.0f GB/s" % (rr, r, ms, 4 * (rr * r + rr + r) / ms / 1e6), flush=True)

@@ -196,8 +196,8 @@ def extras(la, hbm_peak, peak_src):
                               "roofline": {"bound": "tensor", "achieved": round(10 * tops, 1), "peak": round(int8_peak, 1), "unit": "Top/s",
                                            "frac": round(10 * tops / int8_peak, 3), "note": "achieved = int8 MMA work issued (10 per product, pre-pass in the time); peak = 2 x measured bf16"}}
     del X, Y, Z
-    # f32 GEMM sweep (BASELINE.json configs[3]) on both engines; the tensor-core engine is opt-in
-    # (LA_GEMM_3XTF32: tf32 hi/lo split, 3 tcgen05 MMAs per product, FP32 accumulate, same f32 bar)
+    # f32 GEMM sweep (BASELINE.json configs[3]) on both engines (LA_GEMM_SIMT: FP32 FMA pipe; LA_GEMM_3XTF32: tf32
+    # hi/lo split, 3 tcgen05 MMAs per product, chunked FP32 accumulation, same f32 bar; LA_GEMM_AUTO picks the latter)
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
     tf32_peak = peaks.get("bf16_tflops", 1590.0) / 2.0          # tf32 runs at half the bf16 rate
     sweep = {}

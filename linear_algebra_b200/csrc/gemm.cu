@@ -4,20 +4,25 @@
 // (src/kernels.cl:134-140), launched by mul_helper (src/matrix.rs:240-265).  The reference
 // runs one work-item per C element with two global loads per multiply-add and no reuse.
 //
-// Two engines here:
-//  * gemm_tma_kernel  (4-byte element types, M % 4 == 0, N % 4 == 0, 16-byte aligned bases):
-//      TMA-fed, shared-memory-staged, register-tiled SIMT kernel.  A dedicated producer warp
-//      issues cp.async.bulk.tensor.2d loads of a [BK x BM] slab of A^T and a [BK x BN] slab of
-//      B into a STAGES-deep ring guarded by full/empty mbarriers; 8 consumer warps read both
-//      operands k-major with conflict-free LDS.128 and keep a TM x TN accumulator tile per
-//      thread.  f32 uses the sm_100 packed FFMA2 (two FMAs per issued instruction); integers
-//      use IMAD and wrap.  Each C element is accumulated k-ascending with one fused
-//      multiply-add per k -- the reference's order (kernels.cl:136-138) with contraction.
-//      A^T is produced once per call by the transpose kernel into scratch (8 B/element of A,
-//      <1% of the GEMM time at 8192^2), so both operand fragments are contiguous in k-major
-//      shared memory; edge tiles rely on TMA's out-of-bounds zero fill.
-//  * gemm_generic_kernel (every dtype, any shape / alignment): 64x64x16 shared-memory tiling
-//      with guarded scalar loads.  8/16-bit integers accumulate in 32 bits and truncate.
+// la_mul_mat_mat dispatches over five engines (la_mul_mat_mat_impl at the bottom of this file):
+//  * gemm_tc.cu    3xTF32 tcgen05 tensor-core engine: f32, >= 512^3 multiply-adds, operands in range (LA_GEMM_AUTO)
+//  * gemm_limb.cu  exact byte-limb products on the INT8 tensor cores: 8/16/32-bit integers, >= 512^3 multiply-adds
+//  * gemm_tma_kernel  (below; 4-byte element types, M % 4 == 0, N % 4 == 0, 16-byte aligned bases; what
+//      LA_GEMM_SIMT forces, and what mid-sized or out-of-range f32 products get):
+//      TMA-fed, shared-memory-staged, register-tiled SIMT kernel.  A dedicated producer warpgroup issues
+//      cp.async.bulk.tensor.2d loads of a [BK x BM] slab of A^T and a [BK x BN] slab of B into a
+//      STAGES-deep ring guarded by full/empty mbarriers; 8 consumer warps (setmaxnreg 240) read both
+//      operands k-major with conflict-free LDS.128, fragments double-buffered one k-step ahead across
+//      slab boundaries, and keep a TM x TN accumulator tile per thread.  f32 uses the sm_100 packed FFMA2
+//      (two FMAs per issued instruction, scalar-broadcast operand form); integers use IMAD and wrap.  Each
+//      C element is accumulated k-ascending with one fused multiply-add per k -- the reference's order
+//      (kernels.cl:136-138) with contraction.  A^T is produced once per call by the transpose kernel into
+//      scratch (8 B/element of A, <1% of the GEMM time at 8192^2); edge tiles rely on TMA's out-of-bounds
+//      zero fill.
+//  * zero-padding path: large products with ragged sizes / unaligned bases are copied into padded, aligned
+//      temporaries and run on the engines above.
+//  * gemm_generic_kernel (every dtype, any shape / alignment; small or 64-bit problems): 64x64x16
+//      shared-memory tiling with guarded scalar loads.  8/16-bit integers accumulate in 32 bits and truncate.
 //
 // Roofline: FP32 FMA pipe (f32), integer multiply-add pipe (i32/u32).  Work: 2*M*N*K flop.
 #include "common.cuh"

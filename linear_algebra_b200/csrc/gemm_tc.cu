@@ -1,11 +1,11 @@
-// csrc/gemm_tc.cu -- optional 3xTF32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32).
+// csrc/gemm_tc.cu -- 3xTF32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32; what LA_GEMM_AUTO picks for large products).
 //
 // Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other
 // arithmetic: every f32 operand is split x = hi + lo with hi = tf32(x) (round to nearest) and
 // lo = tf32(x - hi), and each product is formed as hi*hi + hi*lo + lo*hi on the 5th-generation
 // tensor cores (tcgen05.mma kind::tf32) with FP32 accumulation in tensor memory.  The dropped
 // lo*lo term is below 2^-22 relative, so results stay inside the f32 bar of DESIGN.md section 4;
-// the mode is opt-in (la_set_gemm_mode) and tests/test_gpu_parity.py gates it on that bar.
+// tests/test_gpu_parity.py gates the engine on that bar; la_set_gemm_mode(LA_GEMM_SIMT) switches it off.
 //
 // Kernels in this file (la_gemm_tc_set_variant picks one; 0 is the default):
 //   0  gemm_3xtf32_2cta_kernel      CTA pairs (tcgen05 cta_group::2), 256x256 tile per pair, 3-stage

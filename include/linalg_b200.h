@@ -139,6 +139,11 @@ la_status la_dot_vec_vec(int dtype, const void* a, const void* b, size_t n, void
 la_status la_sum_vec_dev(int dtype, const void* data, size_t n, void* out_dev, void* stream);
 la_status la_dot_vec_vec_dev(int dtype, const void* a, const void* b, size_t n, void* out_dev, void* stream);
 
+/* normalize / normalized (src/vector.rs:313-323) as one stream-ordered call: dot(A, A), sqrt, 1 / length, scale,
+ * without the reference's host round trip for the length.  C == A normalises in place.  f32 / f64 only (`Real`,
+ * src/traits.rs:76-78).  Bit-identical to length() followed by `* (1 / length)`. */
+la_status la_normalize_vec(int dtype, void* C, const void* A, size_t n, void* stream);
+
 /* ------------------------------------------------------------------ multi-GPU reductions (no counterpart in
  * the single-device reference).  One process per GPU.  sum / dot over all ranks in ONE
  * launch per rank: the reduction kernel stores its partial into every peer's mailbox over NVLink peer memory and

@@ -67,6 +67,7 @@ SIGNATURES = {
     "la_dot_vec_vec": [_I, _V, _V, _Z, _V, _V],
     "la_sum_vec_dev": [_I, _V, _Z, _V, _V],
     "la_dot_vec_vec_dev": [_I, _V, _V, _Z, _V, _V],
+    "la_normalize_vec": [_I, _V, _V, _Z, _V],
     "la_p2p_buffer_create": [_Z, _PV, _V],
     "la_p2p_buffer_open": [_V, _PV],
     "la_p2p_buffer_close": [_V],

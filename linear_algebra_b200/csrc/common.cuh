@@ -107,7 +107,7 @@ template <typename T, int OP> struct ApplyOp {
     }
 
 static inline bool la_valid_dtype(int d) { return d >= LA_U8 && d <= LA_F64; }
-static inline bool la_aligned16(const void* p) { return (((uintptr_t)p) & 15u) == 0; }
+static __host__ __device__ inline bool la_aligned16(const void* p) { return (((uintptr_t)p) & 15u) == 0; }
 
 // ---------------------------------------------------------------- 128-bit streaming access
 // One 16-byte packet of T.  Streaming (evict-first) loads/stores: every hot-path operand of the

@@ -169,6 +169,29 @@ __global__ void __launch_bounds__(EW_THREADS) synth_kernel(T* dst, uint64_t seed
     for (size_t i = (size_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) dst[i] = synth_value<T>(splitmix64(seed ^ (uint64_t)i));
 }
 
+// C[i] = A[i] * (1 / sqrt(*dot_dev)): the scale step of normalize / normalized (src/vector.rs:313-323) with the
+// squared length taken from device memory, so length -> 1/length -> scale needs no host round trip.  sqrt and the
+// divide are the correctly rounded IEEE operations the reference's host code performs (traits.rs:63-65, vector.rs:314).
+template <typename T>
+__global__ void __launch_bounds__(EW_THREADS)
+scale_by_inv_norm_kernel(T* C, const T* A, const T* __restrict__ dot_dev, size_t n) {
+    const T inv = T(1) / sqrt(*dot_dev);
+    const size_t stride = (size_t)gridDim.x * EW_THREADS;
+    if (la_aligned16(C) && la_aligned16(A)) {
+        using P = Pack<T>;
+        const size_t n_pack = n / P::N;
+        for (size_t p = (size_t)blockIdx.x * EW_THREADS + threadIdx.x; p < n_pack; p += stride) {
+            P a = ld_stream(reinterpret_cast<const P*>(A) + p), c;
+#pragma unroll
+            for (int k = 0; k < P::N; ++k) c.v[k] = a.v[k] * inv;
+            st_stream(reinterpret_cast<P*>(C) + p, c);
+        }
+        for (size_t i = n_pack * P::N + (size_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) C[i] = A[i] * inv;
+    } else {
+        for (size_t i = (size_t)blockIdx.x * EW_THREADS + threadIdx.x; i < n; i += stride) C[i] = A[i] * inv;
+    }
+}
+
 la_status check_common(int dtype, size_t n) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "unknown dtype %d", dtype);
     (void)n;
@@ -250,5 +273,26 @@ extern "C" la_status la_synth(int dtype, void* dst_dev, uint64_t seed, size_t n,
         synth_kernel<T><<<(unsigned)blocks, EW_THREADS, 0, (cudaStream_t)stream>>>((T*)dst_dev, seed, n);
     });
     LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
+// normalized (C != A) / normalize (C == A), vector.rs:313-323: dot(a, a), sqrt, 1/length, scale -- stream-ordered,
+// no host wait.  Real types only (traits.rs:76-78).
+extern "C" la_status la_normalize_vec(int dtype, void* C, const void* A, size_t n, void* stream) {
+    if (dtype != LA_F32 && dtype != LA_F64) return la_fail(LA_ERR_DTYPE, "la_normalize_vec: needs a Real element type (f32 / f64)");
+    if (n && (!C || !A)) return la_fail(LA_ERR_ARG, "la_normalize_vec: NULL operand");
+    if (n == 0) return LA_OK;
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    cudaStream_t st = (cudaStream_t)stream;
+    void* scratch; LA_TRY(la_scratch(st, 0, &scratch));
+    void* slot = (char*)scratch + 32;                      // bytes 32..39 of the header (restored to zero below)
+    LA_TRY(la_dot_vec_vec_dev(dtype, A, A, n, slot, stream));
+    size_t blocks = (n / 4 + EW_THREADS) / EW_THREADS;
+    const size_t cap = (size_t)info->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    if (dtype == LA_F32) scale_by_inv_norm_kernel<float><<<(unsigned)blocks, EW_THREADS, 0, st>>>((float*)C, (const float*)A, (const float*)slot, n);
+    else                 scale_by_inv_norm_kernel<double><<<(unsigned)blocks, EW_THREADS, 0, st>>>((double*)C, (const double*)A, (const double*)slot, n);
+    LA_LAUNCH_CHECK();
+    LA_CUDA(cudaMemsetAsync(slot, 0, 8, st));
     return LA_OK;
 }

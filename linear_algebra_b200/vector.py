@@ -254,13 +254,17 @@ class Vector:
         return self.dtype.np.type(math.sqrt(dot(self, self))) if self.dtype.np == np.float64 else np.sqrt(dot(self, self))
 
     def normalize(self):                          # consumes self in Rust; here: in place, returns self
-        inv = self.dtype.np.type(1.0) / self.length()
-        self *= inv
+        assert self.dtype.real, "normalize() needs a Real element type (traits.rs:76-78)"
+        call("la_normalize_vec", self.dtype.code, self._ptr, self._ptr, self._len, _STREAM)     # dot, sqrt, 1/len, scale on the device
+        _done()
         return self
 
     def normalized(self):
-        inv = self.dtype.np.type(1.0) / self.length()
-        return self * inv
+        assert self.dtype.real, "normalized() needs a Real element type (traits.rs:76-78)"
+        res = Vector.uninitialized(self._len, self.dtype)
+        call("la_normalize_vec", self.dtype.code, res._ptr, self._ptr, self._len, _STREAM)
+        _done()
+        return res
 
     # ---- persistence (vector.rs:183-245, util.rs:6-21): native-endian u64 element size, u64 element
     # count, raw data.  Files written by the reference load here and vice versa.

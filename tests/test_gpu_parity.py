@@ -433,3 +433,21 @@ def test_matmat_large_ragged_shapes_take_the_fast_engines_through_padding(la):
     # small ragged products stay on the generic kernel
     check_f32_gemm(la, gen.values("f32", 33 * 17, 86), gen.values("f32", 17 * 29, 87), 33, 17, 29, "small ragged")
     assert lib.la_gemm_last_padded() == 0 and lib.la_gemm_last_engine() == 0
+
+
+# ------------------------------------------------------------------ fused normalize
+@pytest.mark.parametrize("name", ["f32", "f64"])
+def test_normalize_is_the_three_step_sequence(la, name):
+    """la_normalize_vec (dot, sqrt, 1/length, scale on the device) gives the bits of the reference's sequence
+    length() -> 1/length -> `* scalar` (vector.rs:303-323)."""
+    for n in (1, 5, 1000, (1 << 20) + 3):
+        a = gen.values(name, n, 90)
+        A = la.Vector.from_vec(a, name)
+        inv = NP[name](1.0) / A.length()
+        expect = (A * inv).to_vec()
+        assert same(A.normalized().to_vec(), expect), (name, n)
+        B = A.clone().normalize()
+        assert same(B.to_vec(), expect)
+        assert abs(float(B.length()) - 1.0) < 1e-5
+    with pytest.raises(AssertionError):
+        la.Vector.from_vec([1, 2, 3], "i32").normalized()

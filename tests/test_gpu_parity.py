@@ -451,3 +451,17 @@ def test_normalize_is_the_three_step_sequence(la, name):
         assert abs(float(B.length()) - 1.0) < 1e-5
     with pytest.raises(AssertionError):
         la.Vector.from_vec([1, 2, 3], "i32").normalized()
+
+
+def test_8bit_division_is_exact_for_every_operand_pair(la):
+    """8-bit `/` runs through the FP32 pipe (common.cuh la_div_u8 / la_div_i8): all 256 x 255 (u8) and
+    256 x 254 (i8, divisors 0 and -1 excluded as in OpenCL) operand pairs against the oracle."""
+    P = oracle.port()
+    a = np.repeat(np.arange(256, dtype=np.uint8), 255); b = np.tile(np.arange(1, 256, dtype=np.uint8), 256)
+    assert same((la.Vector.from_vec(a, "u8") / la.Vector.from_vec(b, "u8")).to_vec(), P.ew_vec_vec(DIV, a, b))
+    divs = np.array([d for d in range(-128, 128) if d not in (0, -1)], dtype=np.int8)
+    a = np.repeat(np.arange(-128, 128, dtype=np.int8), divs.size); b = np.tile(divs, 256)
+    assert same((la.Vector.from_vec(a, la.I8_CHAR) / la.Vector.from_vec(b, la.I8_CHAR)).to_vec(), P.ew_vec_vec(DIV, a, b))
+    s = la.Vector.from_vec(np.arange(256, dtype=np.uint8), "u8")
+    for d in (1, 2, 3, 7, 255):
+        assert same((s / np.uint8(d)).to_vec(), P.ew_vec_scl(DIV, np.arange(256, dtype=np.uint8), np.uint8(d)))

@@ -157,17 +157,17 @@ struct GemmShape {
     static constexpr int WM = 4 * TM, WN = 8 * TN;
     static constexpr int BM = WARPS_M * WM, BN = WARPS_N * WN;
     static constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
-    static_assert(CONSUMER_WARPS == 8, "two consumer warpgroups");
-    // 8 consumer warps + one producer warpgroup (setmaxnreg moves registers between whole
-    // warpgroups; a 9th lone warp would put 3 warps on one SM sub-partition and cap everyone
-    // at 168 registers).
+    static_assert(CONSUMER_WARPS % 4 == 0, "whole consumer warpgroups");
+    // consumer warpgroups + one producer warpgroup (setmaxnreg moves registers between whole
+    // warpgroups; a lone extra warp would put one more warp on one SM sub-partition and cap
+    // everyone's registers).
     static constexpr int THREADS = (CONSUMER_WARPS + 4) * 32;
     static constexpr int STAGE_ELEMS = (BM + BN) * BK;
     static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_ELEMS * 4;
     // setmaxnreg trades registers inside the CTA's own launch-time pool: THREADS * (launch regs),
     // launch regs = 65536 / (THREADS * MIN_BLOCKS) rounded down to a multiple of 8.
     static constexpr int LAUNCH_REGS = (65536 / (THREADS * MIN_BLOCKS)) / 8 * 8;
-    static_assert(128 * PRODUCER_REGS + 256 * CONSUMER_REGS <= THREADS * LAUNCH_REGS, "CTA register pool");
+    static_assert(128 * PRODUCER_REGS + CONSUMER_WARPS * 32 * CONSUMER_REGS <= THREADS * LAUNCH_REGS, "CTA register pool");
 };
 
 template <typename T, typename S, bool PACKED>
@@ -375,6 +375,9 @@ using Shape_8x16  = GemmShape< 8, 16, 4, 2, 16, 4, 1, 240>;    // 128 x 256 bloc
 using Shape_16x8k = GemmShape<16,  8, 4, 2,  8, 8, 1, 240>;    // 256 x 128 block, BK 8
 using Shape_8x8   = GemmShape< 8,  8, 4, 2, 16, 4, 2, 104>;    // 128 x 128 block, two per SM
 using Shape_8x8s  = GemmShape< 8,  8, 4, 2, 16, 6, 1, 240>;    // 128 x 128 block, one per SM
+using Shape_8x8w  = GemmShape< 8,  8, 6, 2, 16, 4, 1, 160>;    // 192 x 128 block, 12 consumer warps (3 per scheduler)
+using Shape_8x8v  = GemmShape< 8,  8, 4, 3, 16, 4, 1, 160>;    // 128 x 192 block, 12 consumer warps
+using Shape_16x8d = GemmShape<16,  8, 4, 2, 32, 3, 1, 240>;    // 256 x 128 block, BK 32
 
 template <typename T>
 la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, cudaStream_t st) {
@@ -385,7 +388,10 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
     constexpr bool F = std::is_same<T, float>::value;
     switch (g_gemm_variant) {
     default:
-    case 0: return gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);
+    case 0:                                                                      // 256 x 128 tile; f32: BK 32 (65.0 vs 63.5 TFLOP/s at 8192^2),
+        if (F) return gemm_tma_launch<T, Shape_16x8d, F>(C, At, B, M, K, N, st);  // integers: BK 16 (35.7 vs 30.4 Top/s: the IMAD body spills at BK 32)
+        return gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);
+    case 12: return gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);
     case 1: return gemm_tma_launch<T, Shape_16x8, false>(C, At, B, M, K, N, st);
     case 2: return gemm_tma_launch<T, Shape_8x8, F>(C, At, B, M, K, N, st);
     case 3: return gemm_tma_launch<T, Shape_8x8, false>(C, At, B, M, K, N, st);
@@ -394,6 +400,8 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
     case 6: return gemm_tma_launch<T, Shape_16x8k, F>(C, At, B, M, K, N, st);
     case 7: return gemm_tma_launch<T, Shape_8x8s, F>(C, At, B, M, K, N, st);
     case 8: return gemm_tma_launch<T, Shape_8x16, false>(C, At, B, M, K, N, st);
+    case 9: return gemm_tma_launch<T, Shape_8x8w, F>(C, At, B, M, K, N, st);
+    case 10: return gemm_tma_launch<T, Shape_8x8v, F>(C, At, B, M, K, N, st);
     }
 }
 

@@ -232,7 +232,7 @@ def test_matmat_f32_tolerance(la):
         check_f32_gemm(la, gen.values("f32", M * K, 23), gen.values("f32", K * N, 24), M, K, N, (M, K, N))
 
 
-@pytest.mark.parametrize("variant", list(range(0, 9)) + [-1])
+@pytest.mark.parametrize("variant", list(range(0, 11)) + [12, -1])
 def test_matmat_every_engine_variant(la, variant):
     """All tile shapes of the TMA engine (and the generic engine, -1) on shapes with ragged
     edge tiles and a K tail."""

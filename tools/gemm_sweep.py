@@ -9,8 +9,9 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import linear_algebra_b200 as la  # noqa: E402
 
-VARIANTS = {0: "16x8 256x128 ffma2", 1: "16x8 256x128 ffma", 2: "8x8 128x128 x2/SM ffma2", 3: "8x8 128x128 x2/SM ffma",
-            4: "8x16 128x256 ffma2", 5: "16x8 128x256 ffma2", 6: "16x8 256x128 BK8 ffma2", 7: "8x8 128x128 x1/SM ffma2", 8: "8x16 128x256 ffma"}
+VARIANTS = {0: "16x8 256x128 BK32 ffma2 (default)", 12: "16x8 256x128 BK16 ffma2", 1: "16x8 256x128 ffma", 2: "8x8 128x128 x2/SM ffma2", 3: "8x8 128x128 x2/SM ffma",
+            4: "8x16 128x256 ffma2", 5: "16x8 128x256 ffma2", 6: "16x8 256x128 BK8 ffma2", 7: "8x8 128x128 x1/SM ffma2", 8: "8x16 128x256 ffma",
+            9: "8x8 192x128 12 warps ffma2", 10: "8x8 128x192 12 warps ffma2"}
 
 
 def main():
@@ -26,7 +27,7 @@ def main():
         lib.call("la_set_gemm_mode", 0)      # SIMT engine variants first
         for dtype_code, label in ((8, "f32"), (5, "i32")):
             for v, desc in VARIANTS.items():
-                if label == "i32" and "ffma2" in desc and v not in (0, 2, 4):
+                if label == "i32" and v not in (0, 4, 7):
                     continue
                 lib.lib.la_gemm_set_variant(v)
                 try:

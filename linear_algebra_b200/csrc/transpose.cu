@@ -60,6 +60,62 @@ transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
     }
 }
 
+// 1- and 2-byte elements: the tile lives in shared memory as 32-bit words (G = 4 / sizeof(E) elements each), so the
+// shared-memory traffic is word-sized instead of byte-sized; the G x G sub-blocks are transposed in registers with
+// byte permutes.  Tile: TR = 128 / sizeof(E) input rows x 32 words (128 bytes) -> 32 G output rows of 128 bytes.
+template <int G> __device__ __forceinline__ void subword_transpose(const uint32_t* in, uint32_t* out);
+template <> __device__ __forceinline__ void subword_transpose<4>(const uint32_t* in, uint32_t* out) {      // 4 x 4 bytes
+    const uint32_t t0 = __byte_perm(in[0], in[1], 0x5140), t1 = __byte_perm(in[0], in[1], 0x7362);       // a0 b0 a1 b1 | a2 b2 a3 b3
+    const uint32_t t2 = __byte_perm(in[2], in[3], 0x5140), t3 = __byte_perm(in[2], in[3], 0x7362);       // c0 d0 c1 d1 | c2 d2 c3 d3
+    out[0] = __byte_perm(t0, t2, 0x5410); out[1] = __byte_perm(t0, t2, 0x7632);                          // a0 b0 c0 d0 | a1 b1 c1 d1
+    out[2] = __byte_perm(t1, t3, 0x5410); out[3] = __byte_perm(t1, t3, 0x7632);
+}
+template <> __device__ __forceinline__ void subword_transpose<2>(const uint32_t* in, uint32_t* out) {      // 2 x 2 halves
+    out[0] = __byte_perm(in[0], in[1], 0x5410); out[1] = __byte_perm(in[0], in[1], 0x7632);
+}
+
+template <typename E>
+__global__ void __launch_bounds__(TR_THREADS)
+transpose_subword_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x) {
+    constexpr int G = 4 / (int)sizeof(E);            // elements per word
+    constexpr int TR = 128 / (int)sizeof(E);          // input rows per tile
+    constexpr int TW = 32;                            // input words per tile row
+    constexpr int TC = TW * G;                        // input columns (= output rows) per tile
+    __shared__ uint32_t tile[TR][TW + 1];
+    const size_t r0 = (size_t)(blockIdx.x / tiles_x) * TR, c0 = (size_t)(blockIdx.x % tiles_x) * TC;
+    // load: TR rows x 8 packets of 16 bytes; R and C are multiples of 16 / sizeof(E) on this path
+    constexpr int LOADS = TR * 8 / TR_THREADS;
+    uint4 p[LOADS];
+#pragma unroll
+    for (int j = 0; j < LOADS; ++j) {
+        const int idx = threadIdx.x + j * TR_THREADS, r = idx / 8, q = idx % 8;
+        p[j] = (r0 + r < R && c0 + (size_t)q * 4 * G < C) ? __ldcs(reinterpret_cast<const uint4*>(in + (r0 + r) * C + c0 + (size_t)q * 4 * G)) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int j = 0; j < LOADS; ++j) {
+        const int idx = threadIdx.x + j * TR_THREADS, r = idx / 8, q = idx % 8;
+        tile[r][q * 4 + 0] = p[j].x; tile[r][q * 4 + 1] = p[j].y; tile[r][q * 4 + 2] = p[j].z; tile[r][q * 4 + 3] = p[j].w;
+    }
+    __syncthreads();
+    // thread (w, jj): word column w, input rows 4 G jj .. 4 G jj + 4 G - 1 -> G output rows, 16 bytes each
+    const int jj = threadIdx.x % 8, w = threadIdx.x / 8;
+    uint32_t o[G][4];
+#pragma unroll
+    for (int blk = 0; blk < 4; ++blk) {
+        uint32_t a[G], t[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) a[g] = tile[4 * G * jj + blk * G + g][w];
+        subword_transpose<G>(a, t);
+#pragma unroll
+        for (int g = 0; g < G; ++g) o[g][blk] = t[g];
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const size_t orow = c0 + (size_t)w * G + g, ocol = r0 + (size_t)jj * 4 * G;
+        if (orow < C && ocol < R) __stcs(reinterpret_cast<uint4*>(out + orow * R + ocol), make_uint4(o[g][0], o[g][1], o[g][2], o[g][3]));
+    }
+}
+
 // Any shape / alignment: 32x32 tile, scalar accesses (coalesced on both sides).
 template <typename E>
 __global__ void __launch_bounds__(TR_THREADS)
@@ -97,6 +153,16 @@ la_status transpose_launch(E* out, const E* in, size_t R, size_t C, cudaStream_t
     constexpr int V = Pack<E>::N;
     const bool packed = la_aligned16(out) && la_aligned16(in) && R % V == 0 && C % V == 0;
     if (packed) {
+        if constexpr (sizeof(E) < 4) {
+            constexpr int TRs = 128 / (int)sizeof(E), TCs = 32 * (4 / (int)sizeof(E));
+            const size_t gx = (C + TCs - 1) / TCs, gy = (R + TRs - 1) / TRs;
+            if (gx * gy > 0x7fffffffull || gx > 0xffffffffull) return la_fail(LA_ERR_UNSUPPORTED, "transpose: %zu x %zu is too large", R, C);
+            if (g_tr_variant != 9) {       // 9 = the generic tile kernel (tuning reference)
+                transpose_subword_kernel<E><<<(unsigned)(gx * gy), TR_THREADS, 0, st>>>(out, in, R, C, (unsigned)gx);
+                LA_LAUNCH_CHECK();
+                return LA_OK;
+            }
+        }
         if constexpr (sizeof(E) == 4) {
             switch (g_tr_variant) {
             case 1: return transpose_pack_launch<E, 32, 64>(out, in, R, C, st);

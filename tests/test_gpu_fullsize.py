@@ -146,6 +146,15 @@ def test_more_than_2_pow_32_elements(la):
     T = X.transpose()
     for r, c in ((0, 0), (65535, 65542), (40000, 123), (7, 65000)):
         assert T.data.slice_to_vec(c * R + r, 1)[0] == synth.values("u8", 0xC, r * Cc + c, 1)[0]
+    del X, T
+    # same size with columns a multiple of 16: the register-permute sub-word kernel, 64-bit offsets
+    Cc = 65552
+    X = la.Matrix(la.Vector.synth(0xD, R * Cc, "u8"), R, Cc)
+    T = X.transpose()
+    for r, c in ((0, 0), (65535, 65551), (40000, 123), (7, 65000), (65535, 0), (0, 65551)):
+        assert T.data.slice_to_vec(c * R + r, 1)[0] == synth.values("u8", 0xD, r * Cc + c, 1)[0]
+    row = T.data.slice_to_vec(65551 * R, R)                       # one whole output row = last input column
+    assert row[:4096].tobytes() == np.array([synth.values("u8", 0xD, r * Cc + 65551, 1)[0] for r in range(4096)], np.uint8).tobytes()
 
 
 def test_empty_operands(la):

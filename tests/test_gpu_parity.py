@@ -333,7 +333,7 @@ def test_matrix_elementwise_delegates(la):     # matrix.rs:134-218, 268-277
 @pytest.mark.parametrize("name", gen.ALL_NAMES)
 def test_transpose(la, name):
     P = oracle.port()
-    for R, C in ((1, 1), (1, 9), (9, 1), (33, 65), (64, 32), (128, 256), (1000, 516), (520, 1000), (2049, 31)):
+    for R, C in ((1, 1), (1, 9), (9, 1), (33, 65), (64, 32), (128, 256), (1000, 516), (520, 1000), (2049, 31), (2064, 1056), (4112, 48), (16, 4096)):
         a = gen.values(name, R * C, 35)
         T = la.Matrix.from_vec(a, R, C, dt(la, name)).transpose()
         assert T.len() == (C, R)

@@ -120,10 +120,11 @@ def run_reference_arm(args):
     if rank != 0:
         return
     vals = []
+    budget = float(os.environ.get("LA_BENCH_REF_BUDGET_S", "30"))      # CPU seconds over all timed steps (tests shrink it)
     for _ in range(args.warmup):
-        time_reference_gemm(1.0)
+        time_reference_gemm(min(1.0, budget))
     for _ in range(args.steps):
-        vals.append(time_reference_gemm(max(2.0, 30.0 / max(1, args.steps))))
+        vals.append(time_reference_gemm(max(min(2.0, budget), budget / max(1, args.steps))))
     v = statistics.mean(x["value"] for x in vals)
     cb = dict(vals[-1]); cb["value"] = v
     ms = statistics.mean(x["seconds"] for x in vals) * 1e3

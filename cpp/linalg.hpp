@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -46,6 +47,60 @@ LINALG_PARAM(double, LA_F64, "double")
 #undef LINALG_PARAM
 
 template <typename T> class Matrix;
+template <typename T> class Vector;
+
+// ---- user kernels: create_kernel (lib.rs:156-171) and the named-argument `ocl::Kernel` it returns.  `source` is the
+// text of the user's src/extra_kernels.cl ({T}, IS_<TYPE>, `i`: lib.rs:158-163); declare the arguments in
+// signature order with arg_buf_named / arg_scl_named, as lib.rs:189-274 does for the built-in kernels.
+template <typename T>
+class Kernel {
+  public:
+    Kernel(const std::string& kernel_name, const std::string& source) {
+        check(la_user_kernel_create(Parameter<T>::DTYPE, source.c_str(), kernel_name.c_str(), &k_));
+    }
+    Kernel(const Kernel&) = delete;
+    Kernel& operator=(const Kernel&) = delete;
+    Kernel(Kernel&& o) noexcept : k_(o.k_), names_(std::move(o.names_)), slots_(std::move(o.slots_)) { o.k_ = nullptr; }
+    ~Kernel() { if (k_) la_user_kernel_destroy(k_); }
+
+    Kernel& arg_buf_named(const std::string& name) { names_.push_back(name); slots_.emplace_back(sizeof(void*), 0); return *this; }
+    template <typename S> Kernel& arg_scl_named(const std::string& name, S value) {
+        names_.push_back(name); slots_.emplace_back(sizeof(S), 0); return set_arg_scl_named(name, value);
+    }
+    Kernel& set_arg_buf_named(const std::string& name, const void* dev_ptr) { return store(name, &dev_ptr, sizeof(dev_ptr)); }
+    template <typename S> Kernel& set_arg_scl_named(const std::string& name, S value) { return store(name, &value, sizeof(S)); }
+    void enq(size_t gws) {                                          // kernel.cmd().gws(n).enq() + event.wait_for()
+        std::vector<void*> argv;
+        for (auto& sl : slots_) argv.push_back(sl.data());
+        check(la_user_kernel_launch(k_, gws, argv.data(), nullptr));
+        check(la_stream_sync(nullptr));
+    }
+
+  private:
+    Kernel& store(const std::string& name, const void* bytes, size_t n) {
+        for (size_t j = 0; j < names_.size(); ++j)
+            if (names_[j] == name) {
+                if (slots_[j].size() != n) throw Panic("kernel argument '" + name + "' has another size");
+                std::memcpy(slots_[j].data(), bytes, n);
+                return *this;
+            }
+        throw Panic("kernel has no argument named '" + name + "'");
+    }
+    la_user_kernel* k_ = nullptr;
+    std::vector<std::string> names_;
+    std::vector<std::vector<unsigned char>> slots_;
+};
+
+inline std::string load_extra_src(const std::string& path = "src/extra_kernels.cl") {      // lib.rs:173-180; missing file = ""
+    std::string text;
+    if (std::FILE* f = std::fopen(path.c_str(), "rb")) {
+        char buf[4096]; size_t n;
+        while ((n = std::fread(buf, 1, sizeof(buf), f)) > 0) text.append(buf, n);
+        std::fclose(f);
+    }
+    return text;
+}
+template <typename T> Kernel<T> create_kernel(const std::string& kernel_name) { return Kernel<T>(kernel_name, load_extra_src()); }   // lib.rs:165-171
 
 template <typename T>
 class Vector {                              // vector.rs:23-27
@@ -116,6 +171,25 @@ class Vector {                              // vector.rs:23-27
         std::FILE* f = std::fopen(path.c_str(), "rb"); if (!f) throw Panic("Failed to open file");
         Vector v = read_from_file(f); std::fclose(f); return v;
     }
+    // user kernels (vector.rs:80-151): slots named "C" (result / self), "A", "B"
+    static Vector generate(Kernel<T>& k, size_t size) {             // vector.rs:80-90
+        Vector r = uninitialized(size); k.set_arg_buf_named("C", r.ptr_).enq(size); return r;
+    }
+    static Vector from_for_each2(const Vector& a, const Vector& b, Kernel<T>& k) {              // vector.rs:96-112
+        assert_eq(a.len_, b.len_);
+        Vector r = uninitialized(a.len_);
+        k.set_arg_buf_named("C", r.ptr_).set_arg_buf_named("A", a.ptr_).set_arg_buf_named("B", b.ptr_).enq(r.len_);
+        return r;
+    }
+    void for_each_mut(const Vector& o, Kernel<T>& k) {              // vector.rs:114-125
+        assert_eq(len_, o.len_);
+        k.set_arg_buf_named("C", ptr_).set_arg_buf_named("B", o.ptr_).enq(len_);
+    }
+    void map_mut(Kernel<T>& k) { k.set_arg_buf_named("C", ptr_).enq(len_); }                   // vector.rs:127-136
+    Vector map(Kernel<T>& k) const {                                // vector.rs:138-151
+        Vector r = uninitialized(len_); k.set_arg_buf_named("C", r.ptr_).set_arg_buf_named("B", ptr_).enq(len_); return r;
+    }
+
     T length() const;                                               // vector.rs:303-305
     Vector normalized() const { T inv = T(1) / length(); return *this * inv; }                  // vector.rs:320-323
     Vector normalize() && { T inv = T(1) / length(); *this *= inv; return std::move(*this); }   // vector.rs:313-317

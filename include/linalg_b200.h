@@ -225,6 +225,36 @@ la_status la_get_gemm_mode(int* mode);
  * north star.  out[c*rows + r] = in[r*cols + c]; out must not alias in. */
 la_status la_transpose(int dtype, void* out, const void* in, size_t rows, size_t cols, void* stream);
 
+/* ------------------------------------------------------------------ user kernels
+ * The reference's extension point: `create_kernel` (src/lib.rs:156-171) hands out a kernel from the
+ * text of src/extra_kernels.cl, which `get_src` (src/lib.rs:337-354, `load_extra_src` :173-180)
+ * appends to its own kernel source once per element type with {T} replaced by the OpenCL type
+ * name and IS_<TYPE> defined; src/vector.rs:80-151 (generate, from_for_each2, for_each_mut,
+ * map_mut, map) launches it with one work-item per element.  Here `source` is that text and
+ * NVRTC compiles it for sm_100a.  It may stay in the dialect the reference documents -- `kernel
+ * void {T}_name(global {T}* C, ...)`, `i` for get_global_id(0), plain helper functions,
+ * get_global_size/get_local_id/barrier/local, `{T}_dot_product` (src/kernels.cl:134-140) -- or be
+ * CUDA C++ (`extern "C" __global__`).  {T}: uchar char ushort short uint int ulong long float double.
+ *
+ * la_user_kernel_compile   compiles only (needs no device): a syntax check; *cubin_bytes may be NULL.
+ * la_user_kernel_create    compiles, loads and looks up `kernel_name` (the full name, {T} already
+ *                          substituted, e.g. "float_test_kernel").  A compile error returns
+ *                          LA_ERR_ARG with the start of NVRTC's log in la_last_error() and the whole
+ *                          log in la_user_kernel_build_log() (the reference panics with the build log).
+ * la_user_kernel_launch    one work-item per index 0..global_size-1, never more (sizes that are not
+ *                          a multiple of the 256-thread block run their remainder as a second,
+ *                          smaller launch).  arg_values[j] points at the value of the kernel's j-th
+ *                          parameter (a device pointer or a scalar), as for cuLaunchKernel.
+ *                          Stream-ordered, returns without waiting.  A handle carries launch state on
+ *                          the device: use it from one stream at a time (ocl::Kernel is the same). */
+typedef struct la_user_kernel la_user_kernel;
+la_status la_user_kernel_compile(int dtype, const char* source, size_t* cubin_bytes);
+la_status la_user_kernel_create(int dtype, const char* source, const char* kernel_name, la_user_kernel** kernel);
+la_status la_user_kernel_launch(la_user_kernel* kernel, size_t global_size, void** arg_values, void* stream);
+la_status la_user_kernel_destroy(la_user_kernel* kernel);
+const char* la_user_kernel_build_log(void);          /* NVRTC's log of this thread's last compile */
+const char* la_user_kernel_type_name(int dtype);     /* what {T} becomes; NULL for an unknown dtype */
+
 #ifdef __cplusplus
 }
 #endif

@@ -83,9 +83,14 @@ SIGNATURES = {
     "la_set_gemm_mode": [_I],
     "la_get_gemm_mode": [_PI],
     "la_transpose": [_I, _V, _V, _Z, _Z, _V],
+    "la_user_kernel_compile": [_I, ctypes.c_char_p, ctypes.POINTER(ctypes.c_size_t)],
+    "la_user_kernel_create": [_I, ctypes.c_char_p, ctypes.c_char_p, _PV],
+    "la_user_kernel_launch": [_V, _Z, _PV, _V],
+    "la_user_kernel_destroy": [_V],
 }
 NON_STATUS = {"la_last_error": ctypes.c_char_p, "la_version": ctypes.c_char_p, "la_dtype_size": ctypes.c_size_t,
-              "la_p2p_mailbox_bytes": ctypes.c_size_t, "la_p2p_handle_bytes": ctypes.c_size_t}
+              "la_p2p_mailbox_bytes": ctypes.c_size_t, "la_p2p_handle_bytes": ctypes.c_size_t,
+              "la_user_kernel_build_log": ctypes.c_char_p, "la_user_kernel_type_name": ctypes.c_char_p}
 
 for _name, _args in SIGNATURES.items():
     _f = getattr(lib, _name)
@@ -99,6 +104,10 @@ lib.la_p2p_mailbox_bytes.argtypes = []
 lib.la_p2p_mailbox_bytes.restype = ctypes.c_size_t
 lib.la_p2p_handle_bytes.argtypes = []
 lib.la_p2p_handle_bytes.restype = ctypes.c_size_t
+lib.la_user_kernel_build_log.argtypes = []
+lib.la_user_kernel_build_log.restype = ctypes.c_char_p
+lib.la_user_kernel_type_name.argtypes = [_I]
+lib.la_user_kernel_type_name.restype = ctypes.c_char_p
 lib.la_dtype_size.argtypes = [_I]
 lib.la_dtype_size.restype = ctypes.c_size_t
 # tuning hook (not declared in the public header)

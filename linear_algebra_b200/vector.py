@@ -159,6 +159,49 @@ class Vector:
                 pass
             self._ptr = None
 
+    # ---- user kernels (vector.rs:80-151); `kernel` is a linear_algebra_b200.kernel.Kernel whose argument slots
+    #      are named "C" (result / self), "A", "B" as the reference's helpers expect
+    @staticmethod
+    def generate(kernel, size, dtype=None):                       # vector.rs:80-90
+        res = Vector.uninitialized(size, dtype if dtype is not None else kernel.dtype)
+        kernel.set_arg_buf_named("C", res)
+        kernel.enq(res._len, _STREAM)
+        call("la_stream_sync", _STREAM)
+        return res
+
+    @staticmethod
+    def from_for_each2(a, b, kernel):                             # vector.rs:96-112 (the `_lock_free` body)
+        assert a._len == b._len, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (a._len, b._len)
+        res = Vector.uninitialized(a._len, a.dtype)
+        kernel.set_arg_buf_named("C", res)
+        kernel.set_arg_buf_named("A", a)
+        kernel.set_arg_buf_named("B", b)
+        kernel.enq(res._len, _STREAM)
+        call("la_stream_sync", _STREAM)
+        return res
+
+    def for_each_mut(self, other, kernel):                        # vector.rs:114-125
+        assert self._len == other._len, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (self._len, other._len)
+        kernel.set_arg_buf_named("C", self)
+        kernel.set_arg_buf_named("B", other)
+        kernel.enq(self._len, _STREAM)
+        call("la_stream_sync", _STREAM)
+        return self
+
+    def map_mut(self, kernel):                                    # vector.rs:127-136
+        kernel.set_arg_buf_named("C", self)
+        kernel.enq(self._len, _STREAM)
+        call("la_stream_sync", _STREAM)
+        return self
+
+    def map(self, kernel):                                        # vector.rs:138-151
+        res = Vector.uninitialized(self._len, self.dtype)
+        kernel.set_arg_buf_named("C", res)
+        kernel.set_arg_buf_named("B", self)
+        kernel.enq(res._len, _STREAM)
+        call("la_stream_sync", _STREAM)
+        return res
+
     # ---- helpers (vector.rs:96-125)
     def _check_same(self, other):
         assert isinstance(other, Vector), "expected a Vector"

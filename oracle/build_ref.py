@@ -65,8 +65,11 @@ def build_cl_source(reference: str) -> str:
         text.append(("#define IS_%s\n" % ty.upper() + kernels_cl + "\n").replace("{T}", ty))
         text.append("\n#undef IS_%s\n" % ty.upper())
     src = "".join(text).encode()
+    raw = kernels_cl.encode()                  # untemplated: cl_ref.py re-runs get_src with a user's extra_kernels.cl text appended
     c = "static const unsigned char text[] = {" + ",".join(str(b) for b in src) + ",0};\n" \
-        "const char* ref_cl_source(void) { return (const char*)text; }\n"
+        "const char* ref_cl_source(void) { return (const char*)text; }\n" \
+        "static const unsigned char raw[] = {" + ",".join(str(b) for b in raw) + ",0};\n" \
+        "const char* ref_cl_raw_source(void) { return (const char*)raw; }\n"
     out_dir = os.path.join(HERE, "_ref")
     os.makedirs(out_dir, exist_ok=True)
     out = os.path.join(out_dir, "libref_clsrc.so")

@@ -64,13 +64,27 @@ def _open_library():
 class ClRef:
     kind = "reference-opencl"
 
-    def __init__(self):
+    TYPES = ["uchar", "char", "ushort", "short", "uint", "int", "ulong", "long", "float"]      # lib.rs:84-92
+
+    def __init__(self, extra_source=None):
+        """`extra_source`: the text of a user's src/extra_kernels.cl; the program is then assembled as lib.rs:337-354
+        `get_src` does when that file exists (core source + "\n" + extra, per type)."""
         src_so = os.path.join(HERE, "_ref", "libref_clsrc.so")
         if not os.path.exists(src_so):
             raise ClUnavailable(src_so + " missing (built by oracle/build_ref.py where /root/reference exists)")
         srclib = ctypes.CDLL(src_so)
         srclib.ref_cl_source.restype = ctypes.c_char_p
         source = srclib.ref_cl_source()
+        if extra_source is not None:
+            if not hasattr(srclib, "ref_cl_raw_source"):
+                raise ClUnavailable(src_so + " predates user-kernel support: rebuild with oracle/build_ref.py")
+            srclib.ref_cl_raw_source.restype = ctypes.c_char_p
+            raw = srclib.ref_cl_raw_source().decode()
+            parts = []
+            for ty in self.TYPES:
+                parts.append(("#define IS_%s\n" % ty.upper() + raw + "\n" + extra_source).replace("{T}", ty))
+                parts.append("\n#undef IS_%s\n" % ty.upper())
+            source = "".join(parts).encode()
         self.cl, self.libname = _open_library()
         cl = self.cl
         for f, res in (("clCreateContext", _P), ("clCreateCommandQueue", _P), ("clCreateProgramWithSource", _P), ("clCreateKernel", _P), ("clCreateBuffer", _P)):
@@ -170,6 +184,26 @@ class ClRef:
         self.cl.clGetEventProfilingInfo(ev, CL_PROFILING_COMMAND_END, 8, ctypes.byref(t1), None)
         self.last_kernel_ns = t1.value - t0.value
         self.cl.clReleaseEvent(ev)
+
+    def run_user_kernel(self, full_name, args, gws):
+        """create_kernel (lib.rs:165-171) + one launch with `gws` work-items and no local size (vector.rs:80-151).
+        args: numpy arrays (buffers, returned with their contents after the launch) or ('val', numpy scalar array)."""
+        err = _I(0)
+        k = _P(self.cl.clCreateKernel(self.program, full_name.encode(), ctypes.byref(err)))
+        self._ok(err.value, "clCreateKernel(%s)" % full_name)
+        mems, largs = [], []
+        for a in args:
+            if isinstance(a, tuple):
+                largs.append(a)
+            else:
+                m = self._buf(np.ascontiguousarray(a))
+                mems.append((m, a))
+                largs.append(("buf", m))
+        self._launch(k, largs, gws)
+        outs = [self._read(m, a.dtype, a.size) for m, a in mems]
+        self._free(*[m for m, _ in mems])
+        self.cl.clReleaseKernel(k)
+        return outs
 
     def preferred_multiple(self, kernel):                         # lib.rs:101-113
         v = _Z(0)

@@ -123,11 +123,36 @@ static void panics_like_the_reference() {
     CHECK(o == Matrix<TestType>::from_vec({3, 4, 5, 6, 8, 10}, 2, 3));
 }
 
+static void user_kernels() {                     // lib.rs:156-171 + vector.rs:80-151 (the reference has no test of these)
+    const std::string src =
+        "kernel void {T}_twice(global {T}* C, global {T}* B) { C[i] = B[i] * ({T})(2); }\n"
+        "kernel void {T}_blend(global {T}* C, global {T}* A, global {T}* B) { C[i] = A[i] * B[i] + A[i]; }\n"
+        "kernel void {T}_ramp(global {T}* C, {T} first) { C[i] = first + ({T})i; }\n";
+    const std::string ty = linalg::Parameter<TestType>::type_to_str();
+    linalg::Kernel<TestType> twice(ty + "_twice", src), blend(ty + "_blend", src), ramp(ty + "_ramp", src);
+    twice.arg_buf_named("C").arg_buf_named("B");
+    blend.arg_buf_named("C").arg_buf_named("A").arg_buf_named("B");
+    ramp.arg_buf_named("C").arg_scl_named("first", (TestType)10);
+    auto a = Vector<TestType>::from_vec({1, 2, 3, 4, 5}); auto b = Vector<TestType>::from_vec({5, 4, 3, 2, 1});
+    CHECK(a.map(twice) == Vector<TestType>::from_vec({2, 4, 6, 8, 10}));
+    CHECK(Vector<TestType>::from_for_each2(a, b, blend) == Vector<TestType>::from_vec({6, 10, 12, 12, 10}));
+    auto c = a.clone(); c.for_each_mut(a, twice);
+    CHECK(c == Vector<TestType>::from_vec({2, 4, 6, 8, 10}));
+    auto g = Vector<TestType>::generate(ramp, 300);
+    std::vector<TestType> want; for (int x = 0; x < 300; ++x) want.push_back((TestType)(10 + x));
+    CHECK(g == Vector<TestType>::from_vec(want));
+    g.map_mut(ramp);
+    CHECK(g == Vector<TestType>::from_vec(want));
+    CHECK(panics([&] { linalg::Kernel<TestType>(ty + "_absent", src); }));       // lib.rs:169 panic
+    CHECK(panics([&] { linalg::Kernel<TestType>(ty + "_twice", "kernel void {T}_twice(global {T}* C) { C[i] = oops; }"); }));
+    CHECK(panics([&] { Vector<TestType>::from_for_each2(a, Vector<TestType>::from_vec({1}), blend); }));
+}
+
 int main() {
     try {
         check(la_init(0));
         f32_vec_mat_mul(); vec_eq(); vec_sum(); vec_vec_dot(); mat_eq(); vec_mat_mul(); mat_mat_mul(); vec_transpose_mat_mul();
-        vec_add(); vec_mul_scl(); save_load_vec(); save_load_mat(); normalize_vec(); length_vec(); vec_clone(); panics_like_the_reference();
+        vec_add(); vec_mul_scl(); save_load_vec(); save_load_mat(); normalize_vec(); length_vec(); vec_clone(); panics_like_the_reference(); user_kernels();
     } catch (const std::exception& e) { std::printf("EXCEPTION: %s\n", e.what()); return 2; }
     std::printf(failures ? "%d checks failed\n" : "all reference tests passed (%d failures)\n", failures);
     return failures ? 1 : 0;

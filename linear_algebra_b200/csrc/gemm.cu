@@ -7,8 +7,9 @@
 // la_mul_mat_mat dispatches over five engines (la_mul_mat_mat_impl at the bottom of this file):
 //  * gemm_tc.cu    3xTF32 tcgen05 tensor-core engine: f32, >= 512^3 multiply-adds, operands in range (LA_GEMM_AUTO)
 //  * gemm_limb.cu  exact byte-limb products on the INT8 tensor cores: 8/16/32-bit integers, >= 512^3 multiply-adds
-//  * gemm_tma_kernel  (below; 4-byte element types, M % 4 == 0, N % 4 == 0, 16-byte aligned bases; what
-//      LA_GEMM_SIMT forces, and what mid-sized or out-of-range f32 products get):
+//  * gemm_tma_kernel  (below; 4- and 8-byte element types, M and N multiples of 16 bytes' worth of elements, 16-byte
+//      aligned bases; what LA_GEMM_SIMT forces, what mid-sized or out-of-range f32 products get, and where f64 / 64-bit
+//      integer products run):
 //      TMA-fed, shared-memory-staged, register-tiled SIMT kernel.  A dedicated producer warpgroup issues
 //      cp.async.bulk.tensor.2d loads of a [BK x BM] slab of A^T and a [BK x BN] slab of B into a
 //      STAGES-deep ring guarded by full/empty mbarriers; 8 consumer warps (setmaxnreg 240) read both
@@ -21,16 +22,17 @@
 //      zero fill.
 //  * zero-padding path: large products with ragged sizes / unaligned bases are copied into padded, aligned
 //      temporaries and run on the engines above.
-//  * gemm_generic_kernel (every dtype, any shape / alignment; small or 64-bit problems): 64x64x16
+//  * gemm_generic_kernel (every dtype, any shape / alignment; small problems): 64x64x16
 //      shared-memory tiling with guarded scalar loads.  8/16-bit integers accumulate in 32 bits and truncate.
 //
-// Roofline: FP32 FMA pipe (f32), integer multiply-add pipe (i32/u32).  Work: 2*M*N*K flop.
+// Roofline: FP32 FMA pipe (f32), FP64 pipe (f64), integer multiply-add pipe (integers).  Work: 2*M*N*K flop.
 #include "common.cuh"
 #include <cuda.h>
 #include <cstdlib>
 #include <mutex>
 
 la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st);   // transpose.cu
+la_status la_transpose_raw64(uint64_t* out, const uint64_t* in, size_t R, size_t C, cudaStream_t st);
 
 namespace {
 
@@ -136,7 +138,15 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
         ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y) : "memory");
 }
 
-template <typename T> struct Mac;       // multiply-accumulate on the 4-byte element types
+template <typename T> struct Mac;       // multiply-accumulate on the 4- and 8-byte element types
+template <> struct Mac<double> {
+    using Acc = double;
+    static __device__ __forceinline__ void mac(double& c, double a, double b) { c = fma(a, b, c); }
+};
+template <> struct Mac<uint64_t> {
+    using Acc = uint64_t;
+    static __device__ __forceinline__ void mac(uint64_t& c, uint64_t a, uint64_t b) { c += a * b; }
+};
 template <> struct Mac<float> {
     using Acc = float;
     static __device__ __forceinline__ void mac(float& c, float a, float b) { c = fmaf(a, b, c); }
@@ -146,8 +156,9 @@ template <> struct Mac<uint32_t> {
     static __device__ __forceinline__ void mac(uint32_t& c, uint32_t a, uint32_t b) { c += a * b; }
 };
 
-// Geometry: lanes are 4 (m) x 8 (n); a thread's TM rows are TM/4 chunks of 4 rows, 16 rows
-// apart; its TN columns are TN/4 chunks of 4 columns, 32 columns apart.  So an A fragment load
+// Geometry: lanes are 4 (m) x 8 (n).  With CH = 16 / sizeof(T) elements per 16-byte chunk (4 for the
+// 4-byte types, 2 for the 8-byte ones), a thread's TM rows are TM/CH chunks of CH rows, 4*CH rows
+// apart; its TN columns are TN/CH chunks of CH columns, 8*CH columns apart.  So an A fragment load
 // is a broadcast within each quarter-warp and a B fragment load is 128 contiguous bytes per
 // quarter-warp: both conflict-free LDS.128.
 template <int TM_, int TN_, int WARPS_M_, int WARPS_N_, int BK_, int STAGES_, int MIN_BLOCKS_, int CONSUMER_REGS_>
@@ -163,7 +174,7 @@ struct GemmShape {
     // everyone's registers).
     static constexpr int THREADS = (CONSUMER_WARPS + 4) * 32;
     static constexpr int STAGE_ELEMS = (BM + BN) * BK;
-    static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_ELEMS * 4;
+    static constexpr size_t smem_bytes(size_t elem_size) { return (size_t)STAGES * STAGE_ELEMS * elem_size; }
     // setmaxnreg trades registers inside the CTA's own launch-time pool: THREADS * (launch regs),
     // launch regs = 65536 / (THREADS * MIN_BLOCKS) rounded down to a multiple of 8.
     static constexpr int LAUNCH_REGS = (65536 / (THREADS * MIN_BLOCKS)) / 8 * 8;
@@ -175,6 +186,9 @@ __global__ void __launch_bounds__(S::THREADS, S::MIN_BLOCKS)
 gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, const __grid_constant__ CUtensorMap map_b,
                 int M, int N, int K, int tiles_m) {
     constexpr int TM = S::TM, TN = S::TN, BK = S::BK, BM = S::BM, BN = S::BN, STAGES = S::STAGES;
+    constexpr int CH = 16 / (int)sizeof(T);                 // elements per 16-byte chunk
+    static_assert(TM % CH == 0 && TN % CH == 0, "thread tile is made of whole 16-byte chunks");
+    static_assert(!PACKED || sizeof(T) == 4, "FFMA2 is the f32 path");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ alignas(8) uint64_t full_bar[STAGES];
     __shared__ alignas(8) uint64_t empty_bar[STAGES];
@@ -202,7 +216,7 @@ gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, c
                 mbar_wait(&empty_bar[s], ph ^ 1u);
                 T* as = smem + (size_t)s * S::STAGE_ELEMS;
                 T* bs = as + BM * BK;
-                mbar_expect_tx(&full_bar[s], (uint32_t)(S::STAGE_ELEMS * 4));
+                mbar_expect_tx(&full_bar[s], (uint32_t)(S::STAGE_ELEMS * sizeof(T)));
                 tma_load_2d(as, &map_at, &full_bar[s], m0, kb * BK);      // A^T slab: BK rows of BM
                 tma_load_2d(bs, &map_b, &full_bar[s], n0, kb * BK);       // B slab:   BK rows of BN
             }
@@ -215,8 +229,8 @@ gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, c
     using Acc = typename Mac<T>::Acc;
     const int wm = warp % S::WARPS_M, wn = warp / S::WARPS_M;
     const int mi = lane >> 3, ni = lane & 7;
-    const int a_off = wm * S::WM + mi * 4;        // + cm*16
-    const int b_off = wn * S::WN + ni * 4;        // + cn*32
+    const int a_off = wm * S::WM + mi * CH;       // + cm*4*CH
+    const int b_off = wn * S::WN + ni * CH;       // + cn*8*CH
 
     Acc acc[TM][TN];
 #pragma unroll
@@ -232,11 +246,11 @@ gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, c
     T fa[2][TM], fb[2][TN];
     auto load_frag = [&](int buf, const T* as, const T* bs, int k) {
 #pragma unroll
-        for (int cm = 0; cm < TM / 4; ++cm)
-            *reinterpret_cast<uint4*>(&fa[buf][cm * 4]) = *reinterpret_cast<const uint4*>(as + k * BM + cm * 16);
+        for (int cm = 0; cm < TM / CH; ++cm)
+            *reinterpret_cast<uint4*>(&fa[buf][cm * CH]) = *reinterpret_cast<const uint4*>(as + k * BM + cm * 4 * CH);
 #pragma unroll
-        for (int cn = 0; cn < TN / 4; ++cn)
-            *reinterpret_cast<uint4*>(&fb[buf][cn * 4]) = *reinterpret_cast<const uint4*>(bs + k * BN + cn * 32);
+        for (int cn = 0; cn < TN / CH; ++cn)
+            *reinterpret_cast<uint4*>(&fb[buf][cn * CH]) = *reinterpret_cast<const uint4*>(bs + k * BN + cn * 8 * CH);
     };
     static_assert(BK % 2 == 0, "fragment double-buffering alternates per k-step");
 
@@ -304,14 +318,14 @@ gemm_tma_kernel(T* __restrict__ C, const __grid_constant__ CUtensorMap map_at, c
     // ---------------- epilogue: 16-byte stores, 128 contiguous bytes per quarter-warp
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
-        const int m = m0 + a_off + (i / 4) * 16 + (i % 4);
+        const int m = m0 + a_off + (i / CH) * (4 * CH) + (i % CH);
         if (m < M) {
 #pragma unroll
-            for (int cn = 0; cn < TN / 4; ++cn) {
-                const int n = n0 + b_off + cn * 32;
-                if (n < N) {   // N % 4 == 0: a 4-column chunk is wholly inside or outside
+            for (int cn = 0; cn < TN / CH; ++cn) {
+                const int n = n0 + b_off + cn * 8 * CH;
+                if (n < N) {   // N % CH == 0: a chunk of CH columns is wholly inside or outside
                     uint4 v;
-                    memcpy(&v, &acc[i][cn * 4], 16);
+                    memcpy(&v, &acc[i][cn * CH], 16);
                     __stcs(reinterpret_cast<uint4*>(C + (size_t)m * N + n), v);
                 }
             }
@@ -339,14 +353,16 @@ la_status get_encode(EncodeTiledFn* out) {
     return LA_OK;
 }
 
-// 2-D row-major tensor of 4-byte elements: `rows` x `cols`, box `box_rows` x `box_cols`.
-la_status make_map(CUtensorMap* map, const void* base, size_t rows, size_t cols, int box_rows, int box_cols, bool is_float) {
+// 2-D row-major tensor of 4- or 8-byte elements: `rows` x `cols`, box `box_rows` x `box_cols`.
+la_status make_map(CUtensorMap* map, const void* base, size_t rows, size_t cols, int box_rows, int box_cols, bool is_float, size_t elem_size) {
     EncodeTiledFn enc; LA_TRY(get_encode(&enc));
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * elem_size};
     cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(map, is_float ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base),
+    const CUtensorMapDataType type = elem_size == 8 ? (is_float ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_UINT64)
+                                                    : (is_float ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT32);
+    CUresult r = enc(map, type, 2, const_cast<void*>(base),
                      dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%zu cols=%zu box=%dx%d)", (int)r, rows, cols, box_rows, box_cols);
@@ -358,12 +374,16 @@ int g_gemm_variant = 0;     // la_gemm_set_variant (tuning hook, not part of the
 template <typename T, typename S, bool PACKED>
 la_status gemm_tma_launch(T* C, const T* At, const T* B, size_t M, size_t K, size_t N, cudaStream_t st) {
     CUtensorMap map_at, map_b;
-    LA_TRY(make_map(&map_at, At, K, M, S::BK, S::BM, std::is_same<T, float>::value));
-    LA_TRY(make_map(&map_b, B, K, N, S::BK, S::BN, std::is_same<T, float>::value));
+    static_assert(S::smem_bytes(sizeof(T)) <= 227 * 1024, "shared-memory ring fits one SM");
+    static_assert(S::BM <= 256 && S::BN <= 256, "TMA box dimension limit");
+    constexpr bool is_float = std::is_floating_point<T>::value;
+    LA_TRY(make_map(&map_at, At, K, M, S::BK, S::BM, is_float, sizeof(T)));
+    LA_TRY(make_map(&map_b, B, K, N, S::BK, S::BN, is_float, sizeof(T)));
     auto kern = gemm_tma_kernel<T, S, PACKED>;
-    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM_BYTES));
+    constexpr size_t smem = S::smem_bytes(sizeof(T));
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const size_t tm = (M + S::BM - 1) / S::BM, tn = (N + S::BN - 1) / S::BN;
-    kern<<<(unsigned)(tm * tn), S::THREADS, S::SMEM_BYTES, st>>>(C, map_at, map_b, (int)M, (int)N, (int)K, (int)tm);
+    kern<<<(unsigned)(tm * tn), S::THREADS, smem, st>>>(C, map_at, map_b, (int)M, (int)N, (int)K, (int)tm);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
@@ -379,11 +399,32 @@ using Shape_8x8w  = GemmShape< 8,  8, 6, 2, 16, 4, 1, 160>;    // 192 x 128 bloc
 using Shape_8x8v  = GemmShape< 8,  8, 4, 3, 16, 4, 1, 160>;    // 128 x 192 block, 12 consumer warps
 using Shape_16x8d = GemmShape<16,  8, 4, 2, 32, 3, 1, 240>;    // 256 x 128 block, BK 32
 
+// 8-byte element types: thread tile 8 x 8 (64 accumulators = 128 registers)
+using Shape64_8x8  = GemmShape< 8,  8, 4, 2, 16, 4, 1, 240>;    // 128 x 128 block, 8 consumer warps, 4 x 32 KB stages
+using Shape64_8x8d = GemmShape< 8,  8, 4, 2, 32, 3, 1, 240>;    // 128 x 128 block, BK 32, 3 x 64 KB stages
+using Shape64_8x8k = GemmShape< 8,  8, 4, 2,  8, 8, 1, 240>;    // 128 x 128 block, BK 8, 8 x 16 KB stages
+using Shape64_8x4  = GemmShape< 8,  4, 4, 2, 16, 4, 1, 240>;    // 128 x 64 block: the 64-bit integer multiply-add needs the registers an 8 x 8 tile would take
+using Shape64_4x8  = GemmShape< 4,  8, 4, 2, 16, 4, 1, 240>;    // 64 x 128 block
+
 template <typename T>
 la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, cudaStream_t st) {
     // A^T (K x M) into scratch
-    void* scratch; LA_TRY(la_scratch(st, M * K * 4, &scratch));
+    void* scratch; LA_TRY(la_scratch(st, M * K * sizeof(T), &scratch));
     T* At = (T*)((char*)scratch + LA_SCRATCH_ZEROED);
+    if constexpr (sizeof(T) == 8) {
+        LA_TRY(la_transpose_raw64((uint64_t*)At, (const uint64_t*)A, M, K, st));
+        switch (g_gemm_variant) {
+        default:
+        case 0:                                                                          // f64: 8 x 8 tile, BK 32 (28.7 TFLOP/s at 4096^3; generic engine 12.1)
+            if (std::is_same<T, double>::value) return gemm_tma_launch<T, Shape64_8x8d, false>(C, At, B, M, K, N, st);
+            return gemm_tma_launch<T, Shape64_8x4, false>(C, At, B, M, K, N, st);
+        case 1: return gemm_tma_launch<T, Shape64_8x8, false>(C, At, B, M, K, N, st);
+        case 2: return gemm_tma_launch<T, Shape64_8x8k, false>(C, At, B, M, K, N, st);
+        case 3: return gemm_tma_launch<T, Shape64_8x4, false>(C, At, B, M, K, N, st);
+        case 4: return gemm_tma_launch<T, Shape64_4x8, false>(C, At, B, M, K, N, st);
+        case 5: return gemm_tma_launch<T, Shape64_8x8d, false>(C, At, B, M, K, N, st);
+        }
+    } else {
     LA_TRY(la_transpose_raw32((uint32_t*)At, (const uint32_t*)A, M, K, st));
     constexpr bool F = std::is_same<T, float>::value;
     switch (g_gemm_variant) {
@@ -402,6 +443,7 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
     case 8: return gemm_tma_launch<T, Shape_8x16, false>(C, At, B, M, K, N, st);
     case 9: return gemm_tma_launch<T, Shape_8x8w, F>(C, At, B, M, K, N, st);
     case 10: return gemm_tma_launch<T, Shape_8x8v, F>(C, At, B, M, K, N, st);
+    }
     }
 }
 
@@ -455,8 +497,8 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     cudaStream_t st = (cudaStream_t)stream;
     if (K == 0) { LA_CUDA(cudaMemsetAsync(C, 0, M * N * la_dtype_size(dtype), st)); return LA_OK; }
 
-    const bool four_byte = (dtype == LA_F32 || dtype == LA_U32 || dtype == LA_I32);
-    const bool tma_ok = four_byte && g_gemm_variant >= 0 && M % 4 == 0 && N % 4 == 0 && la_aligned16(A) && la_aligned16(B) && la_aligned16(C) &&
+    const size_t chunk = 16 / la_dtype_size(dtype);        // elements per 16 bytes: TMA row pitches and the 16-byte C stores need whole chunks
+    const bool tma_ok = la_dtype_size(dtype) >= 4 && g_gemm_variant >= 0 && M % chunk == 0 && N % chunk == 0 && la_aligned16(A) && la_aligned16(B) && la_aligned16(C) &&
                         M >= 64 && N >= 64 && K >= 16 && M < (1u << 31) && N < (1u << 31) && K < (1u << 31);
     g_last_padded = 0;
     const bool big = (double)M * (double)N * (double)K >= 134217728.0;      // 512^3 multiply-adds
@@ -477,7 +519,7 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     // run the fast engines on those and copy C back.  Zero padding adds exact zeros to every dot product.
     const size_t es = la_dtype_size(dtype);
     const bool ragged = (M % 16) || (K % 16) || (N % 16) || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C);   // false on the padded call
-    if (ragged && es <= 4 && big && M < (1u << 30) && N < (1u << 30) && K < (1u << 30)) {
+    if (ragged && big && M < (1u << 30) && N < (1u << 30) && K < (1u << 30)) {
         const size_t Mp = (M + 15) / 16 * 16, Kp = (K + 15) / 16 * 16, Np = (N + 15) / 16 * 16;
         void *Ap = nullptr, *Bp = nullptr, *Cp = nullptr;
         LA_CUDA(cudaMallocAsync(&Ap, Mp * Kp * es, st));
@@ -496,6 +538,8 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     if (tma_ok) {
         g_last_engine = 1;
         if (dtype == LA_F32) return gemm_tma<float>((float*)C, (const float*)A, (const float*)B, M, K, N, st);
+        if (dtype == LA_F64) return gemm_tma<double>((double*)C, (const double*)A, (const double*)B, M, K, N, st);
+        if (la_dtype_size(dtype) == 8) return gemm_tma<uint64_t>((uint64_t*)C, (const uint64_t*)A, (const uint64_t*)B, M, K, N, st);   // i64 == u64 mod 2^64
         return gemm_tma<uint32_t>((uint32_t*)C, (const uint32_t*)A, (const uint32_t*)B, M, K, N, st);   // i32 == u32 mod 2^32
     }
     g_last_engine = 0;

@@ -186,6 +186,10 @@ la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t
     return transpose_launch<uint32_t, 64>(out, in, R, C, st);
 }
 
+la_status la_transpose_raw64(uint64_t* out, const uint64_t* in, size_t R, size_t C, cudaStream_t st) {
+    return transpose_launch<uint64_t, 32>(out, in, R, C, st);
+}
+
 extern "C" la_status la_transpose_set_variant(int v) { g_tr_variant = v; return LA_OK; }      // tuning hook
 
 extern "C" la_status la_transpose(int dtype, void* out, const void* in, size_t rows, size_t cols, void* stream) {

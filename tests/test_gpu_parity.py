@@ -411,6 +411,40 @@ def test_matmat_limb_engine_is_bit_exact(la, name):
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+# ------------------------------------------------------------------ 8-byte element types on the TMA-fed SIMT engine
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+def test_matmat_64bit_types_on_the_tma_engine(la, variant):
+    """f64 (DFMA, k ascending, one fused multiply-add per k) and u64/i64 (wrapping) through gemm_tma_kernel's 8-byte
+    instantiation: interior and ragged edge tiles, a K tail, every tile shape.  Integers bit-exact; f64 against the oracle's
+    own k-ascending f64 sum within 1e-13 of sum|a||b| (fused vs unfused rounding of each step)."""
+    P = oracle.port(); lib = la._lib.lib
+    lib.la_gemm_set_variant(variant)
+    try:
+        for M, K, N in ((512, 256, 384), (386, 1001, 262), (64, 16, 64)):
+            for name in ("u64", "i64"):
+                a = gen.values(name, M * K, 91); b = gen.values(name, K * N, 92)
+                C = la.Matrix.from_vec(a, M, K, dt(la, name)) * la.Matrix.from_vec(b, K, N, dt(la, name))
+                assert lib.la_gemm_last_engine() == 1, (name, M, K, N)
+                assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (variant, name, M, K, N)
+            a = gen.values("f64", M * K, 93); b = gen.values("f64", K * N, 94)
+            C = (la.Matrix.from_vec(a, M, K, "f64") * la.Matrix.from_vec(b, K, N, "f64")).to_vec()
+            assert lib.la_gemm_last_engine() == 1
+            ref = P.mul_mat_mat(a, b, M, K, N)
+            scale = (np.abs(a.reshape(M, K)) @ np.abs(b.reshape(K, N))).reshape(-1)
+            assert np.max(np.abs(C - ref) / scale) < 1e-13, (variant, M, K, N)
+        # odd M or N: the 16-byte chunks do not divide the rows -> generic engine (small) or padding (large)
+        a = gen.values("i64", 65 * 32, 95); b = gen.values("i64", 32 * 67, 96)
+        C = la.Matrix.from_vec(a, 65, 32, "i64") * la.Matrix.from_vec(b, 32, 67, "i64")
+        assert lib.la_gemm_last_engine() == 0 and same(C.to_vec(), P.mul_mat_mat(a, b, 65, 32, 67))
+        M, K, N = 515, 1031, 523
+        a = gen.values("u64", M * K, 97); b = gen.values("u64", K * N, 98)
+        C = la.Matrix.from_vec(a, M, K, "u64") * la.Matrix.from_vec(b, K, N, "u64")
+        assert lib.la_gemm_last_padded() == 1 and lib.la_gemm_last_engine() == 1
+        assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N))
+    finally:
+        lib.la_gemm_set_variant(0)
+
+
 # ------------------------------------------------------------------ ragged large products: padded onto the fast engines
 def test_matmat_large_ragged_shapes_take_the_fast_engines_through_padding(la):
     P = oracle.port(); lib = la._lib.lib

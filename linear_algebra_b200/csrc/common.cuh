@@ -44,6 +44,8 @@ la_status la_scratch(cudaStream_t stream, size_t bytes, void** ptr);
 // *host_ptr after waiting for them (no device-to-host copy involved).
 la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsigned** dev_ptr);
 
+int la_gemm_raster_group(size_t pair_tiles_m);   // gemm_tc.cu: tile rows per band of the tensor engines' tile order (0 = m-major; tuning hook la_gemm_set_raster)
+
 // ---------------------------------------------------------------- dtype traits
 template <typename T> struct Arith {                       // wrap-safe arithmetic
     using U = typename std::make_unsigned<T>::type;        // same width, unsigned

@@ -50,7 +50,7 @@ __device__ __forceinline__ void umma_i8_2sm(uint32_t tmem_d, uint64_t a_desc, ui
 template <typename OutT, int L>
 __global__ void __launch_bounds__(LB_THREADS, 1)
 gemm_limb_2cta_kernel(OutT* __restrict__ C, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                      int M, int N, int K, int pair_tiles_m) {
+                      int M, int N, int K, int pair_tiles_m, int tiles_n, int raster_group) {
     using S = LimbShape<L>;
     constexpr int STAGES = S::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -63,9 +63,10 @@ gemm_limb_2cta_kernel(OutT* __restrict__ C, const __grid_constant__ CUtensorMap 
     uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();
-    const int pair = blockIdx.x >> 1;
-    const int m0 = (pair % pair_tiles_m) * 256 + (int)crank * 128;
-    const int n0 = (pair / pair_tiles_m) * LB_BN;
+    int tile_m, tile_n;
+    la_raster_tile((int)(blockIdx.x >> 1), pair_tiles_m, tiles_n, raster_group, tile_m, tile_n);
+    const int m0 = tile_m * 256 + (int)crank * 128;
+    const int n0 = tile_n * LB_BN;
     const int num_kb = (K + LB_BK - 1) / LB_BK;
 
     if (threadIdx.x == 0) {
@@ -268,7 +269,7 @@ la_status limb_gemm(U* C, const U* A, const U* B, size_t M, size_t K, size_t N, 
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, map_a, map_b, (int)M, (int)N, (int)K, (int)ptm));
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, map_a, map_b, (int)M, (int)N, (int)K, (int)ptm, (int)tnn, la_gemm_raster_group(ptm)));
     return LA_OK;
 }
 

@@ -366,7 +366,7 @@ __device__ __forceinline__ void umma_tf32_2sm(uint32_t tmem_d, uint64_t a_desc, 
 __global__ void __launch_bounds__(TC3_THREADS, 1)
 gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                         const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
-                        int M, int N, int K, int pair_tiles_m) {
+                        int M, int N, int K, int pair_tiles_m, int tiles_n, int raster_group) {
     constexpr int STAGES = TC3_STAGES;
     extern __shared__ uint8_t smem_raw[];
     __shared__ alignas(8) uint64_t full_bar[STAGES];     // used in the leader: both CTAs' slabs have landed
@@ -379,9 +379,10 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
     uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();
-    const int pair = blockIdx.x >> 1;
-    const int m0 = (pair % pair_tiles_m) * 256 + (int)crank * 128;
-    const int n0 = (pair / pair_tiles_m) * 256;
+    int tile_m, tile_n;
+    la_raster_tile((int)(blockIdx.x >> 1), pair_tiles_m, tiles_n, raster_group, tile_m, tile_n);
+    const int m0 = tile_m * 256 + (int)crank * 128;
+    const int n0 = tile_n * 256;
     const int num_kb = (K + TC_BK - 1) / TC_BK;
     const int num_chunks = (num_kb + TC_CHUNK_KB - 1) / TC_CHUNK_KB;
 
@@ -630,7 +631,7 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    LA_CUDA(cudaLaunchKernelEx(&cfg, gemm_3xtf32_2cta_kernel, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, (int)K, (int)ptm));
+    LA_CUDA(cudaLaunchKernelEx(&cfg, gemm_3xtf32_2cta_kernel, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, (int)K, (int)ptm, (int)tn, la_gemm_raster_group(ptm)));
     return LA_OK;
 }
 
@@ -639,6 +640,13 @@ int g_tc_variant = 0;
 }  // namespace
 
 extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA_OK; }     // tuning hook
+// Tile order of the tensor engines.  In m-major order one wave of 74 CTA pairs spans every tile row, so each wave streams
+// all of A's planes from HBM: 1.8 TB/s at M = 8192 (harmless), 3.5 TB/s at M = 16384 (the kernel then waits on HBM:
+// 16384^3 f32 42.6 ms).  Bands of 8 tile rows keep a wave on ~17 row/column slabs whatever the size (16384^3: 36.5 ms;
+// i32 37.6 -> 31.8 ms); at M <= 8192 the two orders time the same, so the plain order stays there.
+static int g_raster_group = -1;                         // -1: by size; 0: m-major; g > 0: bands of g tile rows
+int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m > 32 ? 8 : 0); }
+extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; return LA_OK; }   // tuning hook
 
 // Pieces shared by la_gemm_3xtf32 and the host-streaming GEMM (gemm_host.cu).
 la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size_t K, unsigned* flag, cudaStream_t st) {

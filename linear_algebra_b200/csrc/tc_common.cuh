@@ -57,6 +57,21 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// Linear tile index -> (tile_m, tile_n), walking the tile grid in bands of `group` tile rows: m fastest inside a
+// band, then n, then the next band.  The ~74 CTA pairs in flight then cover about `group` x 74/group tiles and share
+// that few A row-slabs and B column-slabs through L2, instead of every tile row of the matrix (m-major order), which
+// at 16384^2 re-streams all of A from HBM once per wave.  group <= 0 or >= tiles_m is the plain m-major order.
+__device__ __forceinline__ void la_raster_tile(int t, int tiles_m, int tiles_n, int group, int& tm, int& tn) {
+    if (group <= 0 || group >= tiles_m) { tm = t % tiles_m; tn = t / tiles_m; return; }
+    const int band_tiles = group * tiles_n;
+    const int band = t / band_tiles;
+    const int first_m = band * group;
+    const int rows = min(group, tiles_m - first_m);
+    const int r = t - band * band_tiles;
+    tm = first_m + r % rows;
+    tn = r / rows;
+}
+
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
 }

@@ -94,6 +94,33 @@ def test_f32_gemm_8192(la, mode):              # the headline config, on both f3
         assert np.linalg.norm(C[r * n:(r + 1) * n] - truth) / np.linalg.norm(truth) <= 1e-5
 
 
+def test_gemm_16384_banded_tile_order(la):     # C3's largest size; above M = 8192 the tensor engines walk the tiles in bands
+    n = 16384
+    A = la.Matrix(la.Vector.synth(0x5EED0003, n * n, "f32"), n, n); B = la.Matrix(la.Vector.synth(0x5EED0004, n * n, "f32"), n, n)
+    C = A * B
+    assert la._lib.lib.la_gemm_last_engine() == 2
+    rng = np.random.default_rng(104)
+    Bt = B.transpose()                          # rows of Bt = columns of B, so a sampled entry needs two contiguous downloads
+    worst = 0.0
+    for r, col in rng.integers(0, n, (48, 2)):
+        ar = A.data.slice_to_vec(int(r) * n, n).astype(np.float64); bc = Bt.data.slice_to_vec(int(col) * n, n).astype(np.float64)
+        got = float(C.data.slice_to_vec(int(r) * n + int(col), 1)[0])
+        worst = max(worst, abs(got - float(ar @ bc)) / float(np.abs(ar) @ np.abs(bc)))
+    assert worst <= 64 * 2.0 ** -24, worst
+    del Bt
+    # every entry at once: C x = A (B x) with the library's own M.v (verified independently), x a +-1 vector, normwise
+    x = la.Vector.from_vec((rng.integers(0, 2, n) * 2 - 1).astype(np.float32))
+    lhs = la.mul_transpose_mat(x, C).to_vec().astype(np.float64)
+    rhs = la.mul_transpose_mat(la.mul_transpose_mat(x, B), A).to_vec().astype(np.float64)
+    assert np.linalg.norm(lhs - rhs) / np.linalg.norm(rhs) <= 1e-5
+    # and the same product in m-major order is bit-identical
+    la._lib.lib.la_gemm_set_raster(0)
+    try:
+        assert (A * B) == C
+    finally:
+        la._lib.lib.la_gemm_set_raster(-1)
+
+
 def test_matvec_32768(la):                     # configs[2], one GPU
     n = 32768
     rng = np.random.default_rng(103)

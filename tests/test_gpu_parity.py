@@ -411,6 +411,34 @@ def test_matmat_limb_engine_is_bit_exact(la, name):
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+# ------------------------------------------------------------------ tile order of the tensor engines
+@pytest.mark.parametrize("group", [1, 3, 8])
+def test_matmat_banded_tile_order_changes_nothing(la, group):
+    """la_gemm_set_raster: bands of `group` tile rows instead of m-major order (the default above M = 8192).  Which CTA
+    computes which tile cannot change a bit of the result: f32 tensor engine and i32 limb engine against their m-major
+    runs, on shapes whose last band is ragged (8 and 5 tile rows of 256) and with partial edge tiles."""
+    lib = la._lib.lib
+    P = oracle.port()
+    try:
+        for M, K, N in ((1800, 160, 1100), (1280, 256, 640)):
+            a = gen.values("f32", M * K, 61); b = gen.values("f32", K * N, 62)
+            ai = gen.values("i32", M * K, 63); bi = gen.values("i32", K * N, 64)
+            out = {}
+            for g in (0, group):
+                lib.la_gemm_set_raster(g)
+                la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+                out["f", g] = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+                assert lib.la_gemm_last_engine() == 2
+                la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+                out["i", g] = (la.Matrix.from_vec(ai, M, K) * la.Matrix.from_vec(bi, K, N)).to_vec()
+                assert lib.la_gemm_last_engine() == 3
+            assert same(out["f", 0], out["f", group]) and same(out["i", 0], out["i", group]), (group, M, K, N)
+            assert same(out["i", group], P.mul_mat_mat(ai, bi, M, K, N))
+    finally:
+        lib.la_gemm_set_raster(-1)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
 # ------------------------------------------------------------------ 8-byte element types on the TMA-fed SIMT engine
 @pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
 def test_matmat_64bit_types_on_the_tma_engine(la, variant):

@@ -363,10 +363,39 @@ __device__ __forceinline__ void umma_tf32_2sm(uint32_t tmem_d, uint64_t a_desc, 
         ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+// Work plan of the CTA-pair kernel.  Items 0 .. dp_items-1 are whole tiles.  The tiles after them (stream_tiles of them:
+// the last full wave plus the ragged remainder) are cut into stream_items equal spans of accumulation chunks, one span per
+// CTA pair, so the final wave is as long for every pair instead of leaving most SMs idle behind a partial wave.  A span is
+// at least one tile long (stream_tiles >= stream_items), so a tile receives at most two contributions: both are added
+// onto zeroed memory with atomics, and a sum of two addends does not depend on their order -- results stay reproducible.
+struct TcPlan {
+    int pair_tiles_m, tiles_n, raster_group;
+    int num_kb, chunk_kb, num_chunks;            // k-blocks of 32; k-blocks per tensor-core accumulation chain; chains per tile
+    int dp_items, stream_items, stream_tiles;
+};
+
+// Segment `seg` of work item `item`: tile (linear index) and its chunk range [c_begin, c_end).  False when there is none.
+__device__ __forceinline__ bool tc_segment(const TcPlan& p, int item, int seg, int& tile, int& c_begin, int& c_end) {
+    if (item < p.dp_items) {
+        tile = item; c_begin = 0; c_end = p.num_chunks;
+        return seg == 0;
+    }
+    const long long total = (long long)p.stream_tiles * p.num_chunks;
+    const long long j = item - p.dp_items;
+    const long long span_b = j * total / p.stream_items, span_e = (j + 1) * total / p.stream_items;
+    const long long t = span_b / p.num_chunks + seg;
+    const long long tb = t * p.num_chunks;
+    if (tb >= span_e) return false;
+    tile = p.dp_items + (int)t;
+    c_begin = (int)((span_b > tb ? span_b : tb) - tb);
+    c_end = (int)((span_e < tb + p.num_chunks ? span_e : tb + p.num_chunks) - tb);
+    return c_begin < c_end;
+}
+
 __global__ void __launch_bounds__(TC3_THREADS, 1)
 gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                         const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
-                        int M, int N, int K, int pair_tiles_m, int tiles_n, int raster_group) {
+                        int M, int N, const TcPlan plan) {
     constexpr int STAGES = TC3_STAGES;
     extern __shared__ uint8_t smem_raw[];
     __shared__ alignas(8) uint64_t full_bar[STAGES];     // used in the leader: both CTAs' slabs have landed
@@ -379,12 +408,8 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
     uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();
-    int tile_m, tile_n;
-    la_raster_tile((int)(blockIdx.x >> 1), pair_tiles_m, tiles_n, raster_group, tile_m, tile_n);
-    const int m0 = tile_m * 256 + (int)crank * 128;
-    const int n0 = tile_n * 256;
-    const int num_kb = (K + TC_BK - 1) / TC_BK;
-    const int num_chunks = (num_kb + TC_CHUNK_KB - 1) / TC_CHUNK_KB;
+    const int item = (int)(blockIdx.x >> 1);
+    const int num_kb = plan.num_kb;
 
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -409,32 +434,43 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
         if (warp == 8) {
             // ---------------- TMA producer (both CTAs)
             if (lane == 0) {
-                for (int kb = 0; kb < num_kb; ++kb) {
-                    const int s = kb % STAGES;
-                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-                    mbar_wait(&empty_bar[s], ph ^ 1u);
-                    uint8_t* st = ring_ptr + (size_t)s * TC3_STAGE_BYTES;
-                    if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * TC3_STAGE_BYTES);     // my slabs + the peer's
-                    tma_load_2d_2sm(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
-                    tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
-                    tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
-                    tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
+                int it = 0;                                           // k-blocks issued so far, over all segments: ring position
+                int tile, cb, ce;
+                for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg) {
+                    int tile_m, tile_n;
+                    la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
+                    const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * 256;
+                    const int kb_end = min(ce * plan.chunk_kb, num_kb);
+                    for (int kb = cb * plan.chunk_kb; kb < kb_end; ++kb, ++it) {
+                        const int s = it % STAGES;
+                        const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+                        mbar_wait(&empty_bar[s], ph ^ 1u);
+                        uint8_t* st = ring_ptr + (size_t)s * TC3_STAGE_BYTES;
+                        if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * TC3_STAGE_BYTES);     // my slabs + the peer's
+                        tma_load_2d_2sm(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
+                        tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
+                        tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
+                        tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
+                    }
                 }
             }
         } else if (warp == 9 && crank == 0) {
             // ---------------- MMA issuer (leader CTA only)
             constexpr uint32_t idesc = umma_idesc_tf32(256, 256);
-            int kb = 0;
-            for (int c = 0; c < num_chunks; ++c) {
-                const int b = c & 1;
-                const uint32_t use = (uint32_t)(c >> 1);
+            int it = 0, cc = 0;                                       // k-blocks / chunks consumed so far, over all segments
+            int tile, cb, ce;
+            for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg)
+            for (int c = cb; c < ce; ++c, ++cc) {
+                const int b = cc & 1;
+                const uint32_t use = (uint32_t)(cc >> 1);
                 mbar_wait(&acc_empty_bar[b], (use & 1u) ^ 1u);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t tmem_d = tmem_base + (uint32_t)(b * 256);
-                const int kb_end = (kb + TC_CHUNK_KB < num_kb) ? kb + TC_CHUNK_KB : num_kb;
-                for (int first = 1; kb < kb_end; ++kb) {
-                    const int s = kb % STAGES;
-                    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                int kb = c * plan.chunk_kb;
+                const int kb_end = (kb + plan.chunk_kb < num_kb) ? kb + plan.chunk_kb : num_kb;
+                for (int first = 1; kb < kb_end; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
                     mbar_wait(&full_bar[s], ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     if (elect_one()) {
@@ -461,11 +497,14 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
         asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
         const int quad = warp & 3, half = warp >> 2;
         float acc[128];
+        int cc = 0;
+        int tile, cb, ce;
+        for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg) {
 #pragma unroll
         for (int i = 0; i < 128; ++i) acc[i] = 0.f;
-        for (int c = 0; c < num_chunks; ++c) {
-            const int b = c & 1;
-            const uint32_t use = (uint32_t)(c >> 1);
+        for (int c = cb; c < ce; ++c, ++cc) {
+            const int b = cc & 1;
+            const uint32_t use = (uint32_t)(cc >> 1);
             mbar_wait(&acc_full_bar[b], use & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * 256 + half * 128);
@@ -485,14 +524,23 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
             __syncwarp();
             if (lane == 0) mbar_arrive_on_leader(&acc_empty_bar[b]);
         }
+        int tile_m, tile_n;
+        la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
+        const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * 256;
+        const bool whole = (cb == 0 && ce == plan.num_chunks);       // otherwise one of (at most) two partial sums of this tile
         const int row = m0 + quad * 32 + lane;
         if (row < M) {
             float* crow = C + (size_t)row * N + n0 + half * 128;
 #pragma unroll
             for (int q = 0; q < 32; ++q) {
                 const int n = n0 + half * 128 + q * 4;
-                if (n < N) __stcs(reinterpret_cast<float4*>(crow + q * 4), make_float4(acc[q * 4], acc[q * 4 + 1], acc[q * 4 + 2], acc[q * 4 + 3]));
+                if (n < N) {
+                    const float4 v = make_float4(acc[q * 4], acc[q * 4 + 1], acc[q * 4 + 2], acc[q * 4 + 3]);
+                    if (whole) __stcs(reinterpret_cast<float4*>(crow + q * 4), v);
+                    else atomicAdd(reinterpret_cast<float4*>(crow + q * 4), v);      // onto zeroed memory (tc_launch_2cta)
+                }
             }
+        }
         }
     }
 
@@ -619,19 +667,55 @@ la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, cons
     return LA_OK;
 }
 
+int g_tc_stream = -1;           // la_gemm_set_stream_tail: -1 by the gain model below, 0 never, 1 whenever possible
+
 la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128));
     LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, 128)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, 128));
     LA_CUDA(cudaFuncSetAttribute(gemm_3xtf32_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     const size_t ptm = (M + 255) / 256, tn = (N + 255) / 256;
+    const long long tiles = (long long)(ptm * tn);
+    const long long pairs = info->sm_count / 2;                 // CTA pairs in flight (one per SM pair)
+
+    TcPlan plan = {};
+    plan.pair_tiles_m = (int)ptm; plan.tiles_n = (int)tn; plan.raster_group = la_gemm_raster_group(ptm);
+    plan.num_kb = (int)((K + TC_BK - 1) / TC_BK);
+    // Chains of 64 k, except for short products: a lone 64-chain is where the tensor cores' truncating accumulation shows
+    // most (K = 64, 16M outputs: max error 6.5e-7 of sum|a||b| against a bar of 5.9e-7); chains of 32 keep K <= 128 inside.
+    plan.chunk_kb = plan.num_kb <= 4 ? 1 : TC_CHUNK_KB;
+    plan.num_chunks = (plan.num_kb + plan.chunk_kb - 1) / plan.chunk_kb;
+    plan.dp_items = (int)tiles; plan.stream_items = 0; plan.stream_tiles = 0;
+    // Ragged last wave: `waves` full waves and `rest` tiles more.  When the remainder fills at most half of the GPU, each of
+    // its tiles is cut in two along K (two work items of half the length), so the last wave takes half a wave-time: 4096^3
+    // is 3.46 waves of tiles -> 3.5 instead of 4.  Both halves of all tiles start together and advance in step, like the
+    // whole tiles do, which keeps the operand slabs shared through L2.  (Cutting the last full wave plus the remainder into
+    // equal spans would balance any remainder, but the spans then start at staggered K positions, the CTAs stop sharing
+    // slabs in L2 and the kernel turns HBM-bound: measured 11 % slower at 2048 x 8192 x 8192.)
+    const long long waves = tiles / pairs, rest = tiles % pairs;
+    (void)waves;
+    if (rest > 0 && 2 * rest <= pairs && plan.num_chunks >= 2 && g_tc_stream != 0) {
+        plan.stream_tiles = (int)rest;
+        plan.stream_items = (int)(2 * rest);
+        plan.dp_items = (int)(tiles - rest);
+        // zero the tiles that receive two partial sums.  m-major order: they are the last tile columns (the first of them
+        // possibly shared with whole tiles, which simply overwrite); banded order: all of C.
+        if (plan.raster_group <= 0 || plan.raster_group >= plan.pair_tiles_m) {
+            const size_t first_col = ((size_t)plan.dp_items / ptm) * 256;
+            LA_CUDA(cudaMemset2DAsync(C + first_col, N * sizeof(float), 0, (N - first_col) * sizeof(float), M, st));
+        } else {
+            LA_CUDA(cudaMemsetAsync(C, 0, M * N * sizeof(float), st));
+        }
+    }
+    const long long items = plan.dp_items + plan.stream_items;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(2 * ptm * tn)); cfg.blockDim = dim3(TC3_THREADS); cfg.dynamicSmemBytes = TC3_SMEM_BYTES; cfg.stream = st;
+    cfg.gridDim = dim3((unsigned)(2 * items)); cfg.blockDim = dim3(TC3_THREADS); cfg.dynamicSmemBytes = TC3_SMEM_BYTES; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    LA_CUDA(cudaLaunchKernelEx(&cfg, gemm_3xtf32_2cta_kernel, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, (int)K, (int)ptm, (int)tn, la_gemm_raster_group(ptm)));
+    LA_CUDA(cudaLaunchKernelEx(&cfg, gemm_3xtf32_2cta_kernel, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, plan));
     return LA_OK;
 }
 
@@ -646,6 +730,7 @@ extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA
 // i32 37.6 -> 31.8 ms); at M <= 8192 the two orders time the same, so the plain order stays there.
 static int g_raster_group = -1;                         // -1: by size; 0: m-major; g > 0: bands of g tile rows
 int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m > 32 ? 8 : 0); }
+extern "C" la_status la_gemm_set_stream_tail(int mode) { g_tc_stream = mode; return LA_OK; }   // tuning hook: -1 auto, 0 off, 1 on
 extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; return LA_OK; }   // tuning hook
 
 // Pieces shared by la_gemm_3xtf32 and the host-streaming GEMM (gemm_host.cu).

@@ -258,7 +258,8 @@ def test_matmat_3xtf32_engine_meets_the_f32_bar(la, tc_variant):
     la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
     lib.la_gemm_tc_set_variant(tc_variant)
     try:
-        for M, K, N in ((128, 32, 128), (256, 256, 256), (512, 1000, 384), (388, 1004, 260), (1024, 2048, 512)):
+        # (4096, 64, 4096): a lone accumulation chain over 16M outputs, where the tensor cores' truncating accumulation shows most
+        for M, K, N in ((128, 32, 128), (256, 256, 256), (512, 1000, 384), (388, 1004, 260), (1024, 2048, 512), (4096, 64, 4096), (2048, 96, 2048), (2048, 160, 2048)):
             check_f32_gemm(la, gen.values("f32", M * K, 41), gen.values("f32", K * N, 42), M, K, N, ("3xtf32", tc_variant, M, K, N))
             assert lib.la_gemm_last_engine() == 2, "3xTF32 engine did not take %dx%dx%d" % (M, K, N)
         # shapes it does not cover fall through to the SIMT / generic engines
@@ -436,6 +437,39 @@ def test_matmat_banded_tile_order_changes_nothing(la, group):
             assert same(out["i", group], P.mul_mat_mat(ai, bi, M, K, N))
     finally:
         lib.la_gemm_set_raster(-1)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
+@pytest.mark.parametrize("raster", [0, 3])
+def test_matmat_3xtf32_stream_tail_meets_the_bar_and_is_reproducible(la, raster):
+    """The ragged last wave of the tensor engine cut into equal spans (la_gemm_set_stream_tail): tiles then get up to two
+    partial sums added with atomics onto zeroed memory.  Same f32 bar as every engine; bit-identical from run to run
+    (two addends commute); shapes with one and with several waves, a K tail, ragged edges, both tile orders."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    lib.la_gemm_set_stream_tail(1); lib.la_gemm_set_raster(raster)
+    try:
+        for M, K, N in ((2560, 512, 2304), (2500, 1000, 2300), (4096, 136, 5000), (256 * 75, 64, 256)):
+            a = gen.values("f32", M * K, 65); b = gen.values("f32", K * N, 66)
+            A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+            C1 = (A * B).to_vec()
+            assert lib.la_gemm_last_engine() == 2
+            if M * K * N <= 3e9:
+                P = oracle.port()
+                truth, absab = P.f32_mul_mat_mat_truth(a, b, M, K, N)
+                check_float_dot_like(C1, P.mul_mat_mat(a, b, M, K, N), truth, absab, ("stream tail", raster, M, K, N))
+            else:
+                rows = [0, 255, 256, M // 2, M - 1]
+                ref = a.reshape(M, K)[rows].astype(np.float64) @ b.reshape(K, N).astype(np.float64)
+                assert np.linalg.norm(C1.reshape(M, N)[rows] - ref) / np.linalg.norm(ref) <= 1e-5
+            for _ in range(3):
+                assert same((A * B).to_vec(), C1), ("not reproducible", raster, M, K, N)
+            lib.la_gemm_set_stream_tail(0)
+            C0 = (A * B).to_vec()
+            lib.la_gemm_set_stream_tail(1)
+            assert np.linalg.norm(C0.astype(np.float64) - C1) / np.linalg.norm(C0.astype(np.float64)) <= 1e-6
+    finally:
+        lib.la_gemm_set_stream_tail(-1); lib.la_gemm_set_raster(-1)
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 

@@ -423,6 +423,7 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
         case 3: return gemm_tma_launch<T, Shape64_8x4, false>(C, At, B, M, K, N, st);
         case 4: return gemm_tma_launch<T, Shape64_4x8, false>(C, At, B, M, K, N, st);
         case 5: return gemm_tma_launch<T, Shape64_8x8d, false>(C, At, B, M, K, N, st);
+        case 13: return std::is_same<T, double>::value ? gemm_tma_launch<T, Shape64_8x8d, false>(C, At, B, M, K, N, st) : gemm_tma_launch<T, Shape64_8x4, false>(C, At, B, M, K, N, st);
         }
     } else {
     LA_TRY(la_transpose_raw32((uint32_t*)At, (const uint32_t*)A, M, K, st));
@@ -433,6 +434,7 @@ la_status gemm_tma(T* C, const T* A, const T* B, size_t M, size_t K, size_t N, c
         if (F) return gemm_tma_launch<T, Shape_16x8d, F>(C, At, B, M, K, N, st);  // integers: BK 16 (35.7 vs 30.4 Top/s: the IMAD body spills at BK 32)
         return gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);
     case 12: return gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);
+    case 13: return F ? gemm_tma_launch<T, Shape_16x8d, F>(C, At, B, M, K, N, st) : gemm_tma_launch<T, Shape_16x8, F>(C, At, B, M, K, N, st);   // the default shapes, at any size
     case 1: return gemm_tma_launch<T, Shape_16x8, false>(C, At, B, M, K, N, st);
     case 2: return gemm_tma_launch<T, Shape_8x8, F>(C, At, B, M, K, N, st);
     case 3: return gemm_tma_launch<T, Shape_8x8, false>(C, At, B, M, K, N, st);
@@ -474,7 +476,8 @@ extern "C" la_status la_get_gemm_mode(int* mode) {
     return LA_OK;
 }
 // Tuning hook used by tools/ and bench.py --sweep: picks the tile shape of the TMA engine
-// (0 = default).  -1 forces the generic engine.
+// (0 = default shape, used from the size where it beats the generic kernel; k > 0 = that shape at any size; 13 = the default
+// shapes at any size).  -1 forces the generic engine.
 extern "C" la_status la_gemm_set_variant(int v) { g_gemm_variant = v; return LA_OK; }
 extern "C" int la_gemm_last_engine(void) { return g_last_engine; }
 extern "C" int la_gemm_last_padded(void) { return g_last_padded; }
@@ -501,9 +504,17 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     const bool tma_ok = la_dtype_size(dtype) >= 4 && g_gemm_variant >= 0 && M % chunk == 0 && N % chunk == 0 && la_aligned16(A) && la_aligned16(B) && la_aligned16(C) &&
                         M >= 64 && N >= 64 && K >= 16 && M < (1u << 31) && N < (1u << 31) && K < (1u << 31);
     g_last_padded = 0;
-    const bool big = (double)M * (double)N * (double)K >= 134217728.0;      // 512^3 multiply-adds
-    // AUTO: the tensor engine for problems big enough to amortise its pre-pass
-    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && big))) {
+    const double macs = (double)M * (double)N * (double)K;
+    const bool big = macs >= 134217728.0;                                   // 512^3 multiply-adds
+    // The TMA-fed SIMT kernel gives one CTA a 256 x 128 (8-byte types: 128 x 128) tile: with fewer tiles than SMs it runs at
+    // the speed of one SM per tile (K x 0.135 us whatever M and N), and the generic kernel's 64 x 64 tiles fill the GPU
+    // better.  Measured crossovers: f32 1536^3 (72 tiles), i32 ~1800^3, f64 ~900^3 (tools/gemm_generic_vs_tma.py); e.g.
+    // 512^3 f32 84.5 -> 32.1 us, i32 145 -> 37 us.  An explicit tile-shape variant (tuning hook) always takes the TMA kernel.
+    const size_t tma_tiles = la_dtype_size(dtype) == 8 ? ((M + 127) / 128) * ((N + 127) / 128) : ((M + 255) / 256) * ((N + 127) / 128);
+    const bool tma_worth = g_gemm_variant > 0 || tma_tiles >= (la_dtype_size(dtype) == 8 ? 48u : 96u);
+    // AUTO: the tensor engine for problems big enough to amortise its pre-pass and its flag read-back (its floor is ~37 us:
+    // level with the generic kernel at 640^3)
+    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && macs >= 268435456.0))) {
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 2; return LA_OK; }
@@ -535,7 +546,7 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
         g_last_padded = 1;
         return ps;
     }
-    if (tma_ok) {
+    if (tma_ok && tma_worth) {
         g_last_engine = 1;
         if (dtype == LA_F32) return gemm_tma<float>((float*)C, (const float*)A, (const float*)B, M, K, N, st);
         if (dtype == LA_F64) return gemm_tma<double>((double*)C, (const double*)A, (const double*)B, M, K, N, st);

@@ -232,19 +232,23 @@ def test_matmat_f32_tolerance(la):
         check_f32_gemm(la, gen.values("f32", M * K, 23), gen.values("f32", K * N, 24), M, K, N, (M, K, N))
 
 
-@pytest.mark.parametrize("variant", list(range(0, 11)) + [12, -1])
+@pytest.mark.parametrize("variant", list(range(0, 11)) + [12, 13, -1])
 def test_matmat_every_engine_variant(la, variant):
     """All tile shapes of the TMA engine (and the generic engine, -1) on shapes with ragged
-    edge tiles and a K tail."""
+    edge tiles and a K tail.  Variant 0 is the default policy: the generic kernel while the TMA kernel's
+    big tiles would leave most SMs idle (fewer than 96 of them), the TMA kernel from there on."""
     P = oracle.port(); lib = la._lib.lib
     lib.la_gemm_set_variant(variant)
     la._lib.call("la_set_gemm_mode", la._lib.GEMM_SIMT)
     try:
-        for M, K, N in ((512, 256, 384), (388, 1001, 260)):
+        for M, K, N in ((512, 256, 384), (388, 1001, 260), (2560, 64, 1280)):
             check_f32_gemm(la, gen.values("f32", M * K, 25), gen.values("f32", K * N, 26), M, K, N, (variant, M, K, N))
+            want = 0 if variant < 0 else 1 if (variant > 0 or M == 2560) else 0
+            assert lib.la_gemm_last_engine() == want, (variant, M, K, N)
             a = gen.values("i32", M * K, 27); b = gen.values("i32", K * N, 28)
             C = la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)
             assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (variant, M, K, N)
+            assert lib.la_gemm_last_engine() == want
     finally:
         lib.la_gemm_set_variant(0)
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
@@ -281,7 +285,7 @@ def test_matmat_3xtf32_leaves_non_finite_and_extreme_operands_to_simt(la):
             a = gen.values("f32", M * K, 45).copy(); b = gen.values("f32", K * N, 46).copy()
             (a if where == "a" else b)[777] = poison
             C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
-            assert lib.la_gemm_last_engine() == 1, (poison, "tensor engine should have declined")
+            assert lib.la_gemm_last_engine() in (0, 1), (poison, "tensor engine should have declined")
             with np.errstate(invalid="ignore", over="ignore"):
                 ref = (a.reshape(M, K).astype(np.float64) @ b.reshape(K, N).astype(np.float64)).reshape(-1)
             assert np.array_equal(np.isnan(C), np.isnan(ref)) and np.array_equal(np.isinf(C), np.isinf(ref)), poison
@@ -298,7 +302,7 @@ def test_matmat_auto_mode_picks_the_engine_by_size(la):
     la._lib.call("la_get_gemm_mode", __import__("ctypes").byref(mode))
     assert mode.value == la._lib.GEMM_AUTO
     check_f32_gemm(la, gen.values("f32", 256 * 256, 49), gen.values("f32", 256 * 256, 50), 256, 256, 256, "auto small")
-    assert lib.la_gemm_last_engine() == 1          # below 512^3: SIMT
+    assert lib.la_gemm_last_engine() == 0          # small: the generic SIMT kernel (the TMA kernel's 256 x 128 tiles would use 2 SMs)
     check_f32_gemm(la, gen.values("f32", 512 * 1024, 51), gen.values("f32", 1024 * 512, 52), 512, 1024, 512, "auto large")
     assert lib.la_gemm_last_engine() == 2          # tensor cores
     a = gen.values("i32", 512 * 1024, 53); b = gen.values("i32", 1024 * 512, 54)
@@ -474,7 +478,7 @@ def test_matmat_3xtf32_stream_tail_meets_the_bar_and_is_reproducible(la, raster)
 
 
 # ------------------------------------------------------------------ 8-byte element types on the TMA-fed SIMT engine
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 13])
 def test_matmat_64bit_types_on_the_tma_engine(la, variant):
     """f64 (DFMA, k ascending, one fused multiply-add per k) and u64/i64 (wrapping) through gemm_tma_kernel's 8-byte
     instantiation: interior and ragged edge tiles, a K tail, every tile shape.  Integers bit-exact; f64 against the oracle's
@@ -482,15 +486,16 @@ def test_matmat_64bit_types_on_the_tma_engine(la, variant):
     P = oracle.port(); lib = la._lib.lib
     lib.la_gemm_set_variant(variant)
     try:
-        for M, K, N in ((512, 256, 384), (386, 1001, 262), (64, 16, 64)):
+        for M, K, N in ((512, 256, 384), (386, 1001, 262), (64, 16, 64), (1024, 32, 1024)):
+            want = 1 if (variant > 0 or M == 1024) else 0          # variant 0: by size (48 tiles of 128 x 128 and up)
             for name in ("u64", "i64"):
                 a = gen.values(name, M * K, 91); b = gen.values(name, K * N, 92)
                 C = la.Matrix.from_vec(a, M, K, dt(la, name)) * la.Matrix.from_vec(b, K, N, dt(la, name))
-                assert lib.la_gemm_last_engine() == 1, (name, M, K, N)
+                assert lib.la_gemm_last_engine() == want, (name, M, K, N)
                 assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N)), (variant, name, M, K, N)
             a = gen.values("f64", M * K, 93); b = gen.values("f64", K * N, 94)
             C = (la.Matrix.from_vec(a, M, K, "f64") * la.Matrix.from_vec(b, K, N, "f64")).to_vec()
-            assert lib.la_gemm_last_engine() == 1
+            assert lib.la_gemm_last_engine() == want
             ref = P.mul_mat_mat(a, b, M, K, N)
             scale = (np.abs(a.reshape(M, K)) @ np.abs(b.reshape(K, N))).reshape(-1)
             assert np.max(np.abs(C - ref) / scale) < 1e-13, (variant, M, K, N)
@@ -501,7 +506,7 @@ def test_matmat_64bit_types_on_the_tma_engine(la, variant):
         M, K, N = 515, 1031, 523
         a = gen.values("u64", M * K, 97); b = gen.values("u64", K * N, 98)
         C = la.Matrix.from_vec(a, M, K, "u64") * la.Matrix.from_vec(b, K, N, "u64")
-        assert lib.la_gemm_last_padded() == 1 and lib.la_gemm_last_engine() == 1
+        assert lib.la_gemm_last_padded() == 1 and lib.la_gemm_last_engine() == (1 if variant > 0 else 0)
         assert same(C.to_vec(), P.mul_mat_mat(a, b, M, K, N))
     finally:
         lib.la_gemm_set_variant(0)

@@ -115,6 +115,8 @@ lib.la_gemm_set_variant.argtypes = [_I]
 lib.la_gemm_set_variant.restype = ctypes.c_int
 lib.la_gemm_tc_set_variant.argtypes = [_I]
 lib.la_gemm_tc_set_variant.restype = ctypes.c_int
+lib.la_gemm_tc_set_tile_n.argtypes = [_I]
+lib.la_gemm_tc_set_tile_n.restype = ctypes.c_int
 lib.la_gemm_set_stream_tail.argtypes = [_I]
 lib.la_gemm_set_stream_tail.restype = ctypes.c_int
 lib.la_gemm_set_raster.argtypes = [_I]

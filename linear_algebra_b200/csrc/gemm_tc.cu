@@ -392,11 +392,15 @@ __device__ __forceinline__ bool tc_segment(const TcPlan& p, int item, int seg, i
     return c_begin < c_end;
 }
 
+// BN: columns of the pair's tile (a multiple of 32 up to 256): 256 unless another width packs the waves better (tc_launch_2cta)
+template <int BN>
 __global__ void __launch_bounds__(TC3_THREADS, 1)
 gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                         const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
                         int M, int N, const TcPlan plan) {
     constexpr int STAGES = TC3_STAGES;
+    constexpr int HC = BN / 2;                                   // B rows held by each CTA = accumulator columns drained by each epilogue half
+    static_assert(BN % 32 == 0 && BN >= 64 && BN <= 256, "pair tile width");
     extern __shared__ uint8_t smem_raw[];
     __shared__ alignas(8) uint64_t full_bar[STAGES];     // used in the leader: both CTAs' slabs have landed
     __shared__ alignas(8) uint64_t empty_bar[STAGES];    // per CTA: the pair's MMAs are done with this slot
@@ -439,24 +443,24 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
                 for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg) {
                     int tile_m, tile_n;
                     la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
-                    const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * 256;
+                    const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * BN;
                     const int kb_end = min(ce * plan.chunk_kb, num_kb);
                     for (int kb = cb * plan.chunk_kb; kb < kb_end; ++kb, ++it) {
                         const int s = it % STAGES;
                         const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
                         mbar_wait(&empty_bar[s], ph ^ 1u);
                         uint8_t* st = ring_ptr + (size_t)s * TC3_STAGE_BYTES;
-                        if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * TC3_STAGE_BYTES);     // my slabs + the peer's
+                        if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * (2u * TC3_TILE + 2u * HC * TC_BK * 4u));     // my slabs + the peer's
                         tma_load_2d_2sm(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
                         tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
-                        tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
-                        tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * 128);
+                        tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                        tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
                     }
                 }
             }
         } else if (warp == 9 && crank == 0) {
             // ---------------- MMA issuer (leader CTA only)
-            constexpr uint32_t idesc = umma_idesc_tf32(256, 256);
+            constexpr uint32_t idesc = umma_idesc_tf32(256, BN);
             int it = 0, cc = 0;                                       // k-blocks / chunks consumed so far, over all segments
             int tile, cb, ce;
             for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg)
@@ -496,20 +500,20 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
         // ---------------- epilogue warps 0..7 (both CTAs; each drains its own tensor memory)
         asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
         const int quad = warp & 3, half = warp >> 2;
-        float acc[128];
+        float acc[HC];
         int cc = 0;
         int tile, cb, ce;
         for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg) {
 #pragma unroll
-        for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+        for (int i = 0; i < HC; ++i) acc[i] = 0.f;
         for (int c = cb; c < ce; ++c, ++cc) {
             const int b = cc & 1;
             const uint32_t use = (uint32_t)(cc >> 1);
             mbar_wait(&acc_full_bar[b], use & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * 256 + half * 128);
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * 256 + half * HC);
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
+            for (int j = 0; j < HC / 64; ++j) {
                 uint32_t v0[32], v1[32];
                 tmem_ld32(taddr + j * 64, v0);
                 tmem_ld32(taddr + j * 64 + 32, v1);
@@ -520,20 +524,36 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
                     acc[j * 64 + 32 + i] += __uint_as_float(v1[i]);
                 }
             }
+            if constexpr (HC % 64 >= 32) {
+                constexpr int o = HC / 64 * 64;
+                uint32_t v0[32];
+                tmem_ld32(taddr + o, v0);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[o + i] += __uint_as_float(v0[i]);
+            }
+            if constexpr (HC % 32 == 16) {
+                constexpr int o = HC / 32 * 32;
+                uint32_t v0[16];
+                tmem_ld16(taddr + o, v0);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 16; ++i) acc[o + i] += __uint_as_float(v0[i]);
+            }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive_on_leader(&acc_empty_bar[b]);
         }
         int tile_m, tile_n;
         la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
-        const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * 256;
+        const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * BN;
         const bool whole = (cb == 0 && ce == plan.num_chunks);       // otherwise one of (at most) two partial sums of this tile
         const int row = m0 + quad * 32 + lane;
         if (row < M) {
-            float* crow = C + (size_t)row * N + n0 + half * 128;
+            float* crow = C + (size_t)row * N + n0 + half * HC;
 #pragma unroll
-            for (int q = 0; q < 32; ++q) {
-                const int n = n0 + half * 128 + q * 4;
+            for (int q = 0; q < HC / 4; ++q) {
+                const int n = n0 + half * HC + q * 4;
                 if (n < N) {
                     const float4 v = make_float4(acc[q * 4], acc[q * 4 + 1], acc[q * 4 + 2], acc[q * 4 + 3]);
                     if (whole) __stcs(reinterpret_cast<float4*>(crow + q * 4), v);
@@ -669,15 +689,25 @@ la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, cons
 
 int g_tc_stream = -1;           // la_gemm_set_stream_tail: -1 by the gain model below, 0 never, 1 whenever possible
 
-la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
+int g_tc_bn = 0;                // la_gemm_tc_set_tile_n: 0 = pick by wave count, else 256 / 224 / 192
+
+// Wave-times (in units of a 256-wide tile's) that `tiles` tiles of width bn take on `pairs` CTA pairs, with the half-length
+// last wave the split gives when the remainder fits half of the GPU.
+static double tc_cost(long long tiles, long long pairs, int bn, bool can_split) {
+    const long long waves = tiles / pairs, rest = tiles % pairs;
+    const double last = rest == 0 ? 0.0 : (can_split && 2 * rest <= pairs) ? 0.5 : 1.0;
+    return ((double)waves + last) * (double)bn / 256.0;
+}
+
+template <int BN>
+la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs) {
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
     LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128));
-    LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, 128)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, 128));
-    LA_CUDA(cudaFuncSetAttribute(gemm_3xtf32_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
-    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
-    const size_t ptm = (M + 255) / 256, tn = (N + 255) / 256;
+    LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN / 2)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, BN / 2));
+    auto kern = gemm_3xtf32_2cta_kernel<BN>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
+    const size_t ptm = (M + 255) / 256, tn = (N + BN - 1) / BN;
     const long long tiles = (long long)(ptm * tn);
-    const long long pairs = info->sm_count / 2;                 // CTA pairs in flight (one per SM pair)
 
     TcPlan plan = {};
     plan.pair_tiles_m = (int)ptm; plan.tiles_n = (int)tn; plan.raster_group = la_gemm_raster_group(ptm);
@@ -693,8 +723,7 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
     // whole tiles do, which keeps the operand slabs shared through L2.  (Cutting the last full wave plus the remainder into
     // equal spans would balance any remainder, but the spans then start at staggered K positions, the CTAs stop sharing
     // slabs in L2 and the kernel turns HBM-bound: measured 11 % slower at 2048 x 8192 x 8192.)
-    const long long waves = tiles / pairs, rest = tiles % pairs;
-    (void)waves;
+    const long long rest = tiles % pairs;
     if (rest > 0 && 2 * rest <= pairs && plan.num_chunks >= 2 && g_tc_stream != 0) {
         plan.stream_tiles = (int)rest;
         plan.stream_items = (int)(2 * rest);
@@ -702,7 +731,7 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
         // zero the tiles that receive two partial sums.  m-major order: they are the last tile columns (the first of them
         // possibly shared with whole tiles, which simply overwrite); banded order: all of C.
         if (plan.raster_group <= 0 || plan.raster_group >= plan.pair_tiles_m) {
-            const size_t first_col = ((size_t)plan.dp_items / ptm) * 256;
+            const size_t first_col = ((size_t)plan.dp_items / ptm) * BN;
             LA_CUDA(cudaMemset2DAsync(C + first_col, N * sizeof(float), 0, (N - first_col) * sizeof(float), M, st));
         } else {
             LA_CUDA(cudaMemsetAsync(C, 0, M * N * sizeof(float), st));
@@ -715,8 +744,32 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    LA_CUDA(cudaLaunchKernelEx(&cfg, gemm_3xtf32_2cta_kernel, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, plan));
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, plan));
     return LA_OK;
+}
+
+// Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,
+// 1024 x 8192 x 8192, is 128 tiles = 1.73 waves -> 2 wave-times at width 256, but 148 tiles = exactly 2 waves of 0.875 at 224
+// (measured 0.666 -> 0.645 ms).
+la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    const long long pairs = info->sm_count / 2;                 // CTA pairs in flight (one per SM pair)
+    const long long ptm = (long long)((M + 255) / 256);
+    const bool can_split = g_tc_stream != 0 && K > 32;
+    int bn = 256;
+    if (g_tc_bn) bn = g_tc_bn;
+    else {
+        double best = tc_cost(ptm * (long long)((N + 255) / 256), pairs, 256, can_split);
+        for (int cand : {224, 192}) {
+            const double c = tc_cost(ptm * (long long)((N + cand - 1) / cand), pairs, cand, can_split);
+            if (c < 0.90 * best) { best = c; bn = cand; }       // a 224-wide tile costs ~7 % more per flop (8192^3: 4.86 -> 5.23 ms at equal wave count): it must buy more than that
+        }
+    }
+    switch (bn) {
+    case 224: return tc_launch_2cta_bn<224>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    case 192: return tc_launch_2cta_bn<192>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    default:  return tc_launch_2cta_bn<256>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    }
 }
 
 int g_tc_variant = 0;
@@ -730,6 +783,7 @@ extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA
 // i32 37.6 -> 31.8 ms); at M <= 8192 the two orders time the same, so the plain order stays there.
 static int g_raster_group = -1;                         // -1: by size; 0: m-major; g > 0: bands of g tile rows
 int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m > 32 ? 8 : 0); }
+extern "C" la_status la_gemm_tc_set_tile_n(int bn) { g_tc_bn = (bn == 224 || bn == 192 || bn == 256) ? bn : 0; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_set_stream_tail(int mode) { g_tc_stream = mode; return LA_OK; }   // tuning hook: -1 auto, 0 off, 1 on
 extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; return LA_OK; }   // tuning hook
 

@@ -444,6 +444,29 @@ def test_matmat_banded_tile_order_changes_nothing(la, group):
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+@pytest.mark.parametrize("bn", [224, 192])
+def test_matmat_3xtf32_narrower_tiles_change_nothing(la, bn):
+    """la_gemm_tc_set_tile_n: pair tiles 256 x 224 / 256 x 192 (picked when they pack the waves better, e.g. the 8-GPU shard
+    1024 x 8192 x 8192).  Every output is computed by the same chain of MMAs whatever the tile width, so with the K-split of
+    the last wave off the results are bit-identical to the 256-wide tiles'; with it on they meet the same bar."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    try:
+        for M, K, N in ((512, 256, 1000), (1300, 1004, 2300), (256, 96, 224 * 3), (1024, 64, 8192)):
+            a = gen.values("f32", M * K, 67); b = gen.values("f32", K * N, 68)
+            A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+            lib.la_gemm_set_stream_tail(0)
+            lib.la_gemm_tc_set_tile_n(256); C256 = (A * B).to_vec()
+            lib.la_gemm_tc_set_tile_n(bn); Cbn = (A * B).to_vec()
+            assert lib.la_gemm_last_engine() == 2
+            assert same(C256, Cbn), (bn, M, K, N)
+            lib.la_gemm_set_stream_tail(-1)
+            check_f32_gemm(la, a, b, M, K, N, ("tile width", bn, M, K, N))
+    finally:
+        lib.la_gemm_tc_set_tile_n(0); lib.la_gemm_set_stream_tail(-1)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
 @pytest.mark.parametrize("raster", [0, 3])
 def test_matmat_3xtf32_stream_tail_meets_the_bar_and_is_reproducible(la, raster):
     """The ragged last wave of the tensor engine cut into equal spans (la_gemm_set_stream_tail): tiles then get up to two

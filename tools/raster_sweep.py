@@ -6,7 +6,7 @@ sys.path.insert(0, ".")
 import linear_algebra_b200 as la
 la.init(0); lib = la._lib
 groups = [int(g) for g in sys.argv[1:]] or [0, 4, 8, 16]
-hook = lib.lib.la_gemm_set_stream_tail if os.environ.get("KNOB") == "stream" else lib.lib.la_gemm_set_raster
+hook = {"stream": lib.lib.la_gemm_set_stream_tail, "bn": lib.lib.la_gemm_tc_set_tile_n}.get(os.environ.get("KNOB"), lib.lib.la_gemm_set_raster)
 def shape(spec):
     d = [int(x) for x in spec.split("x")]
     return (d[0], d[0], d[0]) if len(d) == 1 else tuple(d)

@@ -210,9 +210,10 @@ la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const
  *                  FP32 accumulation in 64-wide chunks (32-wide for K <= 128; meets the same f32 tolerance as the SIMT
  *                  engine).  Falls back to SIMT for shapes it does not cover
  *                  (M, N >= 128, K >= 32, all multiples of 4) and whenever an operand holds a NaN, an
- *                  infinity or a magnitude outside [2^-100, 2^100] (the call reads one flag back, so it
- *                  blocks for the length of the pre-pass).
- *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 from 2^28 multiply-adds up (about 640^3, where it overtakes the SIMT kernels),
+ *                  infinity or a magnitude outside [2^-100, 2^100] (the call reads one flag back, so the
+ *                  HOST blocks for the length of the pre-pass; the product itself is already queued behind
+ *                  the pre-pass, so the GPU does not idle meanwhile).
+ *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 from 512^3 multiply-adds up (where it overtakes the SIMT kernels),
  *                  LA_GEMM_SIMT below.
  * 8/16/32-bit integer products of that size run as exact byte-limb products on the INT8 tensor cores
  * (bit-identical results, mod 2^n) unless LA_GEMM_SIMT is selected.

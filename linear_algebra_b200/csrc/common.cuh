@@ -43,6 +43,8 @@ la_status la_scratch(cudaStream_t stream, size_t bytes, void** ptr);
 // One zero-copy flag word per (device, stream): kernels store into *dev_ptr, the host reads
 // *host_ptr after waiting for them (no device-to-host copy involved).
 la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsigned** dev_ptr);
+// One event (no timing) per (device, stream), for waiting on a point inside a chain of launches.
+la_status la_stream_event(cudaStream_t stream, cudaEvent_t* event);
 
 int la_gemm_raster_group(size_t pair_tiles_m);   // gemm_tc.cu: tile rows per band of the tensor engines' tile order (0 = m-major; tuning hook la_gemm_set_raster)
 

@@ -512,9 +512,9 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     // 512^3 f32 84.5 -> 32.1 us, i32 145 -> 37 us.  An explicit tile-shape variant (tuning hook) always takes the TMA kernel.
     const size_t tma_tiles = la_dtype_size(dtype) == 8 ? ((M + 127) / 128) * ((N + 127) / 128) : ((M + 255) / 256) * ((N + 127) / 128);
     const bool tma_worth = g_gemm_variant > 0 || tma_tiles >= (la_dtype_size(dtype) == 8 ? 48u : 96u);
-    // AUTO: the tensor engine for problems big enough to amortise its pre-pass and its flag read-back (its floor is ~37 us:
-    // level with the generic kernel at 640^3)
-    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && macs >= 268435456.0))) {
+    // AUTO: the tensor engine for problems big enough to amortise its pre-pass (its floor is ~27 us: it overtakes the generic
+    // kernel at 512^3, 27.4 against 32.2 us)
+    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && big))) {
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 2; return LA_OK; }

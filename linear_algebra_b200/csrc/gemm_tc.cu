@@ -830,10 +830,14 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
     *flag_host = 0u;                                            // no kernel of this stream that writes it is in flight (each call waits below)
     LA_TRY(la_tc_split_a(a_hi, a_lo, A, M, K, flag, st));
     LA_TRY(la_tc_split_bt(b_hi, b_lo, B, K, N, flag, st));
-    // Were all operands inside the range the split is faithful for?  (wait for the pre-pass, read the word)
-    LA_CUDA(cudaStreamSynchronize(st));
-    if (*flag_host) return LA_OK;                               // inf / NaN / extreme exponents: plain f32 arithmetic instead
+    // Were all operands inside the range the split is faithful for?  The product is launched straight behind the pre-pass, so
+    // the GPU never idles while the host waits for the pre-pass (only) and reads the word.  If it is set -- inf / NaN / extreme
+    // exponents -- the caller runs the plain f32 engine next in the stream, which overwrites whatever this launch left in C.
+    cudaEvent_t split_done; LA_TRY(la_stream_event(st, &split_done));
+    LA_CUDA(cudaEventRecord(split_done, st));
     LA_TRY(la_tc_run(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st));
+    LA_CUDA(cudaEventSynchronize(split_done));
+    if (*flag_host) return LA_OK;
     *handled = true;
     return LA_OK;
 }

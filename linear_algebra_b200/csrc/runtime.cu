@@ -45,6 +45,7 @@ struct DeviceState {
     LaDeviceInfo info;
     std::map<cudaStream_t, std::pair<void*, size_t>> scratch;   // per stream: block, capacity
     std::map<cudaStream_t, unsigned*> host_flags;                // per stream: one mapped, page-locked word
+    std::map<cudaStream_t, cudaEvent_t> events;                  // per stream: one timing-less event
 };
 std::mutex g_mu;
 std::map<int, DeviceState*> g_devices;
@@ -123,6 +124,16 @@ la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsign
     void* d = nullptr;
     LA_CUDA(cudaHostGetDevicePointer(&d, slot, 0));
     *host_ptr = slot; *dev_ptr = (unsigned*)d;
+    return LA_OK;
+}
+
+la_status la_stream_event(cudaStream_t stream, cudaEvent_t* event) {
+    DeviceState* st = nullptr;
+    LA_TRY(device_state(&st));
+    std::lock_guard<std::mutex> lk(g_mu);
+    cudaEvent_t& slot = st->events[stream];
+    if (!slot) LA_CUDA(cudaEventCreateWithFlags(&slot, cudaEventDisableTiming));
+    *event = slot;
     return LA_OK;
 }
 

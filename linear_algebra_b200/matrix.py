@@ -127,12 +127,16 @@ class Matrix:
         with open(path, "rb") as f:
             return Matrix.read_from_file(f, dtype)
 
-    def __repr__(self):                           # matrix.rs:289-317
+    def __repr__(self):
+        """Debug form; large matrices are abbreviated (see Vector.__repr__)."""
+        if self.row_count * self.col_count <= 256:
+            return self.__str__()
+        return "Mat%dx%d %r" % (self.row_count, self.col_count, self.data)
+
+    def __str__(self):                            # matrix.rs:289-317: every element
         v = self.to_vec()
         rows = ["\t " + ", ".join(repr(x.item()) for x in v[r * self.col_count:(r + 1) * self.col_count]) for r in range(self.row_count)]
         return "Mat%dx%d {\n%s\n}\n" % (self.row_count, self.col_count, "\n".join(rows))
-
-    __str__ = __repr__
 
 
 def _mul_helper(a, b, a_row_count, a_col_count, b_col_count):     # matrix.rs:240-265

@@ -333,10 +333,16 @@ class Vector:
             return Vector.read_from_file(f, dtype)
 
     # ---- formatting (vector.rs:678-698)
-    def __repr__(self):
+    def __str__(self):                            # Display, vector.rs:678-687: every element
         return "{ " + ", ".join(repr(x.item()) for x in self.to_vec()) + " }"
 
-    __str__ = __repr__
+    def __repr__(self):
+        """Debug form.  Long vectors are abbreviated (a failing `assert a == b` in a test must not format 2^28 elements)."""
+        if self._len <= 64:
+            return self.__str__()
+        head = ", ".join(repr(x.item()) for x in self.slice_to_vec(0, 8))
+        tail = ", ".join(repr(x.item()) for x in self.slice_to_vec(self._len - 4, 4))
+        return "{ %s, ... (%d elements of %s) ..., %s }" % (head, self._len, self.dtype.name, tail)
 
 
 def _read_exact(f, n):

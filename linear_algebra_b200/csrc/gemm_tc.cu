@@ -782,10 +782,10 @@ extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA
 // M = 16384, where the kernel then waits on HBM (16384^3 f32 42.6 ms).  Bands of 8 tile rows keep a wave on ~17 row/column
 // slabs whatever the size: 4.57 GB at 8192^3, and -- the engines being power-limited -- less DRAM traffic is also time:
 // fresh-process runs (tools/fresh_gemm.py: 3 warm-ups + 5 steps, as bench.py times) f32 8192^3 4.117 -> 3.969 ms,
-// i32 3.498 -> 3.274 ms, 16384^3 f32 42.6 -> 36.5 ms; no difference at 4096^3 (16 tile rows), so bands start above that.
+// i32 3.498 -> 3.274 ms, 16384^3 f32 42.6 -> 36.5 ms; no difference at 4096^3 (16 tile rows; 4096 x 8192 x 8192: 2.108 -> 2.092 ms), below that m-major is better (2048 x 8192 x 8192: 1.110 vs 1.138 ms).
 static int initial_raster_group() { const char* e = getenv("LA_GEMM_RASTER"); return e ? atoi(e) : -1; }
 static int g_raster_group = initial_raster_group();     // -1: by size; 0: m-major; g > 0: bands of g tile rows (LA_GEMM_RASTER in the environment)
-int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m > 16 ? 8 : 0); }
+int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m >= 16 ? 8 : 0); }
 extern "C" la_status la_gemm_tc_set_tile_n(int bn) { g_tc_bn = (bn == 224 || bn == 192 || bn == 256) ? bn : 0; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_set_stream_tail(int mode) { g_tc_stream = mode; return LA_OK; }   // tuning hook: -1 auto, 0 off, 1 on
 extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; return LA_OK; }   // tuning hook

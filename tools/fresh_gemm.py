@@ -1,15 +1,16 @@
 """One GEMM configuration in a fresh process, timed the way bench.py times the headline (3 warm-ups, 5 timed steps, CUDA events):
-   python tools/fresh_gemm.py <dtype> <n> [env LA_GEMM_RASTER=...]"""
+   python tools/fresh_gemm.py <dtype> <n | MxKxN> [env LA_GEMM_RASTER=...]"""
 import os, sys
 sys.path.insert(0, ".")
 import linear_algebra_b200 as la
 la.init(0); lib = la._lib
-dt = sys.argv[1]; n = int(sys.argv[2])
-A = la.Vector.synth(1, n * n, dt); B = la.Vector.synth(2, n * n, dt); C = la.Vector.uninitialized(n * n, dt)
-f = lambda: lib.call("la_mul_mat_mat", la.parameter(dt).code, C.ptr, A.ptr, B.ptr, n, n, n, None)
+dt = sys.argv[1]; dims = [int(x) for x in sys.argv[2].split("x")]
+M, K, N = dims if len(dims) == 3 else (dims[0],) * 3
+A = la.Vector.synth(1, M * K, dt); B = la.Vector.synth(2, K * N, dt); C = la.Vector.uninitialized(M * N, dt)
+f = lambda: lib.call("la_mul_mat_mat", la.parameter(dt).code, C.ptr, A.ptr, B.ptr, M, K, N, None)
 for _ in range(3): f()
 la.synchronize()
 e0, e1 = la.Event(), la.Event(); e0.record()
 for _ in range(5): f()
 e1.record(); ms = e0.elapsed_ms(e1) / 5
-print("%s %d^3 raster=%s engine %d: %.4f ms  %.1f T(FL)OP/s" % (dt, n, os.environ.get("LA_GEMM_RASTER", "auto"), lib.lib.la_gemm_last_engine(), ms, 2.0 * n ** 3 / ms / 1e9), flush=True)
+print("%s %dx%dx%d raster=%s engine %d: %.4f ms  %.1f T(FL)OP/s" % (dt, M, K, N, os.environ.get("LA_GEMM_RASTER", "auto"), lib.lib.la_gemm_last_engine(), ms, 2.0 * M * K * N / ms / 1e9), flush=True)

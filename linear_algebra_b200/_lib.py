@@ -115,6 +115,10 @@ lib.la_gemm_set_variant.argtypes = [_I]
 lib.la_gemm_set_variant.restype = ctypes.c_int
 lib.la_gemm_tc_set_variant.argtypes = [_I]
 lib.la_gemm_tc_set_variant.restype = ctypes.c_int
+lib.la_gemm_tc_set_chunk.argtypes = [_I]
+lib.la_gemm_tc_set_chunk.restype = ctypes.c_int
+lib.la_gemm_tc_set_cross.argtypes = [_I]
+lib.la_gemm_tc_set_cross.restype = ctypes.c_int
 lib.la_gemm_tc_set_tile_n.argtypes = [_I]
 lib.la_gemm_tc_set_tile_n.restype = ctypes.c_int
 lib.la_gemm_set_stream_tail.argtypes = [_I]

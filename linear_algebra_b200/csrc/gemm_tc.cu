@@ -25,6 +25,7 @@
 // detects anything outside [2^-100, 2^100] (or NaN) and the call then falls back to the SIMT engine,
 // so the tensor engine never changes the result class of a product.
 // Roofline: tensor pipe (tf32), 3 MMAs per useful product.
+#include <cuda_bf16.h>
 #include "tc_common.cuh"
 
 la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st);   // transpose.cu
@@ -392,11 +393,24 @@ __device__ __forceinline__ bool tc_segment(const TcPlan& p, int item, int seg, i
     return c_begin < c_end;
 }
 
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {       // kind::f16: D = f32, A = B = bf16, both K-major
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
 // BN: columns of the pair's tile (a multiple of 32 up to 256): 256 unless another width packs the waves better (tc_launch_2cta)
-template <int BN>
+// BF16X: the two cross terms hi*lo and lo*hi as bf16 MMAs (twice the tf32 rate) on bf16(hi), bf16(x - hi) planes: the
+// `lo` maps then describe the bf16(hi) planes and the `x` maps the bf16(x - hi) planes; 64-byte rows, SWIZZLE_64B.
+template <int BN, bool BF16X>
 __global__ void __launch_bounds__(TC3_THREADS, 1)
 gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
                         const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
+                        const __grid_constant__ CUtensorMap map_a_x, const __grid_constant__ CUtensorMap map_b_x,
                         int M, int N, const TcPlan plan) {
     constexpr int STAGES = TC3_STAGES;
     constexpr int HC = BN / 2;                                   // B rows held by each CTA = accumulator columns drained by each epilogue half
@@ -455,6 +469,10 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
                         tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
                         tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
                         tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                        if constexpr (BF16X) {      // the second bf16 plane of each operand, in the upper half of its 16 KB slot
+                            tma_load_2d_2sm(st + TC3_TILE + TC3_TILE / 2, &map_a_x, &full_bar[s], kb * TC_BK, m0);
+                            tma_load_2d_2sm(st + 3 * TC3_TILE + TC3_TILE / 2, &map_b_x, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                        }
                     }
                 }
             }
@@ -479,14 +497,31 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     if (elect_one()) {
                         const uint32_t st = ring + (uint32_t)s * TC3_STAGE_BYTES;
-                        const uint64_t a_hi = umma_desc_k_sw128(st), a_lo = umma_desc_k_sw128(st + TC3_TILE);
-                        const uint64_t b_hi = umma_desc_k_sw128(st + 2 * TC3_TILE), b_lo = umma_desc_k_sw128(st + 3 * TC3_TILE);
+                        const uint64_t a_hi = umma_desc_k_sw128(st), b_hi = umma_desc_k_sw128(st + 2 * TC3_TILE);
+                        if constexpr (BF16X) {
+                            constexpr uint32_t idesc16 = umma_idesc_bf16(256, BN);
+                            const uint64_t a_hb = umma_desc_k_sw64(st + TC3_TILE), a_lb = umma_desc_k_sw64(st + TC3_TILE + TC3_TILE / 2);
+                            const uint64_t b_hb = umma_desc_k_sw64(st + 3 * TC3_TILE), b_lb = umma_desc_k_sw64(st + 3 * TC3_TILE + TC3_TILE / 2);
 #pragma unroll
-                        for (int kk = 0; kk < TC_BK / TC_UMMA_K; ++kk) {
-                            const uint64_t adv = (uint64_t)((kk * TC_UMMA_K * 4) >> 4);
-                            umma_tf32_2sm(tmem_d, a_hi + adv, b_lo + adv, idesc, (first && kk == 0) ? 0u : 1u);
-                            umma_tf32_2sm(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
-                            umma_tf32_2sm(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                            for (int kk = 0; kk < TC_BK / 16; ++kk) {            // bf16: 16 k = 32 bytes per instruction
+                                const uint64_t adv = (uint64_t)((kk * 16 * 2) >> 4);
+                                umma_bf16_2sm(tmem_d, a_hb + adv, b_lb + adv, idesc16, (first && kk == 0) ? 0u : 1u);
+                                umma_bf16_2sm(tmem_d, a_lb + adv, b_hb + adv, idesc16, 1u);
+                            }
+#pragma unroll
+                            for (int kk = 0; kk < TC_BK / TC_UMMA_K; ++kk) {
+                                const uint64_t adv = (uint64_t)((kk * TC_UMMA_K * 4) >> 4);
+                                umma_tf32_2sm(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                            }
+                        } else {
+                            const uint64_t a_lo = umma_desc_k_sw128(st + TC3_TILE), b_lo = umma_desc_k_sw128(st + 3 * TC3_TILE);
+#pragma unroll
+                            for (int kk = 0; kk < TC_BK / TC_UMMA_K; ++kk) {
+                                const uint64_t adv = (uint64_t)((kk * TC_UMMA_K * 4) >> 4);
+                                umma_tf32_2sm(tmem_d, a_hi + adv, b_lo + adv, idesc, (first && kk == 0) ? 0u : 1u);
+                                umma_tf32_2sm(tmem_d, a_lo + adv, b_hi + adv, idesc, 1u);
+                                umma_tf32_2sm(tmem_d, a_hi + adv, b_hi + adv, idesc, 1u);
+                            }
                         }
                         umma_commit_2sm(&empty_bar[s]);
                         if (kb == kb_end - 1) umma_commit_2sm(&acc_full_bar[b]);
@@ -589,22 +624,37 @@ __device__ __forceinline__ void split_one(float x, float& hi, float& lo, bool& b
     bad |= !(ax <= 1.2676506e30f) || (ax < 7.8886091e-31f && ax != 0.0f);      // outside [2^-100, 2^100] (or NaN)
 }
 
+// Cross-term planes of the tf32 + 2 x bf16 engine: bf16(hi) and bf16(x - hi), four values = 8 bytes each.
+__device__ __forceinline__ uint2 pack_bf16x4(float a, float b, float c, float d) {
+    const __nv_bfloat162 p0 = __floats2bfloat162_rn(a, b), p1 = __floats2bfloat162_rn(c, d);
+    return make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+}
+// BF16X: the `lo` plane (4 bytes per element) holds two bf16 planes instead, [bf16(hi) | bf16(x - hi)], n elements each.
+template <bool BF16X>
 __global__ void __launch_bounds__(256)
 split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4, unsigned* flag) {
     const size_t stride = (size_t)gridDim.x * 256;
     bool bad = false;
+    uint2* hb = reinterpret_cast<uint2*>(lo);
+    uint2* lb = hb + n4;                                  // n4 groups of 4 bf16 = the first plane
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
         const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
         float4 h, l;
         split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
         __stcs(reinterpret_cast<float4*>(hi) + i, h);
-        __stcs(reinterpret_cast<float4*>(lo) + i, l);
+        if constexpr (BF16X) {
+            __stcs(hb + i, pack_bf16x4(h.x, h.y, h.z, h.w));
+            __stcs(lb + i, pack_bf16x4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
+        } else {
+            __stcs(reinterpret_cast<float4*>(lo) + i, l);
+        }
     }
     if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;     // flag may live in mapped host memory: plain store
 }
 
 // B (K x N) -> Bt_hi, Bt_lo (N x K) in one pass: 64 x 64 tile through shared memory, 16-byte
 // loads along B's rows, 16-byte stores along Bt's rows.  K % 4 == 0 and N % 4 == 0.
+template <bool BF16X>
 __global__ void __launch_bounds__(256)
 split_transpose_kernel(float* __restrict__ bt_hi, float* __restrict__ bt_lo, const float* __restrict__ B, size_t K, size_t N,
                        unsigned tiles_n, unsigned* flag) {
@@ -630,8 +680,15 @@ split_transpose_kernel(float* __restrict__ bt_hi, float* __restrict__ bt_lo, con
         split_one(tile[q * 4 + 0][cc], h.x, l.x, bad); split_one(tile[q * 4 + 1][cc], h.y, l.y, bad);
         split_one(tile[q * 4 + 2][cc], h.z, l.z, bad); split_one(tile[q * 4 + 3][cc], h.w, l.w, bad);
         if (n0 + cc < N && k0 + q * 4 < K) {
-            __stcs(reinterpret_cast<float4*>(bt_hi + (n0 + cc) * K + k0 + q * 4), h);
-            __stcs(reinterpret_cast<float4*>(bt_lo + (n0 + cc) * K + k0 + q * 4), l);
+            const size_t at = (n0 + cc) * K + k0 + q * 4;
+            __stcs(reinterpret_cast<float4*>(bt_hi + at), h);
+            if constexpr (BF16X) {
+                uint2* hb = reinterpret_cast<uint2*>(bt_lo);
+                __stcs(hb + at / 4, pack_bf16x4(h.x, h.y, h.z, h.w));
+                __stcs(hb + (N * K + at) / 4, pack_bf16x4(tile[q * 4 + 0][cc] - h.x, tile[q * 4 + 1][cc] - h.y, tile[q * 4 + 2][cc] - h.z, tile[q * 4 + 3][cc] - h.w));
+            } else {
+                __stcs(reinterpret_cast<float4*>(bt_lo + at), l);
+            }
         }
     }
     if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;     // flag may live in mapped host memory: plain store
@@ -648,6 +705,19 @@ la_status tc_make_map(CUtensorMap* map, const float* base, size_t rows, size_t K
     CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled (3xTF32) failed with CUresult %d", (int)r);
+    return LA_OK;
+}
+
+// rows x K row-major bf16, box = box_rows x 32 (64 bytes), 64-byte swizzle
+la_status tc_make_map_bf16(CUtensorMap* map, const void* base, size_t rows, size_t K, int box_rows) {
+    EncodeTiledFn enc; LA_TRY(tc_get_encode(&enc));
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled (bf16 cross planes) failed with CUresult %d", (int)r);
     return LA_OK;
 }
 
@@ -689,6 +759,7 @@ la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, cons
 
 int g_tc_stream = -1;           // la_gemm_set_stream_tail: -1 by the gain model below, 0 never, 1 whenever possible
 
+int g_tc_chunk = 0;             // la_gemm_tc_set_chunk: k-blocks of 32 per accumulation chain (0 = by K)
 int g_tc_bn = 0;                // la_gemm_tc_set_tile_n: 0 = pick by wave count, else 256 / 224 / 192
 
 // Wave-times (in units of a 256-wide tile's) that `tiles` tiles of width bn take on `pairs` CTA pairs, with the half-length
@@ -699,12 +770,19 @@ static double tc_cost(long long tiles, long long pairs, int bn, bool can_split) 
     return ((double)waves + last) * (double)bn / 256.0;
 }
 
-template <int BN>
+template <int BN, bool BF16X>
 la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs) {
-    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo;
-    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128));
-    LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN / 2)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, BN / 2));
-    auto kern = gemm_3xtf32_2cta_kernel<BN>;
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x;
+    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN / 2));
+    if (BF16X) {        // the lo planes hold [bf16(hi) | bf16(x - hi)]
+        const __nv_bfloat16* a16 = reinterpret_cast<const __nv_bfloat16*>(a_lo); const __nv_bfloat16* b16 = reinterpret_cast<const __nv_bfloat16*>(b_lo);
+        LA_TRY(tc_make_map_bf16(&ma_lo, a16, M, K, 128)); LA_TRY(tc_make_map_bf16(&ma_x, a16 + M * K, M, K, 128));
+        LA_TRY(tc_make_map_bf16(&mb_lo, b16, N, K, BN / 2)); LA_TRY(tc_make_map_bf16(&mb_x, b16 + N * K, N, K, BN / 2));
+    } else {
+        LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, BN / 2));
+        ma_x = ma_lo; mb_x = mb_lo;
+    }
+    auto kern = gemm_3xtf32_2cta_kernel<BN, BF16X>;
     LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
     const size_t ptm = (M + 255) / 256, tn = (N + BN - 1) / BN;
     const long long tiles = (long long)(ptm * tn);
@@ -712,9 +790,12 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     TcPlan plan = {};
     plan.pair_tiles_m = (int)ptm; plan.tiles_n = (int)tn; plan.raster_group = la_gemm_raster_group(ptm);
     plan.num_kb = (int)((K + TC_BK - 1) / TC_BK);
-    // Chains of 64 k, except for short products: a lone 64-chain is where the tensor cores' truncating accumulation shows
-    // most (K = 64, 16M outputs: max error 6.5e-7 of sum|a||b| against a bar of 5.9e-7); chains of 32 keep K <= 128 inside.
-    plan.chunk_kb = plan.num_kb <= 4 ? 1 : TC_CHUNK_KB;
+    // Accumulation chains (k-blocks of 32 summed inside the tensor cores before the FP32 registers take over).  The tensor
+    // cores' accumulation truncates, and a lone chain is where that shows most (K = 64 as one chain, 16M outputs: 6.5e-7 of
+    // sum|a||b| against a bar of 5.9e-7), so short products use chains of 32; over long products the chain errors average
+    // out (K = 8192: 4.8e-8 with 64-chains, 6.2e-8 with 128, 9.6e-8 with 256, bar 5.4e-7) and longer chains halve the
+    // accumulator drains that otherwise bound the kernel once the cross terms run as bf16 (8192^3: 3.63 -> 3.30 -> 3.28 ms).
+    plan.chunk_kb = g_tc_chunk > 0 ? g_tc_chunk : plan.num_kb <= 4 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB;
     plan.num_chunks = (plan.num_kb + plan.chunk_kb - 1) / plan.chunk_kb;
     plan.dp_items = (int)tiles; plan.stream_items = 0; plan.stream_tiles = 0;
     // Ragged last wave: `waves` full waves and `rest` tiles more.  When the remainder fills at most half of the GPU, each of
@@ -744,8 +825,22 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, (int)M, (int)N, plan));
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan));
     return LA_OK;
+}
+
+// Cross terms in bf16?  hi*lo and lo*hi carry 2^-11 of a product's weight, so bf16's 8 significant bits leave an error of
+// about 2^-20 of |a||b| per term with random sign: after a sum of K terms, 2^-20 * 1.3 / sqrt(K) of sum|a||b| (simulated:
+// K = 8192 max 4e-8 over 150k outputs, K = 1024 1.2e-7) -- against the reference's own ~2.4e-7.  Two bf16 MMAs cost what
+// one tf32 MMA does, so the product needs 2 tensor-core time units instead of 3 (8192^3: 3.97 -> 3.61 ms, and 3.28 ms with
+// the longer accumulation chains the faster MMAs call for).  Measured on the GPU (tools/acc_probe.py) the error is the same
+// as with tf32 cross terms within 20 % at every K tried (K = 256: 2.4e-7 vs 2.2e-7, bar 4.6e-7; K = 8192: 4.8e-8 vs 4.0e-8):
+// the tensor cores' truncating accumulation dominates both.  Used from K = 1024; shorter products keep three tf32 MMAs.
+int g_tc_variant = 0;
+int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross terms, 1 bf16 cross terms whenever K % 8 == 0
+bool la_tc_cross_bf16(size_t K) {
+    if (K % 8 != 0 || g_tc_cross == 0 || g_tc_variant != 0) return false;
+    return g_tc_cross > 0 || K >= 1024;
 }
 
 // Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,
@@ -765,14 +860,20 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
             if (c < 0.90 * best) { best = c; bn = cand; }       // a 224-wide tile costs ~7 % more per flop (8192^3: 4.86 -> 5.23 ms at equal wave count): it must buy more than that
         }
     }
+    if (la_tc_cross_bf16(K)) {
+        switch (bn) {
+        case 224: return tc_launch_2cta_bn<224, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+        case 192: return tc_launch_2cta_bn<192, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+        default:  return tc_launch_2cta_bn<256, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+        }
+    }
     switch (bn) {
-    case 224: return tc_launch_2cta_bn<224>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
-    case 192: return tc_launch_2cta_bn<192>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
-    default:  return tc_launch_2cta_bn<256>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    case 224: return tc_launch_2cta_bn<224, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    case 192: return tc_launch_2cta_bn<192, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    default:  return tc_launch_2cta_bn<256, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
     }
 }
 
-int g_tc_variant = 0;
 
 }  // namespace
 
@@ -786,6 +887,8 @@ extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA
 static int initial_raster_group() { const char* e = getenv("LA_GEMM_RASTER"); return e ? atoi(e) : -1; }
 static int g_raster_group = initial_raster_group();     // -1: by size; 0: m-major; g > 0: bands of g tile rows (LA_GEMM_RASTER in the environment)
 int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m >= 16 ? 8 : 0); }
+extern "C" la_status la_gemm_tc_set_chunk(int kb) { g_tc_chunk = kb; return LA_OK; }       // tuning hook
+extern "C" la_status la_gemm_tc_set_cross(int mode) { g_tc_cross = mode; return LA_OK; }   // tuning hook: -1 by K, 0 tf32 cross terms, 1 bf16
 extern "C" la_status la_gemm_tc_set_tile_n(int bn) { g_tc_bn = (bn == 224 || bn == 192 || bn == 256) ? bn : 0; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_set_stream_tail(int mode) { g_tc_stream = mode; return LA_OK; }   // tuning hook: -1 auto, 0 off, 1 on
 extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; return LA_OK; }   // tuning hook
@@ -793,14 +896,16 @@ extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; ret
 // Pieces shared by la_gemm_3xtf32 and the host-streaming GEMM (gemm_host.cu).
 la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size_t K, unsigned* flag, cudaStream_t st) {
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
-    split_tf32_kernel<<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag);
+    if (la_tc_cross_bf16(K)) split_tf32_kernel<true><<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag);
+    else                     split_tf32_kernel<false><<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
 la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st) {
     const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
     if (tk * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "3xTF32 pre-pass: B is too large");
-    split_transpose_kernel<<<(unsigned)(tk * tn), 256, 0, st>>>(bt_hi, bt_lo, B, K, N, (unsigned)tn, flag);
+    if (la_tc_cross_bf16(K)) split_transpose_kernel<true><<<(unsigned)(tk * tn), 256, 0, st>>>(bt_hi, bt_lo, B, K, N, (unsigned)tn, flag);
+    else                     split_transpose_kernel<false><<<(unsigned)(tk * tn), 256, 0, st>>>(bt_hi, bt_lo, B, K, N, (unsigned)tn, flag);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }

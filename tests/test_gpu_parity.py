@@ -444,6 +444,28 @@ def test_matmat_banded_tile_order_changes_nothing(la, group):
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+@pytest.mark.parametrize("cross", [0, 1])
+@pytest.mark.parametrize("chunk", [0, 2, 8])
+def test_matmat_tensor_engine_cross_terms_and_chain_lengths_meet_the_bar(la, cross, chunk):
+    """The two cross terms hi*lo + lo*hi as tf32 MMAs (cross 0) or as bf16 MMAs on bf16(hi), bf16(x - hi) planes (cross 1,
+    the default from K = 1024), with accumulation chains of 64 / 256 k or the default by K: every combination must pass the
+    f32 gate on short and long products."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    lib.la_gemm_tc_set_cross(cross)
+    try:
+        for M, K, N in ((256, 64, 256), (512, 256, 384), (388, 1000, 260), (1024, 2048, 512), (512, 4096, 768)):
+            # a forced chain length only where it leaves at least 8 chains: the truncating accumulation inside one chain is
+            # what the FP32 registers are there to average out (the defaults: 32-chains up to K = 128, 64 below 2048,
+            # 128 below 8192, 256 from there)
+            lib.la_gemm_tc_set_chunk(chunk if K >= 8 * 32 * chunk else 0)
+            check_f32_gemm(la, gen.values("f32", M * K, 71), gen.values("f32", K * N, 72), M, K, N, ("cross", cross, "chunk", chunk, M, K, N))
+            assert lib.la_gemm_last_engine() == 2
+    finally:
+        lib.la_gemm_tc_set_cross(-1); lib.la_gemm_tc_set_chunk(0)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
 @pytest.mark.parametrize("bn", [224, 192])
 def test_matmat_3xtf32_narrower_tiles_change_nothing(la, bn):
     """la_gemm_tc_set_tile_n: pair tiles 256 x 224 / 256 x 192 (picked when they pack the waves better, e.g. the 8-GPU shard

@@ -466,6 +466,47 @@ def test_matmat_tensor_engine_cross_terms_and_chain_lengths_meet_the_bar(la, cro
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+def test_matmat_tensor_engine_on_structured_data(la):
+    """Data that defeats the 'rounding errors are random' argument: constant matrices (every bf16 rounding of a cross term errs
+    the same way, so the errors add up linearly in K), same-sign data, and integer-valued f32 whose products and sums the
+    reference computes exactly.  Long K, so the bf16 cross terms are in use."""
+    lib = la._lib.lib; P = oracle.port()
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    try:
+        M, N = 256, 384
+        rng = np.random.default_rng(77)
+        cases = {}
+        for K in (2048, 8192):                      # 128-long and 256-long accumulation chains
+            cases["constant 1/3 x 0.7, K=%d" % K] = (K, np.full(M * K, 1.0 / 3.0, np.float32), np.full(K * N, 0.7, np.float32))
+            cases["same sign, K=%d" % K] = (K, rng.random(M * K, dtype=np.float32), rng.random(K * N, dtype=np.float32))
+            cases["rows of one value, K=%d" % K] = (K, np.repeat(rng.random(M, dtype=np.float32), K), rng.random(K * N, dtype=np.float32))
+        for what, (K, a, b) in cases.items():
+            # against the f64 truth only: on such data the reference order itself drifts (constant data: 1.2e-5 of the
+            # result), so "close to the oracle" is no criterion here, "no further from the truth than the oracle" is
+            C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec().astype(np.float64)
+            assert lib.la_gemm_last_engine() == 2
+            truth, absab = P.f32_mul_mat_mat_truth(a, b, M, K, N)
+            e_ours = float((np.abs(C - truth) / absab).max())
+            e_orc = float((np.abs(P.mul_mat_mat(a, b, M, K, N).astype(np.float64) - truth) / absab).max())
+            print("%s: e_ours %.3e  e_oracle %.3e" % (what, e_ours, e_orc))
+            # here even without the factor 2 of the random-data gate (measured: 0.05x - 0.8x of the oracle's error; the
+            # worst, same-sign rows, is the truncation bias of one accumulation chain, which is why chains grow only with K)
+            assert e_ours <= max(e_orc, F32_EPS_FLOOR), (what, e_ours, e_orc)
+        K = 2048
+        # integers small enough that every partial sum stays below 2^24: the reference is exact, so must we be
+        a = rng.integers(-60, 61, M * K).astype(np.float32); b = rng.integers(-60, 61, K * N).astype(np.float32)
+        C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+        exact = (a.reshape(M, K).astype(np.int64) @ b.reshape(K, N).astype(np.int64)).reshape(-1)
+        assert np.abs(exact).max() < 2 ** 24 and np.array_equal(C.astype(np.int64), exact)
+        # 13-bit integers times small ones: hi has more bits than bf16 keeps, but its partner's lo is zero
+        a = rng.integers(4096, 8192, M * K).astype(np.float32); b = rng.integers(0, 2, K * N).astype(np.float32)
+        C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+        exact = (a.reshape(M, K).astype(np.int64) @ b.reshape(K, N).astype(np.int64)).reshape(-1)
+        assert np.abs(exact).max() < 2 ** 24 and np.array_equal(C.astype(np.int64), exact)
+    finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
 @pytest.mark.parametrize("bn", [224, 192])
 def test_matmat_3xtf32_narrower_tiles_change_nothing(la, bn):
     """la_gemm_tc_set_tile_n: pair tiles 256 x 224 / 256 x 192 (picked when they pack the waves better, e.g. the 8-GPU shard

@@ -809,13 +809,21 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
         plan.stream_tiles = (int)rest;
         plan.stream_items = (int)(2 * rest);
         plan.dp_items = (int)(tiles - rest);
-        // zero the tiles that receive two partial sums.  m-major order: they are the last tile columns (the first of them
-        // possibly shared with whole tiles, which simply overwrite); banded order: all of C.
+        // zero the tiles that receive two partial sums (whole tiles inside the zeroed rectangle simply overwrite it later).
+        // m-major order: the last tile columns.  Banded order: the last tile columns of the last band.
         if (plan.raster_group <= 0 || plan.raster_group >= plan.pair_tiles_m) {
             const size_t first_col = ((size_t)plan.dp_items / ptm) * BN;
             LA_CUDA(cudaMemset2DAsync(C + first_col, N * sizeof(float), 0, (N - first_col) * sizeof(float), M, st));
         } else {
-            LA_CUDA(cudaMemsetAsync(C, 0, M * N * sizeof(float), st));
+            const size_t bands = (ptm + plan.raster_group - 1) / plan.raster_group;
+            const size_t first_m = (bands - 1) * plan.raster_group, band_rows = ptm - first_m;      // tile rows of the last band
+            if ((size_t)rest <= band_rows * tn) {
+                const size_t cols = ((size_t)rest + band_rows - 1) / band_rows;                      // tile columns holding the split tiles
+                const size_t first_col = (tn - cols) * BN, first_row = first_m * 256;
+                LA_CUDA(cudaMemset2DAsync(C + first_row * N + first_col, N * sizeof(float), 0, (N - first_col) * sizeof(float), M - first_row, st));
+            } else {
+                LA_CUDA(cudaMemsetAsync(C, 0, M * N * sizeof(float), st));
+            }
         }
     }
     const long long items = plan.dp_items + plan.stream_items;

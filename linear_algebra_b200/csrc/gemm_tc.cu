@@ -469,6 +469,11 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
                         tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
                         tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
                         tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                        // (What bounds this kernel once the cross terms are bf16 is the L2 -> SM path: 34.4 GB per 8192^3 launch in
+                        //  2.96 ms = 11.6 TB/s, at the ~6300 B/clk the L2 slices deliver chip-wide.  A 2-stage ring costs 22 %,
+                        //  and prefetching boxes into L2 ahead of the ring makes it 27 % SLOWER -- it adds L2 requests, which is
+                        //  the scarce thing.  Fewer bytes per MMA -- A multicast across two pairs of a 4-CTA cluster -- is the
+                        //  next step.)
                         if constexpr (BF16X) {      // the second bf16 plane of each operand, in the upper half of its 16 KB slot
                             tma_load_2d_2sm(st + TC3_TILE + TC3_TILE / 2, &map_a_x, &full_bar[s], kb * TC_BK, m0);
                             tma_load_2d_2sm(st + 3 * TC3_TILE + TC3_TILE / 2, &map_b_x, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);

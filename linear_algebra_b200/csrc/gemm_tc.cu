@@ -1,30 +1,35 @@
-// csrc/gemm_tc.cu -- 3xTF32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32; what LA_GEMM_AUTO picks for large products).
+// csrc/gemm_tc.cu -- split-f32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32; what LA_GEMM_AUTO picks from 512^3 up).
 //
-// Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other
-// arithmetic: every f32 operand is split x = hi + lo with hi = tf32(x) (round to nearest) and
-// lo = tf32(x - hi), and each product is formed as hi*hi + hi*lo + lo*hi on the 5th-generation
-// tensor cores (tcgen05.mma kind::tf32) with FP32 accumulation in tensor memory.  The dropped
-// lo*lo term is below 2^-22 relative, so results stay inside the f32 bar of DESIGN.md section 4;
-// tests/test_gpu_parity.py gates the engine on that bar; la_set_gemm_mode(LA_GEMM_SIMT) switches it off.
+// Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other arithmetic: every f32
+// operand is split x = hi + lo with hi = tf32(x) (round to nearest), and each product is formed as hi*hi + hi*lo + lo*hi
+// on the 5th-generation tensor cores with FP32 accumulation in tensor memory:
+//   K < 1024    three tcgen05.mma kind::tf32 per k-step ("3xTF32"), lo = tf32(x - hi);
+//   K >= 1024   hi*hi as kind::tf32, the two cross terms (2^-11 of the weight) as kind::f16 bf16 MMAs at twice the rate
+//               on the planes bf16(hi) and bf16(x - hi): 2 tensor time units per product instead of 3.
+// The dropped lo*lo term is below 2^-22 relative.  Accumulation runs in chains of 32 .. 256 k inside the tensor cores
+// (their FP32 accumulation truncates) and in FP32 registers across chains.  Results stay inside the f32 bar of DESIGN.md
+// section 4 -- tests/test_gpu_parity.py gates every cross-term type / chain length / tile width on it, on random and on
+// structured data; la_set_gemm_mode(LA_GEMM_SIMT) switches the engine off.
 //
 // Kernels in this file (la_gemm_tc_set_variant picks one; 0 is the default):
-//   0  gemm_3xtf32_2cta_kernel      CTA pairs (tcgen05 cta_group::2), 256x256 tile per pair, 3-stage
-//                                   TMA ring, chunked accumulation              <- meets the f32 bar
-//   5/3 gemm_3xtf32_chunked_kernel  one CTA per 128x256 tile (with / without B multicast), chunked
-//   1/2 gemm_3xtf32_kernel          single accumulation chain (tuning reference; drifts, see below)
+//   0  gemm_3xtf32_2cta_kernel<BN, BF16X>  CTA pairs (tcgen05 cta_group::2), 256 x BN tile per pair (BN = 256 / 224 / 192 by
+//                                   wave count), 3-stage TMA ring, work items = (tile, chain range) so the ragged last
+//                                   wave can be cut in two along K, banded tile order above 4096 rows
+//   5/3 gemm_3xtf32_chunked_kernel  one CTA per 128x256 tile (with / without B multicast), 64-chains  (tuning references)
+//   1/2 gemm_3xtf32_kernel          single accumulation chain (tuning reference; drifts)
 // Common structure:
-//   pre-pass   split_tf32_kernel       A -> A_hi, A_lo             (scratch)
-//              split_transpose_kernel  B -> Bt_hi, Bt_lo (N x K)   (scratch) so both operands are K-major
-//   TMA warp   cp.async.bulk.tensor.2d (128-byte swizzle) of the four slabs of a 32-wide k-block
-//              into a ring guarded by full/empty mbarriers
-//   MMA warp   owns tensor memory; one elected lane issues 3 tcgen05.mma per 8-wide k-step
-//              (hi*lo, lo*hi, hi*hi) and tcgen05.commit's the stage back to the producer
-//   epilogue   tcgen05.ld of the FP32 accumulator (lane = row, column = column), FP32 adds in
-//              registers, 16-byte streaming stores to C
-// Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-pass
-// detects anything outside [2^-100, 2^100] (or NaN) and the call then falls back to the SIMT engine,
-// so the tensor engine never changes the result class of a product.
-// Roofline: tensor pipe (tf32), 3 MMAs per useful product.
+//   pre-pass   split_tf32_kernel       A -> A_hi + (A_lo | bf16(A_hi), bf16(A - A_hi))                 (scratch)
+//              split_transpose_kernel  B -> the same planes of B^T (N x K), so both operands are K-major    (scratch)
+//   TMA warp   cp.async.bulk.tensor.2d of the slabs of a 32-wide k-block (128-byte rows / SWIZZLE_128B for tf32 planes,
+//              64-byte rows / SWIZZLE_64B for bf16 planes) into a ring guarded by full/empty mbarriers
+//   MMA warp   owns tensor memory; one elected lane issues the MMAs of a k-block and tcgen05.commit's the stage back
+//   epilogue   tcgen05.ld of the FP32 accumulator after every chain, FP32 adds in registers, 16-byte streaming stores to C
+//              (atomicAdd of the two halves for a tile cut along K)
+// Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-pass detects anything
+// outside [2^-100, 2^100] (or NaN) and the call then runs the SIMT engine over the same C, so the tensor engine never
+// changes the result class of a product.
+// Roofline: tensor pipe, 3 (K < 1024) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
+// bound by the L2 -> SM path (11.6 TB/s of operand loads at 8192^3), see the note in the producer loop.
 #include <cuda_bf16.h>
 #include "tc_common.cuh"
 

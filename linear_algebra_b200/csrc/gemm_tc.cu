@@ -29,7 +29,8 @@
 // outside [2^-100, 2^100] (or NaN) and the call then runs the SIMT engine over the same C, so the tensor engine never
 // changes the result class of a product.
 // Roofline: tensor pipe, 3 (K < 1024) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
-// bound by the L2 -> SM path (11.6 TB/s of operand loads at 8192^3), see the note in the producer loop.
+// at 90 % of that floor with the L2 -> SM path (11.6 TB/s of operand loads at 8192^3) close to its own limit, see the
+// note in the producer loop.
 #include <cuda_bf16.h>
 #include "tc_common.cuh"
 
@@ -474,11 +475,12 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
                         tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
                         tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
                         tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
-                        // (What bounds this kernel once the cross terms are bf16 is the L2 -> SM path: 34.4 GB per 8192^3 launch in
-                        //  2.96 ms = 11.6 TB/s, at the ~6300 B/clk the L2 slices deliver chip-wide.  A 2-stage ring costs 22 %,
-                        //  and prefetching boxes into L2 ahead of the ring makes it 27 % SLOWER -- it adds L2 requests, which is
-                        //  the scarce thing.  Fewer bytes per MMA -- A multicast across two pairs of a 4-CTA cluster -- is the
-                        //  next step.)
+                        // (With bf16 cross terms the kernel runs at 90 % of its tensor-time floor (8192^3: 2.96 ms against
+                        //  2.67) while pulling 34.4 GB per launch through L2 -> SM = 11.6 TB/s, close to what the L2 slices
+                        //  deliver chip-wide.  Experiments: a 2-stage ring costs 22 %; prefetching boxes into L2 ahead of the
+                        //  ring makes it 27 % SLOWER (more L2 requests); not loading A at all for every other tile -- the upper
+                        //  bound of what multicasting A across a 4-CTA cluster could save -- gains only 3 %.  So the operand
+                        //  path is near its limit but not the binding one; what is left is per-tile ramp-up and drain.)
                         if constexpr (BF16X) {      // the second bf16 plane of each operand, in the upper half of its 16 KB slot
                             tma_load_2d_2sm(st + TC3_TILE + TC3_TILE / 2, &map_a_x, &full_bar[s], kb * TC_BK, m0);
                             tma_load_2d_2sm(st + 3 * TC3_TILE + TC3_TILE / 2, &map_b_x, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);

@@ -115,6 +115,8 @@ lib.la_gemm_set_variant.argtypes = [_I]
 lib.la_gemm_set_variant.restype = ctypes.c_int
 lib.la_gemm_tc_set_variant.argtypes = [_I]
 lib.la_gemm_tc_set_variant.restype = ctypes.c_int
+lib.la_gemm_tc_set_persistent.argtypes = [_I]
+lib.la_gemm_tc_set_persistent.restype = ctypes.c_int
 lib.la_gemm_tc_set_chunk.argtypes = [_I]
 lib.la_gemm_tc_set_chunk.restype = ctypes.c_int
 lib.la_gemm_tc_set_cross.argtypes = [_I]

@@ -379,10 +379,19 @@ struct TcPlan {
     int pair_tiles_m, tiles_n, raster_group;
     int num_kb, chunk_kb, num_chunks;            // k-blocks of 32; k-blocks per tensor-core accumulation chain; chains per tile
     int dp_items, stream_items, stream_tiles;
+    int persist;                                 // > 0: that many CTA pairs loop over all work items (persistent grid)
 };
 
 // Segment `seg` of work item `item`: tile (linear index) and its chunk range [c_begin, c_end).  False when there is none.
 __device__ __forceinline__ bool tc_segment(const TcPlan& p, int item, int seg, int& tile, int& c_begin, int& c_end) {
+    if (p.persist > 0) {
+        // persistent grid: CTA pair `item` walks the work items item, item + persist, item + 2 persist, ... as its segments
+        // (each of those is a single segment: a whole tile or one half of a split tile), so the drain and the C stores of one
+        // tile overlap the first chains of the next and tensor memory, barriers and the ring are set up once per pair
+        item += seg * p.persist;
+        if (item >= p.dp_items + p.stream_items) return false;
+        seg = 0;
+    }
     if (item < p.dp_items) {
         tile = item; c_begin = 0; c_end = p.num_chunks;
         return seg == 0;
@@ -771,6 +780,7 @@ la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, cons
 
 int g_tc_stream = -1;           // la_gemm_set_stream_tail: -1 by the gain model below, 0 never, 1 whenever possible
 
+int g_tc_persist = 0;           // la_gemm_tc_set_persistent: 0 one CTA pair per work item, 1 persistent grid of sm_count / 2 pairs
 int g_tc_chunk = 0;             // la_gemm_tc_set_chunk: k-blocks of 32 per accumulation chain (0 = by K)
 int g_tc_bn = 0;                // la_gemm_tc_set_tile_n: 0 = pick by wave count, else 256 / 224 / 192
 
@@ -838,7 +848,9 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
             }
         }
     }
-    const long long items = plan.dp_items + plan.stream_items;
+    long long items = plan.dp_items + plan.stream_items;
+    plan.persist = 0;
+    if (g_tc_persist != 0 && items > pairs) { plan.persist = (int)pairs; items = pairs; }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(2 * items)); cfg.blockDim = dim3(TC3_THREADS); cfg.dynamicSmemBytes = TC3_SMEM_BYTES; cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -907,6 +919,7 @@ extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA
 static int initial_raster_group() { const char* e = getenv("LA_GEMM_RASTER"); return e ? atoi(e) : -1; }
 static int g_raster_group = initial_raster_group();     // -1: by size; 0: m-major; g > 0: bands of g tile rows (LA_GEMM_RASTER in the environment)
 int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m >= 16 ? 8 : 0); }
+extern "C" la_status la_gemm_tc_set_persistent(int on) { g_tc_persist = on; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_tc_set_chunk(int kb) { g_tc_chunk = kb; return LA_OK; }       // tuning hook
 extern "C" la_status la_gemm_tc_set_cross(int mode) { g_tc_cross = mode; return LA_OK; }   // tuning hook: -1 by K, 0 tf32 cross terms, 1 bf16
 extern "C" la_status la_gemm_tc_set_tile_n(int bn) { g_tc_bn = (bn == 224 || bn == 192 || bn == 256) ? bn : 0; return LA_OK; }   // tuning hook

@@ -466,6 +466,24 @@ def test_matmat_tensor_engine_cross_terms_and_chain_lengths_meet_the_bar(la, cro
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+def test_matmat_tensor_engine_persistent_grid_changes_nothing(la):
+    """la_gemm_tc_set_persistent: 74 CTA pairs walk all work items instead of one pair per item (a tuning variant: +0.4 % at
+    8192^3, -6 % at 16384^3, so off by default).  Same MMAs per output, so the bits must not change; with and without
+    split last-wave tiles."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    try:
+        for M, K, N in ((2560, 512, 2304), (4096, 1024, 5000), (4800, 96, 2300)):
+            a = gen.values("f32", M * K, 73); b = gen.values("f32", K * N, 74)
+            A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+            lib.la_gemm_tc_set_persistent(0); C0 = (A * B).to_vec()
+            lib.la_gemm_tc_set_persistent(1); C1 = (A * B).to_vec()
+            assert lib.la_gemm_last_engine() == 2 and same(C0, C1), (M, K, N)
+    finally:
+        lib.la_gemm_tc_set_persistent(0)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
 def test_matmat_tensor_engine_on_structured_data(la):
     """Data that defeats the 'rounding errors are random' argument: constant matrices (every bf16 rounding of a cross term errs
     the same way, so the errors add up linearly in K), same-sign data, and integer-valued f32 whose products and sums the

@@ -60,6 +60,51 @@ transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
     }
 }
 
+// Persistent form of the tile kernel: a fixed grid walks the tiles, the 16-byte loads of the NEXT tile are issued before the
+// stores of the current one (two shared-memory buffers, one barrier per tile), so every thread always has loads in flight and
+// there is no per-tile block launch.
+template <typename E, int T>
+__global__ void __launch_bounds__(TR_THREADS)
+transpose_pack_persistent_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x, unsigned tiles) {
+    using P = Pack<E>;
+    constexpr int V = P::N, VPR = T / V, PITCH = T + 1;
+    constexpr int LOADS = T * VPR / TR_THREADS;
+    static_assert(T * VPR % TR_THREADS == 0, "whole packets per thread");
+    extern __shared__ __align__(16) uint8_t tile_raw[];
+    E* buf[2] = {reinterpret_cast<E*>(tile_raw), reinterpret_cast<E*>(tile_raw) + T * PITCH};
+    P in_p[LOADS];
+    auto fetch = [&](unsigned t) {
+        const size_t r0 = (size_t)(t / tiles_x) * T, c0 = (size_t)(t % tiles_x) * T;
+#pragma unroll
+        for (int j = 0; j < LOADS; ++j) {
+            const int idx = threadIdx.x + j * TR_THREADS, r = idx / VPR, q = idx % VPR;
+            if (r0 + r < R && c0 + (size_t)q * V < C) in_p[j] = ld_stream(reinterpret_cast<const P*>(in + (r0 + r) * C + c0 + (size_t)q * V));
+        }
+    };
+    unsigned t = blockIdx.x;
+    if (t < tiles) fetch(t);
+    for (int b = 0; t < tiles; t += gridDim.x, b ^= 1) {
+        E* tile = buf[b];
+#pragma unroll
+        for (int j = 0; j < LOADS; ++j) {
+            const int idx = threadIdx.x + j * TR_THREADS, r = idx / VPR, q = idx % VPR;
+#pragma unroll
+            for (int e = 0; e < V; ++e) tile[r * PITCH + q * V + e] = in_p[j].v[e];
+        }
+        __syncthreads();            // also orders this tile's writes after the reads of two tiles ago (same buffer)
+        const size_t r0 = (size_t)(t / tiles_x) * T, c0 = (size_t)(t % tiles_x) * T;
+        if (t + gridDim.x < tiles) fetch(t + gridDim.x);
+#pragma unroll
+        for (int j = 0; j < LOADS; ++j) {
+            const int idx = threadIdx.x + j * TR_THREADS, cc = idx / VPR, q = idx % VPR;
+            P p;
+#pragma unroll
+            for (int e = 0; e < V; ++e) p.v[e] = tile[(q * V + e) * PITCH + cc];
+            if (c0 + cc < C && r0 + (size_t)q * V < R) st_stream(reinterpret_cast<P*>(out + (c0 + cc) * R + r0 + (size_t)q * V), p);
+        }
+    }
+}
+
 // 1- and 2-byte elements: the tile lives in shared memory as 32-bit words (G = 4 / sizeof(E) elements each), so the
 // shared-memory traffic is word-sized instead of byte-sized; the G x G sub-blocks are transposed in registers with
 // byte permutes.  Tile: TR = 128 / sizeof(E) input rows x 32 words (128 bytes) -> 32 G output rows of 128 bytes.
@@ -133,7 +178,9 @@ transpose_elem_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
 }
 
 int g_tr_variant = 0;      // la_transpose_set_variant (tuning hook): 4-byte tile shape; measured at i32 8192^2 / 32768^2:
-                           // 64x64 6.06 / 6.51 TB/s (default), 64x32 6.26 / 6.38, 32x64 6.17 / 6.05, 128x128 4.73 / 5.11
+                           // 64x64 6.06 / 6.51 TB/s (default), 64x32 6.26 / 6.38, 32x64 6.17 / 6.05, 128x128 4.73 / 5.11;
+                           // 3..8: persistent pipelined walk with that many blocks per SM: 5.6 - 5.9 / 5.9 - 6.05 (64 registers
+                           // per thread halve the occupancy; plain blocks at 8 per SM keep more loads in flight)
 
 template <typename E, int TROWS, int TCOLS>
 la_status transpose_pack_launch(E* out, const E* in, size_t R, size_t C, cudaStream_t st) {
@@ -164,6 +211,18 @@ la_status transpose_launch(E* out, const E* in, size_t R, size_t C, cudaStream_t
             }
         }
         if constexpr (sizeof(E) == 4) {
+            if (g_tr_variant >= 3 && g_tr_variant <= 8) {          // persistent tile walk, g_tr_variant blocks per SM
+                const size_t gx = (C + 63) / 64, gy = (R + 63) / 64;
+                if (gx * gy > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "transpose: %zu x %zu is too large", R, C);
+                LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+                auto kern = transpose_pack_persistent_kernel<E, 64>;
+                constexpr size_t smem = 2 * (size_t)64 * 65 * sizeof(E);
+                size_t grid = (size_t)info->sm_count * g_tr_variant;
+                if (grid > gx * gy) grid = gx * gy;
+                kern<<<(unsigned)grid, TR_THREADS, smem, st>>>(out, in, R, C, (unsigned)gx, (unsigned)(gx * gy));
+                LA_LAUNCH_CHECK();
+                return LA_OK;
+            }
             switch (g_tr_variant) {
             case 1: return transpose_pack_launch<E, 32, 64>(out, in, R, C, st);
             case 2: return transpose_pack_launch<E, 64, 32>(out, in, R, C, st);

@@ -345,6 +345,20 @@ def test_transpose(la, name):
         assert same(T.to_vec(), P.transpose(a, R, C)), (name, R, C)
 
 
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
+def test_transpose_tile_variants(la, variant):
+    """la_transpose_set_variant: other tile shapes of the 4-byte kernel (1, 2) and the persistent, software-pipelined tile walk
+    (3..8 = blocks per SM) against the oracle, on shapes with partial edge tiles and with more tiles than the grid holds."""
+    P = oracle.port(); lib = la._lib.lib
+    lib.la_transpose_set_variant(variant)
+    try:
+        for R, C in ((64, 32), (1000, 516), (2064, 1056), (4096, 8192), (16, 4096)):
+            a = gen.values("i32", R * C, 36)
+            assert same(la.Matrix.from_vec(a, R, C).transpose().to_vec(), P.transpose(a, R, C)), (variant, R, C)
+    finally:
+        lib.la_transpose_set_variant(0)
+
+
 # ------------------------------------------------------------------ device-side synthetic data
 @pytest.mark.parametrize("name", gen.ALL_NAMES)
 def test_synth_matches_host_mirror(la, name):

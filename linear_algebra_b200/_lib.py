@@ -115,6 +115,10 @@ lib.la_gemm_set_variant.argtypes = [_I]
 lib.la_gemm_set_variant.restype = ctypes.c_int
 lib.la_gemm_tc_set_variant.argtypes = [_I]
 lib.la_gemm_tc_set_variant.restype = ctypes.c_int
+lib.la_gemm_kernel_timing.argtypes = [_I]
+lib.la_gemm_kernel_timing.restype = ctypes.c_int
+lib.la_gemm_kernel_time_ms.argtypes = [ctypes.POINTER(ctypes.c_float), _PI]
+lib.la_gemm_kernel_time_ms.restype = ctypes.c_int
 lib.la_gemm_tc_set_persistent.argtypes = [_I]
 lib.la_gemm_tc_set_persistent.restype = ctypes.c_int
 lib.la_gemm_tc_set_chunk.argtypes = [_I]

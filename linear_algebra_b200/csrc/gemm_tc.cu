@@ -780,6 +780,13 @@ la_status tc_launch_chunked(float* C, const float* a_hi, const float* a_lo, cons
 
 int g_tc_stream = -1;           // la_gemm_set_stream_tail: -1 by the gain model below, 0 never, 1 whenever possible
 
+// Kernel-only timing for bench.py's roofline line: with la_gemm_kernel_timing(1) every launch of the pair kernel is bracketed by
+// two events on its own stream (up to 64 launches are kept); la_gemm_kernel_time_ms() waits for them and returns their sum.
+int g_tc_timing = 0;
+int g_tc_timed = 0;
+cudaEvent_t g_tc_ev[64][2];
+bool g_tc_ev_made = false;
+
 int g_tc_persist = 0;           // la_gemm_tc_set_persistent: 0 one CTA pair per work item, 1 persistent grid of sm_count / 2 pairs
 int g_tc_chunk = 0;             // la_gemm_tc_set_chunk: k-blocks of 32 per accumulation chain (0 = by K)
 int g_tc_bn = 0;                // la_gemm_tc_set_tile_n: 0 = pick by wave count, else 256 / 224 / 192
@@ -857,7 +864,13 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
+    const bool timed = g_tc_timing && g_tc_timed < 64;
+    if (timed) {
+        if (!g_tc_ev_made) { for (auto& e : g_tc_ev) { LA_CUDA(cudaEventCreate(&e[0])); LA_CUDA(cudaEventCreate(&e[1])); } g_tc_ev_made = true; }
+        LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][0], st));
+    }
     LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan));
+    if (timed) { LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][1], st)); ++g_tc_timed; }
     return LA_OK;
 }
 
@@ -919,6 +932,20 @@ extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA
 static int initial_raster_group() { const char* e = getenv("LA_GEMM_RASTER"); return e ? atoi(e) : -1; }
 static int g_raster_group = initial_raster_group();     // -1: by size; 0: m-major; g > 0: bands of g tile rows (LA_GEMM_RASTER in the environment)
 int la_gemm_raster_group(size_t pair_tiles_m) { return g_raster_group >= 0 ? g_raster_group : (pair_tiles_m >= 16 ? 8 : 0); }
+extern "C" la_status la_gemm_kernel_timing(int on) { g_tc_timing = on; g_tc_timed = 0; return LA_OK; }      // bench hook (not in the public header)
+extern "C" la_status la_gemm_kernel_time_ms(float* total_ms, int* launches) {
+    float sum = 0.f;
+    for (int j = 0; j < g_tc_timed; ++j) {
+        float ms = 0.f;
+        LA_CUDA(cudaEventSynchronize(g_tc_ev[j][1]));
+        LA_CUDA(cudaEventElapsedTime(&ms, g_tc_ev[j][0], g_tc_ev[j][1]));
+        sum += ms;
+    }
+    if (total_ms) *total_ms = sum;
+    if (launches) *launches = g_tc_timed;
+    g_tc_timed = 0;
+    return LA_OK;
+}
 extern "C" la_status la_gemm_tc_set_persistent(int on) { g_tc_persist = on; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_tc_set_chunk(int kb) { g_tc_chunk = kb; return LA_OK; }       // tuning hook
 extern "C" la_status la_gemm_tc_set_cross(int mode) { g_tc_cross = mode; return LA_OK; }   // tuning hook: -1 by K, 0 tf32 cross terms, 1 bf16

@@ -212,7 +212,7 @@ def extras(la, hbm_peak, peak_src):
             ms = timed(la, lambda: lib.call("la_mul_mat_mat", 8, R.ptr, P.ptr, Q.ptr, nn, nn, nn, None), it, 2)
             row[label] = {"ms": round(ms, 4), "TFLOP/s": round(2.0 * nn ** 3 / ms / 1e9, 2)}
         lib.call("la_set_gemm_mode", 2)
-        units = 2 if nn >= 1024 else 3         # K >= 1024: 1 tf32 MMA + 2 bf16 MMAs (half the time each) per product; below: 3 tf32 MMAs
+        units = 2 if nn >= 256 else 3          # K >= 256: 1 tf32 MMA + 2 bf16 MMAs (half the time each) per product; below: 3 tf32 MMAs
         row["3xtf32"]["roofline"] = {"bound": "tensor", "achieved": round(units * row["3xtf32"]["TFLOP/s"], 1), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
                                       "frac": round(units * row["3xtf32"]["TFLOP/s"] / tf32_peak, 3),
                                       "note": "achieved = tensor-core work issued in tf32-equivalent flops (%d per useful f32 flop; pre-pass included in the time); peak = measured bf16 / 2" % units}

@@ -3,8 +3,8 @@
 // Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other arithmetic: every f32
 // operand is split x = hi + lo with hi = tf32(x) (round to nearest), and each product is formed as hi*hi + hi*lo + lo*hi
 // on the 5th-generation tensor cores with FP32 accumulation in tensor memory:
-//   K < 1024    three tcgen05.mma kind::tf32 per k-step ("3xTF32"), lo = tf32(x - hi);
-//   K >= 1024   hi*hi as kind::tf32, the two cross terms (2^-11 of the weight) as kind::f16 bf16 MMAs at twice the rate
+//   K < 256     three tcgen05.mma kind::tf32 per k-step ("3xTF32"), lo = tf32(x - hi);
+//   K >= 256    hi*hi as kind::tf32, the two cross terms (2^-11 of the weight) as kind::f16 bf16 MMAs at twice the rate
 //               on the planes bf16(hi) and bf16(x - hi): 2 tensor time units per product instead of 3.
 // The dropped lo*lo term is below 2^-22 relative.  Accumulation runs in chains of 32 .. 256 k inside the tensor cores
 // (their FP32 accumulation truncates) and in FP32 registers across chains.  Results stay inside the f32 bar of DESIGN.md
@@ -28,7 +28,7 @@
 // Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-pass detects anything
 // outside [2^-100, 2^100] (or NaN) and the call then runs the SIMT engine over the same C, so the tensor engine never
 // changes the result class of a product.
-// Roofline: tensor pipe, 3 (K < 1024) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
+// Roofline: tensor pipe, 3 (K < 256) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
 // at 90 % of that floor with the L2 -> SM path (11.6 TB/s of operand loads at 8192^3) close to its own limit, see the
 // note in the producer loop.
 #include <cuda_bf16.h>
@@ -880,12 +880,14 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
 // one tf32 MMA does, so the product needs 2 tensor-core time units instead of 3 (8192^3: 3.97 -> 3.61 ms, and 3.28 ms with
 // the longer accumulation chains the faster MMAs call for).  Measured on the GPU (tools/acc_probe.py) the error is the same
 // as with tf32 cross terms within 20 % at every K tried (K = 256: 2.4e-7 vs 2.2e-7, bar 4.6e-7; K = 8192: 4.8e-8 vs 4.0e-8):
-// the tensor cores' truncating accumulation dominates both.  Used from K = 1024; shorter products keep three tf32 MMAs.
+// the tensor cores' truncating accumulation dominates both.  With 16M outputs, K = 256: 2.9e-7 (tf32 cross terms 2.5e-7, the
+// reference order itself 3.6e-7), and 4096 x 512 x 4096 runs 0.124 -> 0.113 ms.  Used from K = 256; shorter products keep three
+// tf32 MMAs.
 int g_tc_variant = 0;
 int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross terms, 1 bf16 cross terms whenever K % 8 == 0
 bool la_tc_cross_bf16(size_t K) {
     if (K % 8 != 0 || g_tc_cross == 0 || g_tc_variant != 0) return false;
-    return g_tc_cross > 0 || K >= 1024;
+    return g_tc_cross > 0 || K >= 256;
 }
 
 // Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,

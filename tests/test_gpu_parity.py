@@ -462,7 +462,7 @@ def test_matmat_banded_tile_order_changes_nothing(la, group):
 @pytest.mark.parametrize("chunk", [0, 2, 8])
 def test_matmat_tensor_engine_cross_terms_and_chain_lengths_meet_the_bar(la, cross, chunk):
     """The two cross terms hi*lo + lo*hi as tf32 MMAs (cross 0) or as bf16 MMAs on bf16(hi), bf16(x - hi) planes (cross 1,
-    the default from K = 1024), with accumulation chains of 64 / 256 k or the default by K: every combination must pass the
+    the default from K = 256), with accumulation chains of 64 / 256 k or the default by K: every combination must pass the
     f32 gate on short and long products."""
     lib = la._lib.lib
     la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)

@@ -971,7 +971,22 @@ la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, s
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
+// the GPU.  The one kernel with such loads (variant 5, B planes) is therefore only used when both planes are ordinary
+// device allocations of the current device; anything else takes the same kernel without multicast (variant 3).
+static bool tc_planes_are_local(const void* p0, const void* p1) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    for (const void* p : {p0, p1}) {
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+        if (attr.type != cudaMemoryTypeDevice || attr.device != dev) return false;
+    }
+    return true;
+}
+
 la_status la_tc_run(float* C, const float* a_hi, const float* a_lo, const float* bt_hi, const float* bt_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
+    if (g_tc_variant == 5 && !tc_planes_are_local(bt_hi, bt_lo)) return tc_launch_chunked<1>(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);
     switch (g_tc_variant) {
     default:
     case 0: return tc_launch_2cta(C, a_hi, a_lo, bt_hi, bt_lo, M, K, N, st);         // CTA pairs, tcgen05 cta_group::2 (default)

@@ -26,7 +26,17 @@
  *    element type in a fixed, deterministic order that differs from the reference's
  *    device-dependent order (tolerance: DESIGN.md).
  *  - Thread safety: any thread may call any function; scratch memory is keyed by
- *    (device, stream), so concurrent calls must use distinct streams.
+ *    (device, stream), so concurrent calls must use distinct streams.  la_mul_mat_mat_host
+ *    calls on one device are serialised inside the library (they share its copy streams).
+ *    la_set_gemm_mode and the knobs of linalg_b200_tuning.h are process-wide settings: set
+ *    them before threads start calling, not while products are in flight.
+ *  - Buffers and streams: la_malloc / la_free are stream-ordered pool operations on the legacy
+ *    default stream.  The library orders them against every stream made by la_stream_create
+ *    (la_free first lets the legacy stream wait for all work queued on those streams so far;
+ *    after la_malloc those streams wait for the legacy stream), so a buffer may be freed right
+ *    after queueing work that uses it and a fresh buffer may be used at once on any such
+ *    stream.  Streams the caller created itself with cudaStreamNonBlocking are outside that
+ *    arrangement: synchronise them before la_free of a buffer they use.
  */
 #ifndef LINALG_B200_H
 #define LINALG_B200_H
@@ -185,8 +195,12 @@ la_status la_mul_vec_transpose_mat(int dtype, void* C, const void* A, const void
  * counts in la_last_error() -- roughly strips * cols * sizeof(accumulator) <= 8 MiB, e.g.
  * 32768 x 32768 f32 fits, 64 x 2^21 u8 does not.  One block per device, shared by all calls on
  * all streams: calls that overlap on the GPU race; the block keeps the previous call's contents
- * and none of it needs to start at zero.  The first call on a device resolves the block's
- * device address (cudaGetSymbolAddress) and should be made before any stream capture begins. */
+ * and none of it needs to start at zero.  The first call on a device checks that it is an
+ * sm_10x GPU and resolves the block's device address (cudaGetSymbolAddress); with CUDA's lazy
+ * module loading it is also the call that places the kernels and the 8 MiB block on the device,
+ * so it may itself need device memory.  Make one small warm-up call per device and element type
+ * at start-up, before the host's own allocator takes the remaining memory and before any stream
+ * capture begins; later calls only launch kernels. */
 la_status la_mul_vec_mat_noalloc(int dtype, void* C, const void* A, const void* B, size_t rows, size_t cols, void* stream);
 
 /* ------------------------------------------------------------------ matrix x matrix
@@ -200,28 +214,34 @@ la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_
  * once, A and C stream through in row blocks on separate copy streams so uploads, multiplies and
  * downloads overlap.  Same results as la_mul_mat_mat.  Blocks until C_host is complete; pinned host
  * buffers (la_host_alloc) give full PCIe rate, pageable ones work; any of the three may also be a
- * device pointer (e.g. a B that is already resident). */
+ * device pointer (e.g. a B that is already resident).  Calls on the same device run one at a time
+ * (a second caller waits): they share one set of copy streams and one range-flag word. */
 la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N);
 
 /* f32 GEMM engine.
  *  LA_GEMM_SIMT    FP32 FMA pipe, each element accumulated k-ascending with one fused multiply-add
  *                  per k: the reference's own order (src/kernels.cl:136-138).
  *  LA_GEMM_3XTF32  tcgen05 tensor cores: every operand split x = hi + lo (hi = tf32(x)); a product is hi*hi + hi*lo + lo*hi:
- *                  three tf32 MMAs below K = 256; from there hi*hi as a tf32 MMA and the two cross terms (2^-11 of
+ *                  three tf32 MMAs below K = 512; from there hi*hi as a tf32 MMA and the two cross terms (2^-11 of
  *                  the weight) as bf16 MMAs at twice the rate,
- *                  FP32 accumulation in chunks (32 k for K <= 128, 64 below K = 2048, 128 below 8192, 256 from
+ *                  FP32 accumulation in chunks (32 k below K = 512, 64 below K = 2048, 128 below 8192, 256 from
  *                  there; meets the same f32 tolerance as the SIMT
  *                  engine).  Falls back to SIMT for shapes it does not cover
  *                  (M, N >= 128, K >= 32, all multiples of 4) and whenever an operand holds a NaN, an
  *                  infinity or a magnitude outside [2^-100, 2^100] (the call reads one flag back, so the
  *                  HOST blocks for the length of the pre-pass; the product itself is already queued behind
  *                  the pre-pass, so the GPU does not idle meanwhile).
- *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 from 512^3 multiply-adds up (where it overtakes the SIMT kernels),
- *                  LA_GEMM_SIMT below.
+ *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 for products of at least 512^3 multiply-adds (where it overtakes the SIMT
+ *                  kernels) whose K is at least LA_GEMM_AUTO_MIN_K, LA_GEMM_SIMT otherwise.  Below that K a product is a
+ *                  handful of accumulation chains inside the tensor cores and its worst error over many outputs can land
+ *                  slightly ABOVE that of the reference's own summation order, which the f32 gate (DESIGN.md section 4:
+ *                  never less accurate than the reference order) does not allow; forcing LA_GEMM_3XTF32 there is an
+ *                  explicit opt-in to at most twice the reference order's error.
  * 8/16/32-bit integer products of that size run as exact byte-limb products on the INT8 tensor cores
  * (bit-identical results, mod 2^n) unless LA_GEMM_SIMT is selected.
  * Process-wide; LA_GEMM_MODE=simt|3xtf32|auto in the environment sets the initial value. */
 enum { LA_GEMM_SIMT = 0, LA_GEMM_3XTF32 = 1, LA_GEMM_AUTO = 2 };
+enum { LA_GEMM_AUTO_MIN_K = 256 };
 la_status la_set_gemm_mode(int mode);
 la_status la_get_gemm_mode(int* mode);
 

@@ -40,6 +40,12 @@ la_status la_ensure_init(LaDeviceInfo** info);   // lazily binds the current dev
 // (tickets / flags).
 enum { LA_SCRATCH_ZEROED = 256 };
 la_status la_scratch(cudaStream_t stream, size_t bytes, void** ptr);
+// What every reduction asks la_scratch for (its per-block partials: at most 8 bytes x a few blocks per SM).  One fixed
+// request, so pointers into the header taken before a reduction stay valid across it.
+constexpr size_t LA_REDUCE_SCRATCH_BYTES = 64 << 10;
+// Shortest f32 product LA_GEMM_AUTO hands to the tensor engine (gemm.cu, gemm_host.cu): below it the truncating
+// accumulation inside a few tensor-core chains can land above the reference order's own error.
+constexpr size_t LA_TC_AUTO_MIN_K = LA_GEMM_AUTO_MIN_K;      // include/linalg_b200.h
 // One zero-copy flag word per (device, stream): kernels store into *dev_ptr, the host reads
 // *host_ptr after waiting for them (no device-to-host copy involved).
 la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsigned** dev_ptr);

@@ -284,7 +284,7 @@ extern "C" la_status la_normalize_vec(int dtype, void* C, const void* A, size_t 
     if (n == 0) return LA_OK;
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     cudaStream_t st = (cudaStream_t)stream;
-    void* scratch; LA_TRY(la_scratch(st, 0, &scratch));
+    void* scratch; LA_TRY(la_scratch(st, LA_REDUCE_SCRATCH_BYTES, &scratch));   // sized as the reduction below sizes it: the block cannot move under `slot`
     void* slot = (char*)scratch + 32;                      // bytes 32..39 of the header (restored to zero below)
     LA_TRY(la_dot_vec_vec_dev(dtype, A, A, n, slot, stream));
     size_t blocks = (n / 4 + EW_THREADS) / EW_THREADS;

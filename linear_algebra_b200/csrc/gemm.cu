@@ -514,7 +514,11 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     const bool tma_worth = g_gemm_variant > 0 || tma_tiles >= (la_dtype_size(dtype) == 8 ? 48u : 96u);
     // AUTO: the tensor engine for problems big enough to amortise its pre-pass (its floor is ~27 us: it overtakes the generic
     // kernel at 512^3, 27.4 against 32.2 us)
-    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && big))) {
+    // ... and only from K = LA_GEMM_AUTO_MIN_K: a shorter product is one to four accumulation chains inside the tensor cores,
+    // whose FP32 accumulation truncates, and its worst error over many outputs can land slightly above the reference order's
+    // own (4096 x 64 x 4096: 3.1e-7 of sum|a||b| against 3.0e-7), which the gate of DESIGN.md section 4 does not allow.  Those
+    // stay on the k-ascending SIMT engine (the tensor engine gains little there anyway); LA_GEMM_3XTF32 remains the opt-in.
+    if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && big && K >= LA_TC_AUTO_MIN_K))) {
         bool handled = false;
         LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
         if (handled) { g_last_engine = 2; return LA_OK; }

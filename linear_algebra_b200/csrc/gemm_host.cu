@@ -25,6 +25,7 @@ bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_
 namespace {
 
 struct HostGemmStreams {
+    std::mutex busy;      // one la_mul_mat_mat_host at a time per device: the streams, events and the range-flag word below are shared
     cudaStream_t in = nullptr, cmp = nullptr, out = nullptr;
     cudaEvent_t b_up = nullptr, in_done[2] = {nullptr, nullptr}, cmp_done[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
 };
@@ -59,12 +60,21 @@ struct DevBuf {       // stream-ordered pool allocation, freed on scope exit
     ~DevBuf() { if (p) cudaFreeAsync(p, st); }
 };
 
+// Declared after the DevBufs of a pass, so it runs before their destructors on EVERY way out: the frees are ordered on
+// the compute stream only, while copies on the two copy streams may still be reading or writing the blocks when an
+// error return cuts the pipeline short.
+struct DrainStreams {
+    HostGemmStreams* hs;
+    ~DrainStreams() { cudaStreamSynchronize(hs->in); cudaStreamSynchronize(hs->out); cudaStreamSynchronize(hs->cmp); (void)cudaGetLastError(); }
+};
+
 }  // namespace
 
 static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N, bool allow_tensor, bool* redo) {
     *redo = false;
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     HostGemmStreams* hs; LA_TRY(host_streams(&hs));
+    std::lock_guard<std::mutex> one_at_a_time(hs->busy);
     const size_t es = la_dtype_size(dtype);
     const int mode = la_gemm_current_mode();
     static const bool dbg = getenv("LA_DEBUG_HOSTGEMM") != nullptr;
@@ -75,7 +85,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     // one block still fills most SM pairs (512 x N / (256 x 256) tiles).  Other engines are compute bound and
     // tile-quantised: a quarter of M, at least 1024 rows.  Multiples of 128 / 256 rows.
     const bool want_tensor = allow_tensor && dtype == LA_F32 && mode != LA_GEMM_SIMT && K > 0 &&
-                             (mode == LA_GEMM_3XTF32 || (double)M * (double)N * (double)K >= 134217728.0);
+                             (mode == LA_GEMM_3XTF32 || ((double)M * (double)N * (double)K >= 134217728.0 && K >= LA_TC_AUTO_MIN_K));   // la_mul_mat_mat's policy
     size_t rb;
     if (want_tensor) { rb = ((M / 16 + 127) / 128) * 128; if (rb < 512) rb = 512; if (rb > 2048) rb = 2048; }
     else             { rb = ((M / 4 + 255) / 256) * 256;  if (rb < 1024) rb = 1024; if (rb > 4096) rb = 4096; }
@@ -83,6 +93,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     const size_t nblocks = (M + rb - 1) / rb;
 
     DevBuf B(hs->cmp), Abuf0(hs->cmp), Abuf1(hs->cmp), Cbuf0(hs->cmp), Cbuf1(hs->cmp), bt_hi(hs->cmp), bt_lo(hs->cmp), a_hi0(hs->cmp), a_lo0(hs->cmp), a_hi1(hs->cmp), a_lo1(hs->cmp);
+    DrainStreams drain{hs};
     LA_TRY(B.alloc(K * N * es));
     LA_TRY(Abuf0.alloc(rb * K * es)); LA_TRY(Abuf1.alloc(rb * K * es));
     LA_TRY(Cbuf0.alloc(rb * N * es)); LA_TRY(Cbuf1.alloc(rb * N * es));

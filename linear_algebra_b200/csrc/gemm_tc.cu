@@ -824,7 +824,11 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     // sum|a||b| against a bar of 5.9e-7), so short products use chains of 32; over long products the chain errors average
     // out (K = 8192: 4.8e-8 with 64-chains, 6.2e-8 with 128, 9.6e-8 with 256, bar 5.4e-7) and longer chains halve the
     // accumulator drains that otherwise bound the kernel once the cross terms run as bf16 (8192^3: 3.63 -> 3.30 -> 3.28 ms).
-    plan.chunk_kb = g_tc_chunk > 0 ? g_tc_chunk : plan.num_kb <= 4 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB;
+    // Round 2, measured over 16M outputs against the unrelaxed gate e <= max(E_oracle, 2^-22) (tools/short_k_probe.py): with
+    // 64-chains K = 256 comes out at 2.9e-7 against the reference order's 3.1 - 3.7e-7 -- inside, but by so little that a
+    // smaller problem (512 x 256 x 384) fell 1 % outside by chance; with 32-chains and tf32 cross terms it is 1.4e-7, K = 384
+    // 1.2e-7.  So products below K = 512 use chains of 32 (and tf32 cross terms, la_tc_cross_bf16).
+    plan.chunk_kb = g_tc_chunk > 0 ? g_tc_chunk : K < 512 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB;
     plan.num_chunks = (plan.num_kb + plan.chunk_kb - 1) / plan.chunk_kb;
     plan.dp_items = (int)tiles; plan.stream_items = 0; plan.stream_tiles = 0;
     // Ragged last wave: `waves` full waves and `rest` tiles more.  When the remainder fills at most half of the GPU, each of
@@ -881,13 +885,14 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
 // the longer accumulation chains the faster MMAs call for).  Measured on the GPU (tools/acc_probe.py) the error is the same
 // as with tf32 cross terms within 20 % at every K tried (K = 256: 2.4e-7 vs 2.2e-7, bar 4.6e-7; K = 8192: 4.8e-8 vs 4.0e-8):
 // the tensor cores' truncating accumulation dominates both.  With 16M outputs, K = 256: 2.9e-7 (tf32 cross terms 2.5e-7, the
-// reference order itself 3.6e-7), and 4096 x 512 x 4096 runs 0.124 -> 0.113 ms.  Used from K = 256; shorter products keep three
+// reference order itself 3.6e-7), and 4096 x 512 x 4096 runs 0.124 -> 0.113 ms.  Used from K = 512 (round 2: at K = 256 the
+// bf16 form sits at 0.8 - 0.9 of the reference order's error, too close to the unrelaxed gate); shorter products keep three
 // tf32 MMAs.
 int g_tc_variant = 0;
 int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross terms, 1 bf16 cross terms whenever K % 8 == 0
 bool la_tc_cross_bf16(size_t K) {
     if (K % 8 != 0 || g_tc_cross == 0 || g_tc_variant != 0) return false;
-    return g_tc_cross > 0 || K >= 256;
+    return g_tc_cross > 0 || K >= 512;
 }
 
 // Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,

@@ -310,9 +310,14 @@ extern "C" la_status la_mul_vec_mat(int dtype, void* C, const void* A, const voi
 // it.  Nothing in it has to start at zero: every partial the finishing kernel reads is
 // written first by the main kernel of the same call, so no clearing pass is needed.
 //
-// First call on a device: looks up the device address of the block (cudaGetSymbolAddress) and
-// the SM count, once, with that device current.  Make that first call before starting any
-// stream capture.  Later calls only launch kernels.
+// First call on a device: checks that the device is a B200-class GPU (sm_10x; the library holds
+// no code for anything else), looks up the device address of the block (cudaGetSymbolAddress)
+// and the SM count, once, with that device current.  Under CUDA's lazy module loading that
+// first call is also what places this file's kernels and the 8 MiB block on the device, so it
+// can itself need device memory and may synchronise.  A host that is about to hand all device
+// memory to its own allocator should therefore make one small warm-up call per device, per
+// element type it will use, during start-up, BEFORE its allocator takes the memory and before
+// starting any stream capture.  Later calls only launch kernels.
 constexpr size_t LA_NOALLOC_SCRATCH_BYTES = size_t(8) << 20;      // 8 MiB per GPU
 static __device__ __align__(256) unsigned char la_noalloc_scratch[LA_NOALLOC_SCRATCH_BYTES];
 
@@ -332,6 +337,12 @@ la_status noalloc_setup(NoallocDevice** out) {
     std::lock_guard<std::mutex> lk(g_noalloc_mu);
     NoallocDevice& d = g_noalloc[dev];
     if (!d.ready) {
+        // la_ensure_init() is bypassed on purpose (it sizes a memory pool); its device check is repeated here
+        int major = 0, minor = 0;
+        LA_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+        LA_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev));
+        if (major != 10)
+            return la_fail(LA_ERR_CUDA, "la_mul_vec_mat_noalloc: device %d is sm_%d%d; liblinalg_b200 carries sm_100a code only", dev, major, minor);
         void* p = nullptr;
         LA_CUDA(cudaGetSymbolAddress(&p, la_noalloc_scratch));
         if (!p) return la_fail(LA_ERR_CUDA, "la_mul_vec_mat_noalloc: cudaGetSymbolAddress returned NULL");
@@ -343,7 +354,8 @@ la_status noalloc_setup(NoallocDevice** out) {
     return LA_OK;
 }
 
-// Same decomposition as vecmat_cols() above (so the two entry points give identical results),
+// Same decomposition as vecmat_cols() above -- same strips, same kernels, same order of additions -- so the two entry
+// points give bit-identical results for every element type, floats included (tests/test_zz_no_alloc.py asserts it),
 // with the partials in the fixed block.
 template <typename T>
 la_status vecmat_cols_noalloc(T* C, const T* A, const T* B, size_t rows, size_t cols, cudaStream_t st, const NoallocDevice& d) {

@@ -110,8 +110,12 @@ la_status reduce_launch(const T* a, const T* b, size_t n, T* out_dev, cudaStream
     const size_t cap = (size_t)sm_count * RedBlocksPerSm<DOT>::value;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
+    static_assert(sizeof(A) <= 8, "partials are at most 8 bytes");
+    if (blocks * sizeof(A) > LA_REDUCE_SCRATCH_BYTES) blocks = LA_REDUCE_SCRATCH_BYTES / sizeof(A);
+    // Always the same request, so a caller that already holds a pointer into this stream's scratch header (the result slot
+    // of reduce_entry, the length slot of la_normalize_vec -- both made with the same request) never sees the block move.
     void* scratch;
-    LA_TRY(la_scratch(st, blocks * sizeof(A), &scratch));
+    LA_TRY(la_scratch(st, LA_REDUCE_SCRATCH_BYTES, &scratch));
     unsigned* ticket = (unsigned*)scratch;                                  // word 0 of the zeroed header
     A* partials = (A*)((char*)scratch + LA_SCRATCH_ZEROED);
     reduce_kernel<T, DOT><<<(unsigned)blocks, RED_THREADS, 0, st>>>(a, b, n, packed, partials, ticket, out_dev);
@@ -127,7 +131,7 @@ la_status reduce_entry(int dtype, bool dot, const void* a, const void* b, size_t
     void* out_dev = out;
     if (out_is_host) {
         // result slot: bytes 16..23 of the scratch header (re-zeroed below)
-        void* scratch; LA_TRY(la_scratch(st, 0, &scratch));
+        void* scratch; LA_TRY(la_scratch(st, LA_REDUCE_SCRATCH_BYTES, &scratch));    // the one request reduce_launch makes too
         out_dev = (char*)scratch + 16;
     }
     LA_DISPATCH_DTYPE(dtype, T, {

@@ -46,6 +46,8 @@ struct DeviceState {
     std::map<cudaStream_t, std::pair<void*, size_t>> scratch;   // per stream: block, capacity
     std::map<cudaStream_t, unsigned*> host_flags;                // per stream: one mapped, page-locked word
     std::map<cudaStream_t, cudaEvent_t> events;                  // per stream: one timing-less event
+    std::map<cudaStream_t, cudaEvent_t> user_streams;            // streams made by la_stream_create, each with the event la_malloc / la_free order it by
+    cudaEvent_t legacy_event = nullptr;                          // recorded on the legacy stream by la_malloc
 };
 std::mutex g_mu;
 std::map<int, DeviceState*> g_devices;
@@ -171,17 +173,43 @@ extern "C" la_status la_sm_count(int* count) {
 }
 
 // ---------------------------------------------------------------- buffers
+// la_malloc / la_free are stream-ordered pool operations on the legacy default stream.  The streams la_stream_create hands
+// out are cudaStreamNonBlocking, which the legacy stream does NOT order itself against, so the two calls do that explicitly:
+//   la_free    the legacy stream first waits for everything queued so far on every la_stream_create stream (an event
+//              each), so the pool cannot hand the block to anyone while a kernel on such a stream still uses it;
+//   la_malloc  every la_stream_create stream then waits for the legacy stream (one event), so work that the new owner queues
+//              on such a stream starts after legacy-stream work on the block's previous owner has drained.
+// With no la_stream_create stream alive (the reference-style synchronous use) both are a single pool call.  Streams the
+// caller made itself with cudaStreamNonBlocking are outside this: synchronise those before la_free (header).
+static la_status order_legacy_after_user_streams(DeviceState* st) {
+    for (auto& kv : st->user_streams) {
+        LA_CUDA(cudaEventRecord(kv.second, kv.first));
+        LA_CUDA(cudaStreamWaitEvent((cudaStream_t)0, kv.second, 0));
+    }
+    return LA_OK;
+}
 extern "C" la_status la_malloc(void** dev_ptr, size_t bytes) {
     if (!dev_ptr) return la_fail(LA_ERR_ARG, "dev_ptr is NULL");
-    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    DeviceState* st = nullptr; LA_TRY(device_state(&st));
     *dev_ptr = nullptr;
     // bytes == 0: Vector::from_vec(vec![]) is legal in the reference; hand out a real pointer.
     cudaError_t e = cudaMallocAsync(dev_ptr, bytes ? bytes : 16, (cudaStream_t)0);
     if (e != cudaSuccess) return la_cuda_fail(e, "cudaMallocAsync", __FILE__, __LINE__);
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!st->user_streams.empty()) {
+        if (!st->legacy_event) LA_CUDA(cudaEventCreateWithFlags(&st->legacy_event, cudaEventDisableTiming));
+        LA_CUDA(cudaEventRecord(st->legacy_event, (cudaStream_t)0));
+        for (auto& kv : st->user_streams) LA_CUDA(cudaStreamWaitEvent(kv.first, st->legacy_event, 0));
+    }
     return LA_OK;
 }
 extern "C" la_status la_free(void* dev_ptr) {
     if (!dev_ptr) return LA_OK;
+    DeviceState* st = nullptr; LA_TRY(device_state(&st));
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        LA_TRY(order_legacy_after_user_streams(st));
+    }
     LA_CUDA(cudaFreeAsync(dev_ptr, (cudaStream_t)0));
     return LA_OK;
 }
@@ -223,8 +251,14 @@ extern "C" la_status la_host_free(void* host_ptr) {
 }
 extern "C" la_status la_stream_create(void** stream) {
     if (!stream) return la_fail(LA_ERR_ARG, "stream is NULL");
-    cudaStream_t s;
+    DeviceState* st = nullptr; LA_TRY(device_state(&st));
+    cudaStream_t s; cudaEvent_t ev;
     LA_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    LA_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        st->user_streams[s] = ev;          // la_malloc / la_free order themselves against it from now on
+    }
     *stream = (void*)s;
     return LA_OK;
 }
@@ -239,6 +273,14 @@ extern "C" la_status la_stream_destroy(void* stream) {
                 cudaStreamSynchronize((cudaStream_t)stream);
                 cudaFree(it->second.first);
                 st->scratch.erase(it);
+            }
+            auto us = st->user_streams.find((cudaStream_t)stream);
+            if (us != st->user_streams.end()) {
+                // frees issued later must still come after this stream's last work: let the legacy stream wait for it now
+                cudaEventRecord(us->second, us->first);
+                cudaStreamWaitEvent((cudaStream_t)0, us->second, 0);
+                cudaEventDestroy(us->second);
+                st->user_streams.erase(us);
             }
         }
     }

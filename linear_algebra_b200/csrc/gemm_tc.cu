@@ -824,7 +824,7 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     // sum|a||b| against a bar of 5.9e-7), so short products use chains of 32; over long products the chain errors average
     // out (K = 8192: 4.8e-8 with 64-chains, 6.2e-8 with 128, 9.6e-8 with 256, bar 5.4e-7) and longer chains halve the
     // accumulator drains that otherwise bound the kernel once the cross terms run as bf16 (8192^3: 3.63 -> 3.30 -> 3.28 ms).
-    // Round 2, measured over 16M outputs against the unrelaxed gate e <= max(E_oracle, 2^-22) (tools/short_k_probe.py): with
+    // Round 2, measured over 16M outputs against the unrelaxed gate e <= max(E_reference_order, 2^-22) (tools/short_k_probe.py): with
     // 64-chains K = 256 comes out at 2.9e-7 against the reference order's 3.1 - 3.7e-7 -- inside, but by so little that a
     // smaller problem (512 x 256 x 384) fell 1 % outside by chance; with 32-chains and tf32 cross terms it is 1.4e-7, K = 384
     // 1.2e-7.  So products below K = 512 use chains of 32 (and tf32 cross terms, la_tc_cross_bf16).

@@ -222,9 +222,9 @@ la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const
  *  LA_GEMM_SIMT    FP32 FMA pipe, each element accumulated k-ascending with one fused multiply-add
  *                  per k: the reference's own order (src/kernels.cl:136-138).
  *  LA_GEMM_3XTF32  tcgen05 tensor cores: every operand split x = hi + lo (hi = tf32(x)); a product is hi*hi + hi*lo + lo*hi:
- *                  three tf32 MMAs below K = 512; from there hi*hi as a tf32 MMA and the two cross terms (2^-11 of
+ *                  three tf32 MMAs below K = 1024; from there hi*hi as a tf32 MMA and the two cross terms (2^-11 of
  *                  the weight) as bf16 MMAs at twice the rate,
- *                  FP32 accumulation in chunks (32 k below K = 512, 64 below K = 2048, 128 below 8192, 256 from
+ *                  FP32 accumulation in chunks (32 k below K = 1024, 64 below K = 2048, 128 below 8192, 256 from
  *                  there; meets the same f32 tolerance as the SIMT
  *                  engine).  Falls back to SIMT for shapes it does not cover
  *                  (M, N >= 128, K >= 32, all multiples of 4) and whenever an operand holds a NaN, an

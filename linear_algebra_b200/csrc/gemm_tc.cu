@@ -827,8 +827,9 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     // Round 2, measured over 16M outputs against the unrelaxed gate e <= max(E_reference_order, 2^-22) (tools/short_k_probe.py): with
     // 64-chains K = 256 comes out at 2.9e-7 against the reference order's 3.1 - 3.7e-7 -- inside, but by so little that a
     // smaller problem (512 x 256 x 384) fell 1 % outside by chance; with 32-chains and tf32 cross terms it is 1.4e-7, K = 384
-    // 1.2e-7.  So products below K = 512 use chains of 32 (and tf32 cross terms, la_tc_cross_bf16).
-    plan.chunk_kb = g_tc_chunk > 0 ? g_tc_chunk : K < 512 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB;
+    // 1.2e-7; K = 512 with 64-chains and bf16 cross terms 2.0 - 2.3e-7 (0.83 of the bar on a 1024^2 output), K = 1024 1.5e-7
+    // (profiles/r2_short_k_probe.txt).  So products below K = 1024 use chains of 32 (and tf32 cross terms, la_tc_cross_bf16).
+    plan.chunk_kb = g_tc_chunk > 0 ? g_tc_chunk : K < 1024 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB;
     plan.num_chunks = (plan.num_kb + plan.chunk_kb - 1) / plan.chunk_kb;
     plan.dp_items = (int)tiles; plan.stream_items = 0; plan.stream_tiles = 0;
     // Ragged last wave: `waves` full waves and `rest` tiles more.  When the remainder fills at most half of the GPU, each of
@@ -885,14 +886,14 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
 // the longer accumulation chains the faster MMAs call for).  Measured on the GPU (tools/acc_probe.py) the error is the same
 // as with tf32 cross terms within 20 % at every K tried (K = 256: 2.4e-7 vs 2.2e-7, bar 4.6e-7; K = 8192: 4.8e-8 vs 4.0e-8):
 // the tensor cores' truncating accumulation dominates both.  With 16M outputs, K = 256: 2.9e-7 (tf32 cross terms 2.5e-7, the
-// reference order itself 3.6e-7), and 4096 x 512 x 4096 runs 0.124 -> 0.113 ms.  Used from K = 512 (round 2: at K = 256 the
-// bf16 form sits at 0.8 - 0.9 of the reference order's error, too close to the unrelaxed gate); shorter products keep three
+// reference order itself 3.6e-7), and 4096 x 512 x 4096 runs 0.124 -> 0.113 ms.  Used from K = 1024 (round 2: at K = 256 the
+// bf16 form sits at 0.8 - 0.9 of the reference order's error, at K = 512 at 0.6 - 0.85: too close to the unrelaxed gate); shorter products keep three
 // tf32 MMAs.
 int g_tc_variant = 0;
 int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross terms, 1 bf16 cross terms whenever K % 8 == 0
 bool la_tc_cross_bf16(size_t K) {
     if (K % 8 != 0 || g_tc_cross == 0 || g_tc_variant != 0) return false;
-    return g_tc_cross > 0 || K >= 512;
+    return g_tc_cross > 0 || K >= 1024;
 }
 
 // Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,

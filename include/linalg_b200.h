@@ -209,6 +209,28 @@ la_status la_mul_vec_mat_noalloc(int dtype, void* C, const void* A, const void* 
  *   C[M x N] = A[M x K] * B[K x N].  C must not alias A or B. */
 la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream);
 
+/* la_mul_mat_mat that also says what ran (the reference has one kernel, so nothing to report there):
+ * info->engine = 0 generic tiled SIMT kernel, 1 TMA-fed SIMT kernel, 2 f32 tensor engine, 3 integer byte-limb tensor
+ * engine; info->padded = 1 if the operands went through zero-padded, aligned copies.  info may be NULL. */
+typedef struct la_gemm_info { int engine; int padded; } la_gemm_info;
+la_status la_mul_mat_mat_info(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, la_gemm_info* info);
+
+/* One B, many products (no counterpart in the reference, whose kernel reads B as it is; SURVEY.md section 8(e): the
+ * row-block sharded product keeps B replicated on every GPU, "broadcast once").  Part of what a product does is work on B
+ * alone: the tensor engines read B transposed and split into planes (f32: tf32 + bf16 planes of B^T; 8/16/32-bit
+ * integers: byte planes of B^T).  la_gemm_prepare_b does that once and keeps the result in a handle;
+ * la_mul_mat_mat_prepared(C, A, handle, M) is then la_mul_mat_mat(dtype, C, A, B, M, K, N) without that part: same engine
+ * selection, same kernels, bit-identical results.  Where no tensor engine applies (f64, 64-bit integers, small or ragged
+ * shapes, LA_GEMM_SIMT, a B with NaN / inf / extreme exponents) the handle holds nothing extra and the product reads B
+ * itself.  B must stay allocated and unchanged while the handle lives (the handle keeps the pointer, not a copy).
+ * la_gemm_prepare_b allocates device memory for the planes (f32: 8 bytes per element of B, integers: sizeof(T)) and
+ * returns when they are complete; la_gemm_prepared_free waits for the device before releasing them.  A handle belongs
+ * to the device it was made on and may be used from any stream and thread (it is read-only after creation). */
+typedef struct la_gemm_prepared la_gemm_prepared;
+la_status la_gemm_prepare_b(int dtype, const void* B, size_t K, size_t N, void* stream, la_gemm_prepared** handle);
+la_status la_mul_mat_mat_prepared(void* C, const void* A, const la_gemm_prepared* handle, size_t M, void* stream);
+la_status la_gemm_prepared_free(la_gemm_prepared* handle);
+
 /* The reference user's whole sequence -- Matrix::from_vec(a) * Matrix::from_vec(b), then to_vec()
  * (src/matrix.rs:39-46, 221-265, src/vector.rs:53-78) -- as one call on HOST buffers: B is uploaded
  * once, A and C stream through in row blocks on separate copy streams so uploads, multiplies and

@@ -80,6 +80,10 @@ SIGNATURES = {
     "la_mul_vec_mat_noalloc": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_mat_mat": [_I, _V, _V, _V, _Z, _Z, _Z, _V],
     "la_mul_mat_mat_host": [_I, _V, _V, _V, _Z, _Z, _Z],
+    "la_mul_mat_mat_info": [_I, _V, _V, _V, _Z, _Z, _Z, _V, _V],
+    "la_gemm_prepare_b": [_I, _V, _Z, _Z, _V, _PV],
+    "la_mul_mat_mat_prepared": [_V, _V, _V, _Z, _V],
+    "la_gemm_prepared_free": [_V],
     "la_set_gemm_mode": [_I],
     "la_get_gemm_mode": [_PI],
     "la_transpose": [_I, _V, _V, _Z, _Z, _V],
@@ -110,33 +114,18 @@ lib.la_user_kernel_type_name.argtypes = [_I]
 lib.la_user_kernel_type_name.restype = ctypes.c_char_p
 lib.la_dtype_size.argtypes = [_I]
 lib.la_dtype_size.restype = ctypes.c_size_t
-# tuning hook (not declared in the public header)
-lib.la_gemm_set_variant.argtypes = [_I]
-lib.la_gemm_set_variant.restype = ctypes.c_int
-lib.la_gemm_tc_set_variant.argtypes = [_I]
-lib.la_gemm_tc_set_variant.restype = ctypes.c_int
-lib.la_gemm_kernel_timing.argtypes = [_I]
-lib.la_gemm_kernel_timing.restype = ctypes.c_int
-lib.la_gemm_kernel_time_ms.argtypes = [ctypes.POINTER(ctypes.c_float), _PI]
-lib.la_gemm_kernel_time_ms.restype = ctypes.c_int
-lib.la_gemm_tc_set_persistent.argtypes = [_I]
-lib.la_gemm_tc_set_persistent.restype = ctypes.c_int
-lib.la_gemm_tc_set_chunk.argtypes = [_I]
-lib.la_gemm_tc_set_chunk.restype = ctypes.c_int
-lib.la_gemm_tc_set_cross.argtypes = [_I]
-lib.la_gemm_tc_set_cross.restype = ctypes.c_int
-lib.la_gemm_tc_set_tile_n.argtypes = [_I]
-lib.la_gemm_tc_set_tile_n.restype = ctypes.c_int
-lib.la_gemm_set_stream_tail.argtypes = [_I]
-lib.la_gemm_set_stream_tail.restype = ctypes.c_int
-lib.la_gemm_set_raster.argtypes = [_I]
-lib.la_gemm_set_raster.restype = ctypes.c_int
-lib.la_gemm_last_engine.argtypes = []
-lib.la_gemm_last_engine.restype = ctypes.c_int
-lib.la_transpose_set_variant.argtypes = [_I]
-lib.la_transpose_set_variant.restype = ctypes.c_int
-lib.la_gemm_last_padded.argtypes = []
-lib.la_gemm_last_padded.restype = ctypes.c_int
+# tuning / introspection hooks (include/linalg_b200_tuning.h)
+TUNING = {
+    "la_gemm_set_variant": [_I], "la_gemm_tc_set_variant": [_I], "la_gemm_tc_set_persistent": [_I], "la_gemm_tc_set_chunk": [_I],
+    "la_gemm_tc_set_cross": [_I], "la_gemm_tc_set_tile_n": [_I], "la_gemm_set_stream_tail": [_I], "la_gemm_set_raster": [_I],
+    "la_gemm_kernel_timing": [_I], "la_gemm_kernel_time_ms": [ctypes.POINTER(ctypes.c_float), _PI],
+    "la_gemm_last_engine": [], "la_gemm_last_padded": [],
+    "la_transpose_set_variant": [_I],
+}
+for _name, _args in TUNING.items():
+    _f = getattr(lib, _name)
+    _f.argtypes = _args
+    _f.restype = ctypes.c_int
 
 
 def check(status):

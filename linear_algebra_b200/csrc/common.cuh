@@ -52,6 +52,17 @@ la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsign
 // One event (no timing) per (device, stream), for waiting on a point inside a chain of launches.
 la_status la_stream_event(cudaStream_t stream, cudaEvent_t* event);
 
+// What la_gemm_prepare_b keeps about a B that many products will share (include/linalg_b200.h): the caller's B itself (the SIMT
+// and generic engines read it as it is) and, where the tensor engines apply, their pre-processed forms of it.  The planes
+// are plain cudaMalloc blocks of the device the handle was made on.
+struct la_gemm_prepared {
+    int dtype = 0; int device = -1;
+    size_t K = 0, N = 0;
+    const void* B = nullptr;                 // caller's K x N matrix: must stay allocated and unchanged while the handle lives
+    float* tc_hi = nullptr; float* tc_lo = nullptr; bool tc_cross_bf16 = false;    // f32: split planes of B^T (gemm_tc.cu); NULL when not applicable
+    uint8_t* limb_planes = nullptr;          // 8/16/32-bit integers: byte planes of B^T (gemm_limb.cu); NULL when not applicable
+};
+
 int la_gemm_raster_group(size_t pair_tiles_m);   // gemm_tc.cu: tile rows per band of the tensor engines' tile order (0 = m-major; tuning hook la_gemm_set_raster)
 
 // ---------------------------------------------------------------- dtype traits

@@ -27,6 +27,7 @@
 //
 // Roofline: FP32 FMA pipe (f32), FP64 pipe (f64), integer multiply-add pipe (integers).  Work: 2*M*N*K flop.
 #include "common.cuh"
+#include "../../include/linalg_b200_tuning.h"
 #include <cuda.h>
 #include <cstdlib>
 #include <mutex>
@@ -457,13 +458,17 @@ int initial_gemm_mode() {
     return LA_GEMM_AUTO;
 }
 int g_gemm_mode = initial_gemm_mode();
-int g_last_padded = 0;        // the last call went through zero-padded temporaries
-int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32, 3 int8-limb tensor cores (la_gemm_last_engine: test hook)
+// What this thread's last product did (la_gemm_last_engine / la_gemm_last_padded / la_mul_mat_mat_info): thread-local, so
+// callers on different threads and streams do not overwrite each other's answer.
+thread_local int g_last_padded = 0;        // went through zero-padded temporaries
+thread_local int g_last_engine = -1;       // 0 generic, 1 TMA SIMT, 2 3xTF32, 3 int8-limb tensor cores
 
 }  // namespace
 
-la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled);   // gemm_tc.cu
-la_status la_gemm_limb(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled);  // gemm_limb.cu
+la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep);   // gemm_tc.cu
+la_status la_gemm_limb(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep);  // gemm_limb.cu
+la_status la_tc_prepare_b(la_gemm_prepared* h, cudaStream_t st);      // gemm_tc.cu
+la_status la_limb_prepare_b(la_gemm_prepared* h, cudaStream_t st);    // gemm_limb.cu
 
 extern "C" la_status la_set_gemm_mode(int mode) {
     if (mode != LA_GEMM_SIMT && mode != LA_GEMM_3XTF32 && mode != LA_GEMM_AUTO) return la_fail(LA_ERR_ARG, "unknown GEMM mode %d", mode);
@@ -482,16 +487,62 @@ extern "C" la_status la_gemm_set_variant(int v) { g_gemm_variant = v; return LA_
 extern "C" int la_gemm_last_engine(void) { return g_last_engine; }
 extern "C" int la_gemm_last_padded(void) { return g_last_padded; }
 
-la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode);
+la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode, const la_gemm_prepared* prep = nullptr);
 
 extern "C" la_status la_mul_mat_mat(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream) {
     return la_mul_mat_mat_impl(dtype, C, A, B, M, K, N, stream, g_gemm_mode);
 }
 
+extern "C" la_status la_mul_mat_mat_info(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, la_gemm_info* info) {
+    g_last_engine = -1; g_last_padded = 0;
+    const la_status s = la_mul_mat_mat_impl(dtype, C, A, B, M, K, N, stream, g_gemm_mode);
+    if (info) { info->engine = g_last_engine; info->padded = g_last_padded; }
+    return s;
+}
+
+// ---------------------------------------------------------------- a B shared by many products
+// What a product does to B before its main kernel -- the tensor engines' split / transposed planes -- depends on B alone.
+// la_gemm_prepare_b does it once; la_mul_mat_mat_prepared then runs la_mul_mat_mat's engine selection with that part
+// skipped: the same kernels on the same bits, so results are bit-identical to la_mul_mat_mat(A, B).  (The row-block
+// sharded multi-GPU product, B replicated on every rank, is the case it is for: SURVEY.md section 8(e) "B broadcast once;
+// report steady-state and cold separately".)
+extern "C" la_status la_gemm_prepare_b(int dtype, const void* B, size_t K, size_t N, void* stream, la_gemm_prepared** handle) {
+    if (!handle) return la_fail(LA_ERR_ARG, "la_gemm_prepare_b: handle is NULL");
+    *handle = nullptr;
+    if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_gemm_prepare_b: unknown dtype %d", dtype);
+    if (!B && K && N) return la_fail(LA_ERR_ARG, "la_gemm_prepare_b: B is NULL");
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    la_gemm_prepared* h = new la_gemm_prepared();
+    h->dtype = dtype; h->device = info->device; h->K = K; h->N = N; h->B = B;
+    la_status s = LA_OK;
+    if (K && N) {
+        if (dtype == LA_F32) s = la_tc_prepare_b(h, (cudaStream_t)stream);
+        else if (dtype != LA_F64 && la_dtype_size(dtype) <= 4) s = la_limb_prepare_b(h, (cudaStream_t)stream);
+    }
+    if (s != LA_OK) { delete h; return s; }
+    *handle = h;
+    return LA_OK;
+}
+extern "C" la_status la_gemm_prepared_free(la_gemm_prepared* handle) {
+    if (!handle) return LA_OK;
+    // products that use the planes may still be queued: a plain cudaFree waits for the device
+    if (handle->tc_hi) cudaFree(handle->tc_hi);         // (tc_lo is the second half of the same block)
+    if (handle->limb_planes) cudaFree(handle->limb_planes);
+    (void)cudaGetLastError();
+    delete handle;
+    return LA_OK;
+}
+extern "C" la_status la_mul_mat_mat_prepared(void* C, const void* A, const la_gemm_prepared* handle, size_t M, void* stream) {
+    if (!handle) return la_fail(LA_ERR_ARG, "la_mul_mat_mat_prepared: handle is NULL");
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    if (info->device != handle->device) return la_fail(LA_ERR_ARG, "la_mul_mat_mat_prepared: the handle was prepared on device %d, current device is %d", handle->device, info->device);
+    return la_mul_mat_mat_impl(handle->dtype, C, A, handle->B, M, handle->K, handle->N, stream, g_gemm_mode, handle);
+}
+
 int la_gemm_current_mode() { return g_gemm_mode; }
 
 // `mode`: LA_GEMM_SIMT / LA_GEMM_3XTF32 / LA_GEMM_AUTO for this call (gemm_host.cu forces SIMT per block).
-la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode) {
+la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode, const la_gemm_prepared* prep) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: unknown dtype %d", dtype);
     if (M == 0 || N == 0) return LA_OK;
     if (!C || !A || !B) return la_fail(LA_ERR_ARG, "la_mul_mat_mat: NULL operand");
@@ -520,13 +571,13 @@ la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, 
     // stay on the k-ascending SIMT engine (the tensor engine gains little there anyway); LA_GEMM_3XTF32 remains the opt-in.
     if (dtype == LA_F32 && (mode == LA_GEMM_3XTF32 || (mode == LA_GEMM_AUTO && big && K >= LA_TC_AUTO_MIN_K))) {
         bool handled = false;
-        LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled));
+        LA_TRY(la_gemm_3xtf32((float*)C, (const float*)A, (const float*)B, M, K, N, st, &handled, prep));
         if (handled) { g_last_engine = 2; return LA_OK; }
     }
     // 8/16/32-bit integers: exact limb products on the INT8 tensor cores (mode SIMT keeps the IMAD engines)
     if (dtype != LA_F32 && dtype != LA_F64 && la_dtype_size(dtype) <= 4 && mode != LA_GEMM_SIMT && big) {
         bool handled = false;
-        LA_TRY(la_gemm_limb(dtype, C, A, B, M, K, N, st, &handled));
+        LA_TRY(la_gemm_limb(dtype, C, A, B, M, K, N, st, &handled, prep));
         if (handled) { g_last_engine = 3; return LA_OK; }
     }
     // Ragged sizes or unaligned bases of a large product: instead of dropping to the generic kernel (a 30x

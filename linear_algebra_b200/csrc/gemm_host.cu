@@ -15,7 +15,7 @@
 #include <map>
 #include <mutex>
 
-la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode);
+la_status la_mul_mat_mat_impl(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, void* stream, int mode, const la_gemm_prepared* prep = nullptr);
 int la_gemm_current_mode();
 la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size_t K, unsigned* flag, cudaStream_t st);
 la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st);

@@ -242,19 +242,26 @@ la_status limb_make_map(CUtensorMap* map, const uint8_t* base, size_t total_rows
     return LA_OK;
 }
 
+// B -> the L byte planes of B^T (the part of the pre-pass that la_gemm_prepare_b can do once)
 template <typename U, int L>
-la_status limb_gemm(U* C, const U* A, const U* B, size_t M, size_t K, size_t N, cudaStream_t st, int sm_count) {
-    using S = LimbShape<L>;
-    const size_t a_plane = M * K, b_plane = N * K;
-    void* scratch; LA_TRY(la_scratch(st, (size_t)L * (a_plane + b_plane), &scratch));
-    uint8_t* a_planes = (uint8_t*)scratch + LA_SCRATCH_ZEROED;
-    uint8_t* b_planes = a_planes + (size_t)L * a_plane;          // a_plane % 16 == 0 keeps this 16-byte aligned
-    limb_split_kernel<U, L><<<(unsigned)sm_count * 8, 256, 0, st>>>(a_planes, A, a_plane / 16, a_plane);
-    LA_LAUNCH_CHECK();
+la_status limb_split_b(uint8_t* b_planes, const U* B, size_t K, size_t N, cudaStream_t st) {
     const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
     if (tk * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "limb engine pre-pass: B is too large");
-    limb_split_transpose_kernel<U, L><<<(unsigned)(tk * tn), 256, 0, st>>>(b_planes, B, K, N, (unsigned)tn, b_plane);
+    limb_split_transpose_kernel<U, L><<<(unsigned)(tk * tn), 256, 0, st>>>(b_planes, B, K, N, (unsigned)tn, N * K);
     LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
+template <typename U, int L>
+la_status limb_gemm(U* C, const U* A, const U* B, size_t M, size_t K, size_t N, cudaStream_t st, int sm_count, const uint8_t* prep_planes) {
+    using S = LimbShape<L>;
+    const size_t a_plane = M * K, b_plane = N * K;
+    void* scratch; LA_TRY(la_scratch(st, (size_t)L * (a_plane + (prep_planes ? 0 : b_plane)), &scratch));
+    uint8_t* a_planes = (uint8_t*)scratch + LA_SCRATCH_ZEROED;
+    const uint8_t* b_planes = prep_planes ? prep_planes : a_planes + (size_t)L * a_plane;          // a_plane % 16 == 0 keeps this 16-byte aligned
+    limb_split_kernel<U, L><<<(unsigned)sm_count * 8, 256, 0, st>>>(a_planes, A, a_plane / 16, a_plane);
+    LA_LAUNCH_CHECK();
+    if (!prep_planes) LA_TRY((limb_split_b<U, L>(const_cast<uint8_t*>(b_planes), B, K, N, st)));
     // Within a plane, rows past M (or N) would run into the next plane instead of reading zeros; they only
     // feed output rows / columns the epilogue never stores, so that is harmless.
     CUtensorMap map_a, map_b;
@@ -273,23 +280,46 @@ la_status limb_gemm(U* C, const U* A, const U* B, size_t M, size_t K, size_t N, 
     return LA_OK;
 }
 
+// the conditions on B alone (la_gemm_prepare_b) and on the whole product
+bool limb_b_ok(int dtype, const void* B, size_t K, size_t N) {
+    const size_t es = la_dtype_size(dtype);
+    return !(es > 4 || dtype == LA_F32 || N < 64 || K < 128 || K % 16 != 0 || (N * es) % 16 != 0 || !la_aligned16(B) || 4 * N >= (1u << 31) || K >= (1u << 31));
+}
+
 }  // namespace
 
-// Integer GEMM on the INT8 tensor cores when the shape allows; *handled says whether it ran.
-la_status la_gemm_limb(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled) {
+// Integer GEMM on the INT8 tensor cores when the shape allows; *handled says whether it ran.  `prep`: byte planes of B^T made
+// earlier by la_limb_prepare_b, or NULL.
+la_status la_gemm_limb(int dtype, void* C, const void* A, const void* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep) {
     *handled = false;
     const size_t es = la_dtype_size(dtype);
-    if (es > 4 || dtype == LA_F32) return LA_OK;
-    if (M < 128 || N < 64 || K < 128 || K % 16 != 0 || (N * es) % 16 != 0 || !la_aligned16(A) || !la_aligned16(B) || !la_aligned16(C) ||
-        4 * M >= (1u << 31) || 4 * N >= (1u << 31) || K >= (1u << 31))
-        return LA_OK;
+    if (!limb_b_ok(dtype, B, K, N) || M < 128 || !la_aligned16(A) || !la_aligned16(C) || 4 * M >= (1u << 31)) return LA_OK;
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    const uint8_t* pp = prep ? prep->limb_planes : nullptr;
     la_status s;
     switch (es) {
-    case 1: s = limb_gemm<uint8_t, 1>((uint8_t*)C, (const uint8_t*)A, (const uint8_t*)B, M, K, N, st, info->sm_count); break;
-    case 2: s = limb_gemm<uint16_t, 2>((uint16_t*)C, (const uint16_t*)A, (const uint16_t*)B, M, K, N, st, info->sm_count); break;
-    default: s = limb_gemm<uint32_t, 4>((uint32_t*)C, (const uint32_t*)A, (const uint32_t*)B, M, K, N, st, info->sm_count); break;
+    case 1: s = limb_gemm<uint8_t, 1>((uint8_t*)C, (const uint8_t*)A, (const uint8_t*)B, M, K, N, st, info->sm_count, pp); break;
+    case 2: s = limb_gemm<uint16_t, 2>((uint16_t*)C, (const uint16_t*)A, (const uint16_t*)B, M, K, N, st, info->sm_count, pp); break;
+    default: s = limb_gemm<uint32_t, 4>((uint32_t*)C, (const uint32_t*)A, (const uint32_t*)B, M, K, N, st, info->sm_count, pp); break;
     }
     if (s == LA_OK) *handled = true;
     return s;
+}
+
+// la_gemm_prepare_b, integer part: the byte planes of B^T, made once (no planes when the shape is outside the engine's).
+la_status la_limb_prepare_b(la_gemm_prepared* h, cudaStream_t st) {
+    if (!limb_b_ok(h->dtype, h->B, h->K, h->N)) return LA_OK;
+    const size_t es = la_dtype_size(h->dtype);
+    uint8_t* planes = nullptr;
+    LA_CUDA(cudaMalloc(&planes, es * h->K * h->N));
+    la_status s;
+    switch (es) {
+    case 1: s = limb_split_b<uint8_t, 1>(planes, (const uint8_t*)h->B, h->K, h->N, st); break;
+    case 2: s = limb_split_b<uint16_t, 2>(planes, (const uint16_t*)h->B, h->K, h->N, st); break;
+    default: s = limb_split_b<uint32_t, 4>(planes, (const uint32_t*)h->B, h->K, h->N, st); break;
+    }
+    if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the byte-plane split of B failed");
+    if (s != LA_OK) { cudaFree(planes); return s; }
+    h->limb_planes = planes;
+    return LA_OK;
 }

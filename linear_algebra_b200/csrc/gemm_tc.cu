@@ -33,6 +33,7 @@
 // note in the producer loop.
 #include <cuda_bf16.h>
 #include "tc_common.cuh"
+#include "../../include/linalg_b200_tuning.h"
 
 la_status la_transpose_raw32(uint32_t* out, const uint32_t* in, size_t R, size_t C, cudaStream_t st);   // transpose.cu
 
@@ -716,6 +717,68 @@ split_transpose_kernel(float* __restrict__ bt_hi, float* __restrict__ bt_lo, con
 }
 
 
+// Both pre-passes as ONE launch: blocks 0 .. b_tiles-1 each turn and split one 64 x 64 tile of B, the blocks after them
+// split A in a grid-stride loop.  One launch less per product, and the A blocks fill the SMs the B tiles' last wave leaves idle.
+// The planes are bit for bit what split_tf32_kernel and split_transpose_kernel write.
+template <bool BF16X>
+__global__ void __launch_bounds__(256)
+split_both_kernel(float* __restrict__ a_hi, float* __restrict__ a_lo, const float* __restrict__ A, size_t a_n4,
+                  float* __restrict__ bt_hi, float* __restrict__ bt_lo, const float* __restrict__ B, size_t K, size_t N, unsigned tiles_n, unsigned b_tiles,
+                  unsigned* flag) {
+    __shared__ float tile[64][65];
+    bool bad = false;
+    if (blockIdx.x < b_tiles) {
+        const size_t k0 = (size_t)(blockIdx.x / tiles_n) * 64, n0 = (size_t)(blockIdx.x % tiles_n) * 64;
+        float4 in[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
+            in[j] = (k0 + r < K && n0 + q * 4 < N) ? __ldcs(reinterpret_cast<const float4*>(B + (k0 + r) * N + n0 + q * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
+            tile[r][q * 4 + 0] = in[j].x; tile[r][q * 4 + 1] = in[j].y; tile[r][q * 4 + 2] = in[j].z; tile[r][q * 4 + 3] = in[j].w;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int idx = threadIdx.x + j * 256, cc = idx / 16, q = idx % 16;      // Bt row n0+cc, columns k0 + q*4 ..
+            float4 h, l;
+            split_one(tile[q * 4 + 0][cc], h.x, l.x, bad); split_one(tile[q * 4 + 1][cc], h.y, l.y, bad);
+            split_one(tile[q * 4 + 2][cc], h.z, l.z, bad); split_one(tile[q * 4 + 3][cc], h.w, l.w, bad);
+            if (n0 + cc < N && k0 + q * 4 < K) {
+                const size_t at = (n0 + cc) * K + k0 + q * 4;
+                __stcs(reinterpret_cast<float4*>(bt_hi + at), h);
+                if constexpr (BF16X) {
+                    uint2* hb = reinterpret_cast<uint2*>(bt_lo);
+                    __stcs(hb + at / 4, pack_bf16x4(h.x, h.y, h.z, h.w));
+                    __stcs(hb + (N * K + at) / 4, pack_bf16x4(tile[q * 4 + 0][cc] - h.x, tile[q * 4 + 1][cc] - h.y, tile[q * 4 + 2][cc] - h.z, tile[q * 4 + 3][cc] - h.w));
+                } else {
+                    __stcs(reinterpret_cast<float4*>(bt_lo + at), l);
+                }
+            }
+        }
+    } else {
+        const size_t stride = (size_t)(gridDim.x - b_tiles) * 256;
+        uint2* hb = reinterpret_cast<uint2*>(a_lo);
+        uint2* lb = hb + a_n4;
+        for (size_t i = (size_t)(blockIdx.x - b_tiles) * 256 + threadIdx.x; i < a_n4; i += stride) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(A) + i);
+            float4 h, l;
+            split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
+            __stcs(reinterpret_cast<float4*>(a_hi) + i, h);
+            if constexpr (BF16X) {
+                __stcs(hb + i, pack_bf16x4(h.x, h.y, h.z, h.w));
+                __stcs(lb + i, pack_bf16x4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
+            } else {
+                __stcs(reinterpret_cast<float4*>(a_lo) + i, l);
+            }
+        }
+    }
+    if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;
+}
+
 // rows x K row-major f32, box = box_rows x 32 (128 bytes), 128-byte swizzle
 la_status tc_make_map(CUtensorMap* map, const float* base, size_t rows, size_t K, int box_rows) {
     EncodeTiledFn enc; LA_TRY(tc_get_encode(&enc));
@@ -977,6 +1040,21 @@ la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, s
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
+// A and B in one launch.
+la_status la_tc_split_both(float* a_hi, float* a_lo, const float* A, size_t M, float* bt_hi, float* bt_lo, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st) {
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
+    const size_t a_n4 = M * K / 4;
+    size_t a_blocks = (a_n4 + 255) / 256;
+    if (a_blocks > (size_t)info->sm_count * 8) a_blocks = (size_t)info->sm_count * 8;
+    if (tk * tn + a_blocks > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "3xTF32 pre-pass: B is too large");
+    const unsigned grid = (unsigned)(tk * tn + a_blocks);
+    if (la_tc_cross_bf16(K)) split_both_kernel<true><<<grid, 256, 0, st>>>(a_hi, a_lo, A, a_n4, bt_hi, bt_lo, B, K, N, (unsigned)tn, (unsigned)(tk * tn), flag);
+    else                     split_both_kernel<false><<<grid, 256, 0, st>>>(a_hi, a_lo, A, a_n4, bt_hi, bt_lo, B, K, N, (unsigned)tn, (unsigned)(tk * tn), flag);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
 // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
 // the GPU.  The one kernel with such loads (variant 5, B planes) is therefore only used when both planes are ordinary
 // device allocations of the current device; anything else takes the same kernel without multicast (variant 3).
@@ -1007,20 +1085,22 @@ bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_
              M >= (1u << 31) || N >= (1u << 31) || K >= (1u << 31));
 }
 
-la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled) {
+// `prep`: planes of B^T made earlier by la_tc_prepare_b (la_gemm_prepare_b), or NULL to split B here.
+la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep) {
     *handled = false;
     if (!la_tc_shape_ok(A, B, C, M, K, N)) return LA_OK;      // the SIMT engine takes it
-    const size_t a_elems = M * K, b_elems = K * N;
+    if (prep && (!prep->tc_hi || prep->tc_cross_bf16 != la_tc_cross_bf16(K))) prep = nullptr;     // no planes, or made under other tuning settings
+    const size_t a_elems = M * K, b_elems = prep ? 0 : K * N;
     void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 2 * b_elems) * sizeof(float), &scratch));
     volatile unsigned* flag_host; unsigned* flag;               // zero-copy flag word of this stream
     LA_TRY(la_host_flag(st, &flag_host, &flag));
     float* a_hi = (float*)((char*)scratch + LA_SCRATCH_ZEROED);
     float* a_lo = a_hi + a_elems;
-    float* b_hi = a_lo + a_elems;                               // B^T (N x K), split
-    float* b_lo = b_hi + b_elems;
+    const float* b_hi = prep ? prep->tc_hi : a_lo + a_elems;    // B^T (N x K), split
+    const float* b_lo = prep ? prep->tc_lo : b_hi + b_elems;
     *flag_host = 0u;                                            // no kernel of this stream that writes it is in flight (each call waits below)
-    LA_TRY(la_tc_split_a(a_hi, a_lo, A, M, K, flag, st));
-    LA_TRY(la_tc_split_bt(b_hi, b_lo, B, K, N, flag, st));
+    if (prep) LA_TRY(la_tc_split_a(a_hi, a_lo, A, M, K, flag, st));
+    else      LA_TRY(la_tc_split_both(a_hi, a_lo, A, M, const_cast<float*>(b_hi), const_cast<float*>(b_lo), B, K, N, flag, st));
     // Were all operands inside the range the split is faithful for?  The product is launched straight behind the pre-pass, so
     // the GPU never idles while the host waits for the pre-pass (only) and reads the word.  If it is set -- inf / NaN / extreme
     // exponents -- the caller runs the plain f32 engine next in the stream, which overwrites whatever this launch left in C.
@@ -1030,5 +1110,21 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
     LA_CUDA(cudaEventSynchronize(split_done));
     if (*flag_host) return LA_OK;
     *handled = true;
+    return LA_OK;
+}
+
+// la_gemm_prepare_b, f32 part: the split planes of B^T, made once.  No planes when B holds values the split cannot represent
+// or the shape is outside the engine's: products with this handle then take the other engines.
+la_status la_tc_prepare_b(la_gemm_prepared* h, cudaStream_t st) {
+    const size_t K = h->K, N = h->N;
+    if (N < 128 || K < 32 || K % 4 != 0 || N % 4 != 0 || !la_aligned16(h->B) || N >= (1u << 31) || K >= (1u << 31)) return LA_OK;
+    float* planes = nullptr;
+    LA_CUDA(cudaMalloc(&planes, 2 * K * N * sizeof(float)));
+    volatile unsigned* flag_host; unsigned* flag;
+    la_status s = la_host_flag(st, &flag_host, &flag);
+    if (s == LA_OK) { *flag_host = 0u; s = la_tc_split_bt(planes, planes + K * N, (const float*)h->B, K, N, flag, st); }
+    if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the split of B failed");
+    if (s != LA_OK || *flag_host) { cudaFree(planes); return s; }        // out-of-range B: no planes, not an error
+    h->tc_hi = planes; h->tc_lo = planes + K * N; h->tc_cross_bf16 = la_tc_cross_bf16(K);
     return LA_OK;
 }

@@ -9,6 +9,7 @@
 //
 // Roofline: HBM.  Algorithmic bytes per element: 2*sizeof(T).
 #include "common.cuh"
+#include "../../include/linalg_b200_tuning.h"
 
 namespace {
 

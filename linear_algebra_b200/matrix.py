@@ -94,6 +94,20 @@ class Matrix:
         r = self.__eq__(other)
         return r if r is NotImplemented else not r
 
+    def prepare(self):
+        """This matrix as the right-hand operand of many products (la_gemm_prepare_b): the work a product does on B
+        alone is done once.  `a.mul_prepared(p)` then equals `a * b` bit for bit.  No counterpart in the reference."""
+        return PreparedMatrix(self)
+
+    def mul_prepared(self, prepared):
+        assert isinstance(prepared, PreparedMatrix), "expected a PreparedMatrix (Matrix.prepare())"
+        assert self.col_count == prepared.matrix.row_count, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (self.col_count, prepared.matrix.row_count)
+        assert self.dtype.code == prepared.matrix.dtype.code, "element types differ"
+        res = Matrix.uninitialized(self.row_count, prepared.matrix.col_count, self.dtype)
+        call("la_mul_mat_mat_prepared", res.data.ptr, self.data.ptr, prepared.handle, self.row_count, _v._STREAM)
+        _v._done()
+        return res
+
     def transpose(self):
         """Not in the reference; named by the north star: out[c*rows + r] = in[r*cols + c]."""
         res = Matrix.uninitialized(self.col_count, self.row_count, self.dtype)
@@ -137,6 +151,28 @@ class Matrix:
         v = self.to_vec()
         rows = ["\t " + ", ".join(repr(x.item()) for x in v[r * self.col_count:(r + 1) * self.col_count]) for r in range(self.row_count)]
         return "Mat%dx%d {\n%s\n}\n" % (self.row_count, self.col_count, "\n".join(rows))
+
+
+class PreparedMatrix:
+    """Handle of la_gemm_prepare_b.  Keeps the Matrix alive (the library keeps B's pointer, not a copy)."""
+    __slots__ = ("matrix", "handle")
+
+    def __init__(self, matrix):
+        import ctypes
+        self.matrix = matrix
+        self.handle = ctypes.c_void_p()
+        call("la_gemm_prepare_b", matrix.dtype.code, matrix.data.ptr, matrix.row_count, matrix.col_count, _v._STREAM, ctypes.byref(self.handle))
+
+    def free(self):
+        if self.handle is not None and self.handle.value:
+            call("la_gemm_prepared_free", self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 def _mul_helper(a, b, a_row_count, a_col_count, b_col_count):     # matrix.rs:240-265

@@ -9,10 +9,11 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "linalg_b200.h")
+TUNING_HEADER = os.path.join(ROOT, "include", "linalg_b200_tuning.h")
 
 
-def declared_functions():
-    src = open(HEADER).read()
+def declared_functions(header=HEADER):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(la_[a-z0-9_]+)\s*\(", src)))
 
@@ -33,6 +34,26 @@ def test_library_exports_every_declared_symbol():
     # and the ctypes table covers the header (so the binding cannot drift silently)
     bound = set(_lib.SIGNATURES) | set(_lib.NON_STATUS)
     assert set(declared_functions()) == bound
+    assert set(declared_functions(TUNING_HEADER)) == set(_lib.TUNING)
+
+
+def test_library_exports_nothing_that_is_not_declared():
+    """The converse: every dynamic symbol the library defines is declared in one of the two headers (the boundary in
+    linalg_b200.h, the tuning / introspection hooks in linalg_b200_tuning.h).  C++ helpers shared between the .cu files and the
+    statically linked CUDA runtime must not leak out (csrc/exports.map)."""
+    import subprocess
+    from linear_algebra_b200 import _lib
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], check=True, capture_output=True, text=True).stdout
+    exported = {line.split()[-1] for line in out.splitlines() if len(line.split()) >= 3}
+    declared = set(declared_functions()) | set(declared_functions(TUNING_HEADER))
+    assert exported == declared, (sorted(exported - declared), sorted(declared - exported))
+
+
+def test_tuning_header_is_plain_c(tmp_path):
+    import subprocess
+    c = tmp_path / "t.c"
+    c.write_text('#include "linalg_b200_tuning.h"\nint main(void){ return 0; }\n')
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", str(c), "-o", str(tmp_path / "t.o")], check=True)
 
 
 def test_header_is_plain_c(tmp_path):

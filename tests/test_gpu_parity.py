@@ -414,6 +414,70 @@ def test_synth_matches_host_mirror(la, name):
         assert got.min() >= -1.0 and got.max() < 1.0 and abs(float(got.mean())) < 0.02
 
 
+# ------------------------------------------------------------------ one B, many products
+@pytest.mark.parametrize("name,shapes", [
+    ("f32", ((512, 1024, 512), (1024, 256, 768), (388, 1004, 260), (2560, 512, 2304), (64, 64, 64), (4096, 64, 4096), (130, 70, 258))),
+    ("i32", ((512, 1024, 512), (700, 304, 260), (64, 64, 64), (130, 70, 258))),
+    ("u16", ((512, 1024, 512),)), ("u8", ((512, 1024, 512),)), ("f64", ((256, 256, 256),)), ("i64", ((130, 70, 258),))])
+def test_prepared_b_is_bit_identical_to_the_plain_product(la, name, shapes):
+    """la_gemm_prepare_b / la_mul_mat_mat_prepared: the same engine selection and kernels as la_mul_mat_mat with the work on
+    B done once -- so the SAME BITS, for every element type, on shapes of every engine (tensor, limb, TMA SIMT, generic,
+    padded), for several A against one handle, and in every mode."""
+    lib = la._lib.lib
+    for M, K, N in shapes:
+        b = gen.values(name, K * N, 95)
+        B = la.Matrix.from_vec(b, K, N, dt(la, name))
+        for mode in (la._lib.GEMM_AUTO, la._lib.GEMM_SIMT, la._lib.GEMM_3XTF32):
+            la._lib.call("la_set_gemm_mode", mode)
+            try:
+                P = B.prepare()
+                for seed in (96, 97):
+                    A = la.Matrix.from_vec(gen.values(name, M * K, seed), M, K, dt(la, name))
+                    plain = (A * B).to_vec(); engine = lib.la_gemm_last_engine()
+                    prepared = A.mul_prepared(P).to_vec()
+                    assert lib.la_gemm_last_engine() == engine, (name, M, K, N, mode)
+                    assert same(plain, prepared), (name, M, K, N, mode, engine)
+                P.free()
+            finally:
+                la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
+def test_prepared_b_with_non_finite_values_takes_the_simt_engine(la):
+    lib = la._lib.lib
+    M = K = N = 512
+    a = gen.values("f32", M * K, 98); b = gen.values("f32", K * N, 99).copy()
+    b[1234] = np.inf
+    A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+    P = B.prepare()
+    got = A.mul_prepared(P).to_vec()
+    assert lib.la_gemm_last_engine() in (0, 1)
+    assert same(got, (A * B).to_vec())
+    with np.errstate(invalid="ignore", over="ignore"):
+        ref = (a.reshape(M, K).astype(np.float64) @ b.reshape(K, N).astype(np.float64)).reshape(-1)
+    assert np.array_equal(np.isinf(got), np.isinf(ref)) and np.array_equal(np.isnan(got), np.isnan(ref))
+    # an A the split cannot represent, against a clean prepared B: same fallback
+    b2 = gen.values("f32", K * N, 100); a2 = a.copy(); a2[77] = np.nan
+    B2 = la.Matrix.from_vec(b2, K, N); P2 = B2.prepare(); A2 = la.Matrix.from_vec(a2, M, K)
+    got2 = A2.mul_prepared(P2).to_vec()
+    assert lib.la_gemm_last_engine() in (0, 1)
+    assert same(got2, (A2 * B2).to_vec())
+
+
+def test_mul_mat_mat_info_reports_the_engine(la):
+    info = (ctypes.c_int * 2)(-1, -1)
+    M = K = N = 512
+    A = la.Matrix.from_vec(gen.values("f32", M * K, 101), M, K); B = la.Matrix.from_vec(gen.values("f32", K * N, 102), K, N)
+    C = la.Matrix.uninitialized(M, N, "f32")
+    la._lib.call("la_mul_mat_mat_info", 8, C.data.ptr, A.data.ptr, B.data.ptr, M, K, N, None, ctypes.cast(info, ctypes.c_void_p))
+    la.synchronize()
+    assert (info[0], info[1]) == (2, 0)
+    assert same(C.to_vec(), (A * B).to_vec())
+    A3 = la.Matrix.from_vec(gen.values("f32", 33 * 17, 103), 33, 17); B3 = la.Matrix.from_vec(gen.values("f32", 17 * 29, 104), 17, 29)
+    C3 = la.Matrix.uninitialized(33, 29, "f32")
+    la._lib.call("la_mul_mat_mat_info", 8, C3.data.ptr, A3.data.ptr, B3.data.ptr, 33, 17, 29, None, ctypes.cast(info, ctypes.c_void_p))
+    assert info[0] == 0
+
+
 # ------------------------------------------------------------------ streamed host-buffer GEMM
 @pytest.mark.parametrize("name,shape", [("f32", (1000, 512, 768)), ("f32", (2304, 1024, 640)), ("i32", (700, 300, 260)), ("u8", (300, 200, 100)), ("f32", (5, 7, 3))])
 def test_mul_host_equals_the_three_call_sequence(la, name, shape):

@@ -154,8 +154,9 @@ la_status la_dot_vec_vec_dev(int dtype, const void* a, const void* b, size_t n, 
  * src/traits.rs:76-78).  Bit-identical to length() followed by `* (1 / length)`. */
 la_status la_normalize_vec(int dtype, void* C, const void* A, size_t n, void* stream);
 
-/* ------------------------------------------------------------------ multi-GPU reductions (no counterpart in
- * the single-device reference).  One process per GPU.  sum / dot over all ranks in ONE
+/* ------------------------------------------------------------------ multi-GPU building blocks (what la_comm is made of;
+ * use the la_*_sharded calls below unless you manage the buffers yourself).  No counterpart in
+ * the single-device reference; SURVEY.md section 8(e).  One process per GPU.  sum / dot over all ranks in ONE
  * launch per rank: the reduction kernel stores its partial into every peer's mailbox over NVLink peer memory and
  * adds the `world` partials in rank order (deterministic, same bits on every rank), instead of a separate
  * collective.  Set-up: every rank creates a mailbox, the 64-byte handles are exchanged by any means (the Python
@@ -175,6 +176,46 @@ la_status la_dot_vec_vec_allreduce(int dtype, const void* a, const void* b, size
  * already be at byte offset (seq & 1) * half_bytes of ITS buffer, written by earlier work on `stream`. */
 la_status la_vec_allreduce(int dtype, void* out_dev, size_t n, void* const* peer_vectors, size_t half_bytes, void* const* peer_mailboxes,
                            int world, int rank, uint64_t seq, void* stream);
+
+/* ------------------------------------------------------------------ multi-GPU: communicator and sharded operations
+ * The N-device replacement for the reference's single global context (src/lib.rs:125-149, 310-335).  One process per GPU;
+ * vectors and matrices are sharded in contiguous row blocks (la_partition).  An la_comm is one rank's view of the group.
+ * The caller supplies ONE primitive, `exchange`: an all-gather of `bytes` bytes per rank between the processes
+ * (recv holds world * bytes, in rank order; return 0 on success) -- implemented with whatever the host program already
+ * has (MPI_Allgather, a torch process group, files, pipes).  It is used to set the group up (cudaIpc handles of the
+ * buffers peers must reach) and for small host-side agreements; the data path itself runs over NVLink / NVSwitch peer
+ * memory inside the library's kernels, with no collective library.  If peer access or cudaIpc is unavailable
+ * (la_comm_info: peer_memory = 0, reason in la_last_error()) sum / dot / == / v x M fall back to the exchange callback,
+ * la_mul_mat_mat_host_sharded to a plain per-rank upload of B, and la_transpose_sharded returns LA_ERR_UNSUPPORTED.
+ * All la_comm_* / la_*_sharded calls are collectives: every rank makes the same calls in the same order with the same
+ * global shapes.  Results are identical on every rank and deterministic (partials combined in rank order with the
+ * element type's own arithmetic).  At most 16 ranks.  One thread per communicator at a time.  A rank that never shows
+ * up makes the others' kernels trap after a bounded wait rather than hang. */
+typedef struct la_comm la_comm;
+typedef int (*la_exchange_fn)(void* user, const void* send, void* recv, size_t bytes);
+la_status la_comm_create(int world, int rank, la_exchange_fn exchange, void* user, la_comm** comm);   /* on the current device */
+la_status la_comm_destroy(la_comm* comm);
+la_status la_comm_info(const la_comm* comm, int* world, int* rank, int* peer_memory);
+la_status la_comm_barrier(la_comm* comm);
+/* rank's block [*lo, *hi) of n elements (rows): contiguous, the first n % world ranks hold one more */
+void la_partition(size_t n, int world, int rank, size_t* lo, size_t* hi);
+/* sum / dot over all ranks' shards (src/vector.rs:256-293, 326-363 for the one-device case): one launch per rank -- the
+ * reduction kernel delivers its partial to every peer and adds the partials in rank order -- and the scalar arrives in
+ * out_host through a zero-copy word, without a device-to-host copy. */
+la_status la_sum_vec_sharded(la_comm* comm, int dtype, const void* data_local, size_t n_local, void* out_host, void* stream);
+la_status la_dot_vec_vec_sharded(la_comm* comm, int dtype, const void* a_local, const void* b_local, size_t n_local, void* out_host, void* stream);
+la_status la_eq_vec_sharded(la_comm* comm, int dtype, const void* A_local, const void* B_local, size_t n_local, int* equal_host, void* stream);
+/* `&Vector * &Matrix` (src/vector.rs:508-539) with v and M co-sharded by rows: C (cols elements) is the full result on
+ * every rank.  Stream-ordered. */
+la_status la_mul_vec_mat_sharded(la_comm* comm, int dtype, void* C, const void* v_local, const void* M_local, size_t rows_local, size_t cols, void* stream);
+/* Transpose of a row-sharded rows x cols matrix, row-sharded again (rank p gets rows la_partition(cols) of the transpose):
+ * one kernel per rank stores the turned pieces straight into the owners' memory over NVLink. */
+la_status la_transpose_sharded(la_comm* comm, int dtype, void* out_local, const void* in_local, size_t rows, size_t cols, void* stream);
+/* la_mul_mat_mat_host with A and C sharded by rows (each rank passes its rows) and all of B on every rank's host: each rank
+ * uploads only 1/world of B over its own PCIe link and the slices travel between the GPUs over NVLink. */
+la_status la_mul_mat_mat_host_sharded(la_comm* comm, int dtype, void* C_host_local, const void* A_host_local, const void* B_host, size_t M, size_t K, size_t N);
+/* (M x v needs no exchange -- la_mul_vec_transpose_mat on the local rows gives the local slice of the result -- and neither
+ * do elementwise operations on co-sharded operands or A (row-sharded) x B (replicated): la_mul_mat_mat / _prepared.) */
 
 /* ------------------------------------------------------------------ matrix x vector
  * {T}_mul_vec_mat src/kernels.cl:143-147, host `&Vector * &Matrix` src/vector.rs:508-539:

@@ -75,6 +75,16 @@ SIGNATURES = {
     "la_vec_allreduce": [_I, _V, _Z, _PV, _Z, _PV, _I, _I, ctypes.c_uint64, _V],
     "la_sum_vec_allreduce": [_I, _V, _Z, _V, _PV, _I, _I, ctypes.c_uint64, _V],
     "la_dot_vec_vec_allreduce": [_I, _V, _V, _Z, _V, _PV, _I, _I, ctypes.c_uint64, _V],
+    "la_comm_create": [_I, _I, _V, _V, _PV],
+    "la_comm_destroy": [_V],
+    "la_comm_info": [_V, _PI, _PI, _PI],
+    "la_comm_barrier": [_V],
+    "la_sum_vec_sharded": [_V, _I, _V, _Z, _V, _V],
+    "la_dot_vec_vec_sharded": [_V, _I, _V, _V, _Z, _V, _V],
+    "la_eq_vec_sharded": [_V, _I, _V, _V, _Z, _PI, _V],
+    "la_mul_vec_mat_sharded": [_V, _I, _V, _V, _V, _Z, _Z, _V],
+    "la_transpose_sharded": [_V, _I, _V, _V, _Z, _Z, _V],
+    "la_mul_mat_mat_host_sharded": [_V, _I, _V, _V, _V, _Z, _Z, _Z],
     "la_mul_vec_mat": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_vec_transpose_mat": [_I, _V, _V, _V, _Z, _Z, _V],
     "la_mul_vec_mat_noalloc": [_I, _V, _V, _V, _Z, _Z, _V],
@@ -92,7 +102,8 @@ SIGNATURES = {
     "la_user_kernel_launch": [_V, _Z, _PV, _V],
     "la_user_kernel_destroy": [_V],
 }
-NON_STATUS = {"la_last_error": ctypes.c_char_p, "la_version": ctypes.c_char_p, "la_dtype_size": ctypes.c_size_t,
+EXCHANGE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+NON_STATUS = {"la_partition": None, "la_last_error": ctypes.c_char_p, "la_version": ctypes.c_char_p, "la_dtype_size": ctypes.c_size_t,
               "la_p2p_mailbox_bytes": ctypes.c_size_t, "la_p2p_handle_bytes": ctypes.c_size_t,
               "la_user_kernel_build_log": ctypes.c_char_p, "la_user_kernel_type_name": ctypes.c_char_p}
 
@@ -100,6 +111,8 @@ for _name, _args in SIGNATURES.items():
     _f = getattr(lib, _name)
     _f.argtypes = _args
     _f.restype = ctypes.c_int
+lib.la_partition.argtypes = [_Z, _I, _I, ctypes.POINTER(_Z), ctypes.POINTER(_Z)]
+lib.la_partition.restype = None
 lib.la_last_error.argtypes = []
 lib.la_last_error.restype = ctypes.c_char_p
 lib.la_version.argtypes = []

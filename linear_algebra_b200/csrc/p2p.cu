@@ -25,7 +25,7 @@ struct PeerTable { MailSlot* box[P2P_MAX_WORLD]; };      // box[p] = rank p's ma
 template <typename T, bool DOT>
 __global__ void __launch_bounds__(P2P_THREADS)
 reduce_allreduce_kernel(const T* __restrict__ a, const T* __restrict__ b, size_t n, bool packed,
-                        typename Arith<T>::Acc* partials, unsigned* ticket, T* out,
+                        typename Arith<T>::Acc* partials, unsigned* ticket, T* out, unsigned long long* done_flag,
                         PeerTable peers, int world, int rank, unsigned long long seq) {
     using A = typename Arith<T>::Acc;
     using P = Pack<T>;
@@ -86,16 +86,18 @@ reduce_allreduce_kernel(const T* __restrict__ a, const T* __restrict__ b, size_t
     // ---- exchange: thread p delivers to peer p, then waits for peer p's delivery
     const int par = (int)(seq & 1ull);
     if ((int)threadIdx.x < world) {
+        // value, then the round's number with release semantics at system scope; the reader acquires the number before it
+        // reads the value.  (One store and one load each way instead of two full system fences per slot.)
         MailSlot* dst = peers.box[threadIdx.x] + par * P2P_MAX_WORLD + rank;
-        *reinterpret_cast<volatile unsigned long long*>(&dst->value) = mine;
-        __threadfence_system();
-        *reinterpret_cast<volatile unsigned long long*>(&dst->seq) = seq;
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&dst->value), "l"(mine) : "memory");
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&dst->seq), "l"(seq) : "memory");
         const MailSlot* src = peers.box[rank] + par * P2P_MAX_WORLD + threadIdx.x;
         unsigned spins = 0;
-        while (*reinterpret_cast<const volatile unsigned long long*>(&src->seq) != seq) {
-            if (++spins > (1u << 27)) __trap();           // a peer never arrived: fail loudly instead of hanging
-        }
-        __threadfence_system();
+        unsigned long long seen;
+        do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(&src->seq) : "memory");
+            if (seen != seq && ++spins > (1u << 27)) __trap();           // a peer never arrived: fail loudly instead of hanging
+        } while (seen != seq);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -106,6 +108,10 @@ reduce_allreduce_kernel(const T* __restrict__ a, const T* __restrict__ b, size_t
             total = Arith<T>::add(total, x);
         }
         *out = total;
+        if (done_flag) {                                  // `out` and the flag may be zero-copy host memory that the host polls
+            __threadfence_system();
+            *reinterpret_cast<volatile unsigned long long*>(done_flag) = seq;
+        }
     }
 }
 
@@ -141,7 +147,7 @@ vector_allreduce_kernel(T* __restrict__ out, size_t n, PeerTable vecs, size_t pa
     }
 }
 
-la_status fused_entry(int dtype, bool dot, const void* a, const void* b, size_t n, void* out_dev, void* const* peer_mailboxes, int world, int rank,
+la_status fused_entry(int dtype, bool dot, const void* a, const void* b, size_t n, void* out_dev, unsigned long long* done_flag, void* const* peer_mailboxes, int world, int rank,
                       unsigned long long seq, void* stream) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "unknown dtype %d", dtype);
     if (!out_dev || !peer_mailboxes || (n && (!a || (dot && !b)))) return la_fail(LA_ERR_ARG, "la_*_allreduce: NULL operand");
@@ -159,17 +165,24 @@ la_status fused_entry(int dtype, bool dot, const void* a, const void* b, size_t 
         const size_t cap = (size_t)info->sm_count * 4;
         if (blocks > cap) blocks = cap;
         if (blocks < 1) blocks = 1;
-        void* scratch; LA_TRY(la_scratch(st, blocks * sizeof(A), &scratch));
+        if (blocks * sizeof(A) > LA_REDUCE_SCRATCH_BYTES) blocks = LA_REDUCE_SCRATCH_BYTES / sizeof(A);
+        void* scratch; LA_TRY(la_scratch(st, LA_REDUCE_SCRATCH_BYTES, &scratch));
         unsigned* ticket = (unsigned*)scratch;
         A* partials = (A*)((char*)scratch + LA_SCRATCH_ZEROED);
-        if (dot) reduce_allreduce_kernel<T, true><<<(unsigned)blocks, P2P_THREADS, 0, st>>>((const T*)a, (const T*)b, n, packed, partials, ticket, (T*)out_dev, pt, world, rank, seq);
-        else     reduce_allreduce_kernel<T, false><<<(unsigned)blocks, P2P_THREADS, 0, st>>>((const T*)a, (const T*)nullptr, n, packed, partials, ticket, (T*)out_dev, pt, world, rank, seq);
+        if (dot) reduce_allreduce_kernel<T, true><<<(unsigned)blocks, P2P_THREADS, 0, st>>>((const T*)a, (const T*)b, n, packed, partials, ticket, (T*)out_dev, done_flag, pt, world, rank, seq);
+        else     reduce_allreduce_kernel<T, false><<<(unsigned)blocks, P2P_THREADS, 0, st>>>((const T*)a, (const T*)nullptr, n, packed, partials, ticket, (T*)out_dev, done_flag, pt, world, rank, seq);
     });
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
 
 }  // namespace
+
+// comm.cu: the same launch with the result (and a completion word) wherever the caller wants it, e.g. zero-copy host memory
+la_status la_fused_reduce(int dtype, bool dot, const void* a, const void* b, size_t n, void* out_dev, unsigned long long* done_flag,
+                          void* const* peer_mailboxes, int world, int rank, unsigned long long seq, void* stream) {
+    return fused_entry(dtype, dot, a, b, n, out_dev, done_flag, peer_mailboxes, world, rank, seq, stream);
+}
 
 // ---------------------------------------------------------------- mailbox plumbing (cudaIpc)
 extern "C" size_t la_p2p_mailbox_bytes(void) { return 4 * P2P_MAX_WORLD * sizeof(MailSlot); }   // [0,2): scalar rounds, [2,4): vector-ready flags
@@ -210,11 +223,11 @@ extern "C" la_status la_p2p_buffer_destroy(void* mailbox_dev) {
 // total.  peer_mailboxes[p] = rank p's mailbox as mapped in this process (own mailbox at [rank]).
 extern "C" la_status la_sum_vec_allreduce(int dtype, const void* data, size_t n, void* out_dev, void* const* peer_mailboxes, int world, int rank,
                                           uint64_t seq, void* stream) {
-    return fused_entry(dtype, false, data, nullptr, n, out_dev, peer_mailboxes, world, rank, seq, stream);
+    return fused_entry(dtype, false, data, nullptr, n, out_dev, nullptr, peer_mailboxes, world, rank, seq, stream);
 }
 extern "C" la_status la_dot_vec_vec_allreduce(int dtype, const void* a, const void* b, size_t n, void* out_dev, void* const* peer_mailboxes, int world,
                                               int rank, uint64_t seq, void* stream) {
-    return fused_entry(dtype, true, a, b, n, out_dev, peer_mailboxes, world, rank, seq, stream);
+    return fused_entry(dtype, true, a, b, n, out_dev, nullptr, peer_mailboxes, world, rank, seq, stream);
 }
 
 // Sum of every rank's vector, rank order, one launch per rank.  Each rank's contribution (n elements) must already

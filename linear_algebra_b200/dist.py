@@ -1,27 +1,24 @@
 """Row-block sharding of Vector / Matrix over one process per GPU.
 
-The reference is single-device (src/lib.rs:310-335: one context, one in-order queue); this is
-the multi-GPU layer the north star adds.  `torch.distributed` (NCCL on GPUs, gloo in the CPU
-tests) is only plumbing: ranks exchange raw bytes with all_gather and every rank finishes the
-combination locally IN RANK ORDER, so results are deterministic, identical on all ranks, and
-need no NCCL support for the element type (NCCL has no 16-bit integers).
+The reference is single-device (src/lib.rs:310-335: one context, one in-order queue); this is the Python face of the
+multi-GPU layer the north star adds.  On GPUs it is a THIN caller: the group, the NVLink peer-memory exchanges and every
+rank-ordered combination live below the C ABI (csrc/comm.cu: la_comm_create, la_*_sharded), and `torch.distributed` is
+used for one thing only -- the byte all-gather that la_comm_create takes as its `exchange` callback.
 
-  op                         partition                              exchange
+  op                         partition                              exchange (all inside liblinalg_b200)
   elementwise / scale        co-sharded ranges                      none
-  sum / dot                  fused: the reduction kernel stores its partial into every peer's mailbox over NVLink
-                             peer memory and adds the partials in rank order (la_*_allreduce, one launch per rank);
-                             fallback / == : local partial + all_gather of one element
+  sum / dot                  la_sum_vec_sharded / la_dot_vec_vec_sharded: one launch per rank, partials delivered to the
+                             peers' mailboxes over NVLink, added in rank order, scalar back through a zero-copy word
+  ==                         la_eq_vec_sharded (one byte per rank through the callback)
   M x v (mul_transpose_mat)  M by rows, v replicated -> rows shard  none
-  v x M                      v and M by rows -> full-length partial fused: partial into an exported buffer, one kernel
-                                                                    adds the peers' partials over NVLink in rank order
-                                                                    (la_vec_allreduce); fallback: all_gather + adds
+  v x M                      la_mul_vec_mat_sharded: partial into an exported buffer, one kernel adds the peers' partials
   M x M                      A, C by rows, B replicated             none
-  M x M on host buffers      A, C by rows; every rank uploads 1/world all_gather of B over NVLink (mul_host)
-                             of B over its own PCIe link
-  transpose                  rows in -> rows of the transpose out   all_to_all of (rows_q x cols_p) blocks
+  M x M on host buffers      la_mul_mat_mat_host_sharded: 1/world of B per PCIe link, slices over NVLink
+  transpose                  la_transpose_sharded: pieces stored straight into the owners' memory
 
-`Comm` wraps the process group; `local` is the module providing Vector/Matrix (the real one by
-default; the CPU tests inject a numpy stand-in to exercise this file's logic under gloo)."""
+`Comm` wraps the process group; `local` is the module providing Vector/Matrix.  The CPU tests (tests/test_dist_gloo.py)
+inject a numpy stand-in under gloo: for that case only, this file carries a host-side restatement of the partition /
+exchange / rank-ordered-combination logic, so the shapes and orders can be checked without a GPU."""
 import numpy as np
 
 
@@ -41,15 +38,6 @@ class Comm:
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.backend = dist.get_backend(group)
 
-    def _tensor(self, ptr, nbytes):
-        import torch
-        if self.backend == "gloo":
-            raise RuntimeError("device pointers need the nccl backend")
-
-        class _View:      # zero-copy view of library-owned device memory
-            __cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2, "strides": None}
-        return torch.as_tensor(_View(), device="cuda")
-
     def all_gather_host(self, payload: bytes):
         """All ranks contribute `payload` (same length everywhere); returns the list in rank order."""
         import torch
@@ -59,53 +47,41 @@ class Comm:
         self.dist.all_gather(out, mine, group=self.group)
         return [bytes(t.cpu().numpy().tobytes()) for t in out]
 
-    def all_gather_device(self, dst_ptr, src_ptr, nbytes):
-        """dst (world * nbytes device bytes, rank order) <- every rank's src (nbytes device bytes)."""
-        out = self._tensor(dst_ptr, nbytes * self.world)
-        self.dist.all_gather_into_tensor(out, self._tensor(src_ptr, nbytes), group=self.group)
-
-    def all_to_all_device(self, dst_ptr, dst_counts, src_ptr, src_counts):
-        """Byte counts per rank; chunks are contiguous and in rank order on both sides."""
-        out = self._tensor(dst_ptr, sum(dst_counts)); inp = self._tensor(src_ptr, sum(src_counts))
-        self.dist.all_to_all_single(out, inp, output_split_sizes=list(dst_counts), input_split_sizes=list(src_counts), group=self.group)
-
     def barrier(self):
         self.dist.barrier(group=self.group)
 
-    # ---- NVLink peer-memory mailboxes for the fused reductions (la_*_allreduce)
-    def p2p(self, m):
-        """Lazily: create this rank's mailbox, exchange the IPC handles, map the peers' mailboxes.  Returns
-        (ctypes array of `world` device pointers, next sequence number) or None when unavailable."""
-        import ctypes
-        st = getattr(self, "_p2p", None)
-        if st is None:
-            st = self._p2p = {"ok": False, "seq": 0}
-            if self.backend == "nccl" and self.world <= 16:
-                try:
-                    hb = m._lib.lib.la_p2p_handle_bytes()
+    # ---- the communicator below the C ABI (csrc/comm.cu)
+    def on_device(self, m):
+        """True when `m` is the real module on GPUs: the la_*_sharded entry points do the work."""
+        return self.backend == "nccl" and hasattr(m, "_lib")
 
-                    def exported(nbytes):
-                        mine = ctypes.c_void_p(); handle = ctypes.create_string_buffer(hb)
-                        m._lib.call("la_p2p_buffer_create", nbytes, ctypes.byref(mine), handle)
-                        ptrs = (ctypes.c_void_p * self.world)()
-                        for r, h in enumerate(self.all_gather_host(handle.raw)):
-                            if r == self.rank:
-                                ptrs[r] = mine.value
-                            else:
-                                p = ctypes.c_void_p()
-                                m._lib.call("la_p2p_buffer_open", ctypes.create_string_buffer(h, hb), ctypes.byref(p))
-                                ptrs[r] = p.value
-                        return ptrs
-                    st.update(ok=True, ptrs=exported(m._lib.lib.la_p2p_mailbox_bytes()), vec_half=4 << 20,
-                              vecs=exported(2 * (4 << 20)), out=m.Vector.uninitialized(8, "u8"))
-                except Exception as e:  # noqa: BLE001  (no peer access, IPC refused, ...): keep the NCCL path
-                    st["error"] = str(e)
-                flags = self.all_gather_host(b"\x01" if st["ok"] else b"\x00")       # all ranks or none
-                st["ok"] = all(f == b"\x01" for f in flags)
-        if not st["ok"]:
-            return None
-        st["seq"] += 1
-        return st["ptrs"], st["seq"], st["out"]
+    def lacomm(self, m):
+        """Lazily: la_comm_create with a callback that all-gathers bytes over the process group."""
+        import ctypes
+        h = getattr(self, "_la", None)
+        if h is None:
+            def xchg(_user, send, recv, nbytes):
+                try:
+                    parts = self.all_gather_host(ctypes.string_at(send, nbytes))
+                    ctypes.memmove(recv, b"".join(parts), nbytes * self.world)
+                    return 0
+                except Exception:  # noqa: BLE001  (reported by the library as a failed exchange)
+                    return 1
+            self._cb = m._lib.EXCHANGE_FN(xchg)              # must outlive the communicator
+            h = ctypes.c_void_p()
+            m._lib.call("la_comm_create", self.world, self.rank, ctypes.cast(self._cb, ctypes.c_void_p), None, ctypes.byref(h))
+            self._la = h
+            w, r, pm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+            m._lib.call("la_comm_info", h, ctypes.byref(w), ctypes.byref(r), ctypes.byref(pm))
+            self._p2p = {"ok": bool(pm.value), "error": None if pm.value else m._lib.lib.la_last_error().decode("utf-8", "replace")}
+            self._m = m
+        return h
+
+    def close(self):
+        h = getattr(self, "_la", None)
+        if h is not None:
+            self._m._lib.call("la_comm_destroy", h)
+            self._la = None
 
 
 def combine_scalars(parts, np_dtype):
@@ -170,8 +146,8 @@ class ShardedVector:
 
     # one exchange: a single element per rank, combined in rank order
     def sum(self):
-        if self.comm.backend == "nccl":
-            return _device_scalar_exchange(self, None)
+        if self.comm.on_device(self._mod()):
+            return _device_scalar(self, None)
         part = self.local.sum()
         return combine_scalars(self.comm.all_gather_host(np.asarray(part).tobytes()), self.local.dtype.np)
 
@@ -179,6 +155,12 @@ class ShardedVector:
         if not isinstance(other, ShardedVector):
             return NotImplemented
         same_shape = self.global_len == other.global_len and self.local.dtype.code == other.local.dtype.code
+        m = self._mod()
+        if same_shape and self.comm.on_device(m):
+            import ctypes
+            eq = ctypes.c_int(0)
+            m._lib.call("la_eq_vec_sharded", self.comm.lacomm(m), self.local.dtype.code, self.local.ptr, other.local.ptr, self.local.len(), ctypes.byref(eq), None)
+            return bool(eq.value)
         mine = bool(same_shape and self.local == other.local)
         return all(p == b"\x01" for p in self.comm.all_gather_host(b"\x01" if mine else b"\x00"))
 
@@ -203,37 +185,21 @@ def _pad(b, n):
     return b + b"\x00" * (n - len(b))
 
 
-def _device_scalar_exchange(a, b):
-    """NCCL path of sum (b is None) / dot: the local partial stays on the device (la_*_dev writes it into
-    this rank's 8-byte slot of a small gather buffer), one in-place all_gather over NVLink, one download
-    of `world` slots, rank-ordered combination on the host."""
+def _device_scalar(a, b):
+    """sum (b is None) / dot over all ranks: one la_*_sharded call (one fused launch per rank, result on the host)."""
     m, comm, dt = a._mod(), a.comm, a.local.dtype
-    fused = comm.p2p(m)
-    if fused is not None:
-        # ONE launch per rank: reduce, store the partial into every peer's mailbox over NVLink, add in rank order
-        ptrs, seq, out = fused
-        if b is None:
-            m._lib.call("la_sum_vec_allreduce", dt.code, a.local.ptr, a.local.len(), out.ptr, ptrs, comm.world, comm.rank, seq, None)
-        else:
-            m._lib.call("la_dot_vec_vec_allreduce", dt.code, a.local.ptr, b.local.ptr, a.local.len(), out.ptr, ptrs, comm.world, comm.rank, seq, None)
-        return np.frombuffer(out.to_vec().tobytes()[:dt.size], dtype=dt.np, count=1)[0]
-    slots = getattr(comm, "_scalar_slots", None)
-    if slots is None:
-        slots = comm._scalar_slots = m.Vector.uninitialized(8 * comm.world, "u8")
-    mine = slots.ptr + 8 * comm.rank
+    out = np.zeros(1, dtype=dt.np)
     if b is None:
-        m._lib.call("la_sum_vec_dev", dt.code, a.local.ptr, a.local.len(), mine, None)
+        m._lib.call("la_sum_vec_sharded", comm.lacomm(m), dt.code, a.local.ptr, a.local.len(), out.ctypes.data, None)
     else:
-        m._lib.call("la_dot_vec_vec_dev", dt.code, a.local.ptr, b.local.ptr, a.local.len(), mine, None)
-    comm.all_gather_device(slots.ptr, mine, 8)           # in place; ordered after the kernel on the default stream
-    raw = slots.to_vec().tobytes()
-    return combine_scalars([raw[8 * r:8 * r + dt.size] for r in range(comm.world)], dt.np)
+        m._lib.call("la_dot_vec_vec_sharded", comm.lacomm(m), dt.code, a.local.ptr, b.local.ptr, a.local.len(), out.ctypes.data, None)
+    return out[0]
 
 
 def dot(a, b):
     a._co(b)
-    if a.comm.backend == "nccl":
-        return _device_scalar_exchange(a, b)
+    if a.comm.on_device(a._mod()):
+        return _device_scalar(a, b)
     part = a._mod().dot(a.local, b.local)
     return combine_scalars(a.comm.all_gather_host(np.asarray(part).tobytes()), a.local.dtype.np)
 
@@ -287,33 +253,16 @@ class ShardedMatrix:
 
 
 def transpose(sm):
-    """Transpose of a row-sharded matrix, row-sharded again (rank p ends up with rows [p_lo, p_hi) of
-    the transpose = columns of the input).  Local transpose, one all_to_all of contiguous
-    (cols_p x rows_q) blocks over NVLink, then strided placement of the received blocks."""
+    """Transpose of a row-sharded matrix, row-sharded again (rank p ends up with rows [p_lo, p_hi) of the transpose =
+    columns of the input): la_transpose_sharded."""
     comm, m = sm.comm, sm._mod()
     rows_g, cols_g = sm.global_rows, sm.col_count
     if comm.world == 1:
         return ShardedMatrix(comm, sm.local.transpose(), cols_g, sm._m)
-    assert comm.backend == "nccl", "the sharded transpose exchanges device buffers (NCCL)"
-    dt = sm.local.dtype
-    my_rows = sm.hi - sm.lo
-    local_t = sm.local.transpose()                          # cols_g x my_rows: rows [p_lo, p_hi) are rank p's block
-    spans = [partition(cols_g, comm.world, p) for p in range(comm.world)]
-    row_spans = [partition(rows_g, comm.world, q) for q in range(comm.world)]
-    my_lo, my_hi = spans[comm.rank]
-    my_cols = my_hi - my_lo
-    send_counts = [(hi - lo) * my_rows * dt.size for lo, hi in spans]
-    recv_counts = [my_cols * (hi - lo) * dt.size for lo, hi in row_spans]
-    recv = m.Vector.uninitialized(sum(recv_counts) // dt.size, dt)
-    m.synchronize()
-    comm.all_to_all_device(recv.ptr, recv_counts, local_t.data.ptr, send_counts)
-    import torch
-    torch.cuda.current_stream().synchronize()
-    out = m.Matrix.uninitialized(my_cols, rows_g, dt)
-    off = 0
-    for q, (lo, hi) in enumerate(row_spans):                # block from rank q: my_cols x (hi - lo), goes to columns [lo, hi)
-        m._lib.call("la_copy_2d", out.data.ptr + lo * dt.size, rows_g * dt.size, recv.ptr + off, (hi - lo) * dt.size, (hi - lo) * dt.size, my_cols, None)
-        off += recv_counts[q]
+    assert comm.on_device(m), "the sharded transpose runs on GPUs (la_transpose_sharded)"
+    lo, hi = partition(cols_g, comm.world, comm.rank)
+    out = m.Matrix.uninitialized(hi - lo, rows_g, sm.local.dtype)
+    m._lib.call("la_transpose_sharded", comm.lacomm(m), sm.local.dtype.code, out.data.ptr, sm.local.data.ptr, rows_g, cols_g, None)
     m.synchronize()
     return ShardedMatrix(comm, out, cols_g, sm._m)
 
@@ -333,17 +282,10 @@ def mul_host(comm, a_shard_host, b_host, a_rows_global, k, n, out=None, local_mo
     assert a.size == rows * k and b.size == k * n
     if out is None:
         out = np.empty(rows * n, dtype=a.dtype)
-    if comm.world == 1 or comm.backend != "nccl" or (k % comm.world) != 0:
+    if comm.world == 1 or not comm.on_device(m):
         m._lib.call("la_mul_mat_mat_host", dt.code, out.ctypes.data, a.ctypes.data, b.ctypes.data, rows, k, n)
         return out
-    import torch
-    bdev = m.Vector.uninitialized(k * n, dt)
-    slice_elems = (k // comm.world) * n
-    m._lib.call("la_upload", bdev.ptr + comm.rank * slice_elems * dt.size, b.ctypes.data + comm.rank * slice_elems * dt.size, slice_elems * dt.size, None)
-    m.synchronize()
-    comm.all_gather_device(bdev.ptr, bdev.ptr + comm.rank * slice_elems * dt.size, slice_elems * dt.size)     # in place
-    torch.cuda.current_stream().synchronize()
-    m._lib.call("la_mul_mat_mat_host", dt.code, out.ctypes.data, a.ctypes.data, bdev.ptr, rows, k, n)
+    m._lib.call("la_mul_mat_mat_host_sharded", comm.lacomm(m), dt.code, out.ctypes.data, a.ctypes.data, b.ctypes.data, a_rows_global, k, n)
     return out
 
 
@@ -362,34 +304,13 @@ def _sharded_vec_mat(sv, sm):
     comm = sv.comm
     if comm.world == 1:
         return sv.local * sm.local
-    fused = comm.p2p(m) if comm.backend == "nccl" else None
-    dtp = sv.local.dtype
-    if fused is not None and sm.col_count * dtp.size <= comm._p2p["vec_half"]:
-        # local partial straight into this rank's exported buffer, then ONE kernel reads every peer's partial over
-        # NVLink and adds them in rank order
-        ptrs, seq, _ = fused
-        st = comm._p2p
-        mine = st["vecs"][comm.rank] + (seq & 1) * st["vec_half"]
-        m._lib.call("la_mul_vec_mat", dtp.code, mine, sv.local.ptr, sm.local.data.ptr, sm.local.get_row_count(), sm.col_count, None)
+    if comm.on_device(m):
+        dtp = sv.local.dtype
         out = m.Vector.uninitialized(sm.col_count, dtp)
-        m._lib.call("la_vec_allreduce", dtp.code, out.ptr, sm.col_count, st["vecs"], st["vec_half"], ptrs, comm.world, comm.rank, seq, None)
+        m._lib.call("la_mul_vec_mat_sharded", comm.lacomm(m), dtp.code, out.ptr, sv.local.ptr, sm.local.data.ptr, sm.local.get_row_count(), sm.col_count, None)
         m.synchronize()
         return out
-    partial = sv.local * sm.local                  # la_mul_vec_mat on the local rows
-    if comm.backend == "nccl":
-        dt = partial.dtype
-        nbytes = partial.len() * dt.size
-        gathered = m.Vector.uninitialized(partial.len() * comm.world, dt)
-        m.synchronize()
-        comm.all_gather_device(gathered.ptr, partial.ptr, nbytes)
-        import torch
-        torch.cuda.current_stream().synchronize()
-        acc = m.Vector(dt, gathered.ptr, partial.len(), owner=False)
-        for r in range(1, comm.world):             # ascending rank order: deterministic
-            acc += m.Vector(dt, gathered.ptr + r * nbytes, partial.len(), owner=False)
-        out = acc.clone()
-        del acc
-        return out
+    partial = sv.local * sm.local
     # host path (gloo / CPU tests)
     parts = comm.all_gather_host(partial.to_vec().tobytes())
     dt = partial.dtype.np

@@ -389,18 +389,27 @@ def test_transpose(la, name):
         assert same(T.to_vec(), P.transpose(a, R, C)), (name, R, C)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6, 20, 21, 22, 23, 30, 31, 32, 33, 34])
 def test_transpose_tile_variants(la, variant):
-    """la_transpose_set_variant: other tile shapes of the 4-byte kernel (1, 2) and the persistent, software-pipelined tile walk
-    (3..8 = blocks per SM) against the oracle, on shapes with partial edge tiles and with more tiles than the grid holds."""
+    """la_transpose_set_variant: other tile shapes of the LDG/STG 4-byte kernel (1, 2), its persistent, software-pipelined tile
+    walk (3..8 = blocks per SM), and the warp arrangements / ring depths of the two TMA kernels (20..23: TMA loads and TMA
+    stores; 30..34: TMA loads and st.global stores; 4- and 8-byte elements) against the oracle, on shapes with partial edge
+    boxes, with sub-tiles wholly outside the matrix (fewer rows than a block's warps cover), with more tiles than the
+    persistent grid holds, and with a banded tile walk."""
     P = oracle.port(); lib = la._lib.lib
     lib.la_transpose_set_variant(variant)
     try:
-        for R, C in ((64, 32), (1000, 516), (2064, 1056), (4096, 8192), (16, 4096)):
-            a = gen.values("i32", R * C, 36)
-            assert same(la.Matrix.from_vec(a, R, C).transpose().to_vec(), P.transpose(a, R, C)), (variant, R, C)
+        for band in ((-1, 3) if variant >= 20 else (-1,)):
+            lib.la_transpose_set_band(band)
+            for R, C in ((64, 32), (1000, 516), (2064, 1056), (4096, 8192), (16, 4096), (4, 20000), (20000, 4), (36, 100)):
+                a = gen.values("i32", R * C, 36)
+                assert same(la.Matrix.from_vec(a, R, C).transpose().to_vec(), P.transpose(a, R, C)), (variant, band, R, C)
+            if variant >= 20:
+                for R, C in ((66, 34), (1000, 518), (2050, 4098), (2, 30000)):
+                    a = gen.values("u64", R * C, 37)
+                    assert same(la.Matrix.from_vec(a, R, C, dt(la, "u64")).transpose().to_vec(), P.transpose(a, R, C)), (variant, band, "u64", R, C)
     finally:
-        lib.la_transpose_set_variant(0)
+        lib.la_transpose_set_variant(0); lib.la_transpose_set_band(-1)
 
 
 # ------------------------------------------------------------------ device-side synthetic data

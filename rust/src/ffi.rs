@@ -10,6 +10,8 @@ pub const SUB: c_int = 1;
 pub const MUL: c_int = 2;
 pub const DIV: c_int = 3;
 pub type Stream = *mut c_void;
+/// `la_exchange_fn`: all-gather of `bytes` bytes per rank between the processes of a communicator (0 = success).
+pub type ExchangeFn = unsafe extern "C" fn(user: *mut c_void, send: *const c_void, recv: *mut c_void, bytes: usize) -> c_int;
 pub const DEFAULT_STREAM: Stream = 0 as Stream;
 
 extern "C" {
@@ -34,6 +36,21 @@ extern "C" {
     pub fn la_mul_vec_transpose_mat(dtype: c_int, c: *mut c_void, a: *const c_void, b: *const c_void, rows: usize, cols: usize, stream: Stream) -> c_int;
     pub fn la_mul_mat_mat(dtype: c_int, c: *mut c_void, a: *const c_void, b: *const c_void, m: usize, k: usize, n: usize, stream: Stream) -> c_int;
     pub fn la_mul_mat_mat_host(dtype: c_int, c_host: *mut c_void, a_host: *const c_void, b_host: *const c_void, m: usize, k: usize, n: usize) -> c_int;
+    pub fn la_gemm_prepare_b(dtype: c_int, b: *const c_void, k: usize, n: usize, stream: Stream, handle: *mut *mut c_void) -> c_int;
+    pub fn la_mul_mat_mat_prepared(c: *mut c_void, a: *const c_void, handle: *const c_void, m: usize, stream: Stream) -> c_int;
+    pub fn la_gemm_prepared_free(handle: *mut c_void) -> c_int;
+    // multi-GPU: one process per GPU, row-block shards (csrc/comm.cu); `exchange` all-gathers `bytes` bytes per rank
+    pub fn la_comm_create(world: c_int, rank: c_int, exchange: Option<ExchangeFn>, user: *mut c_void, comm: *mut *mut c_void) -> c_int;
+    pub fn la_comm_destroy(comm: *mut c_void) -> c_int;
+    pub fn la_comm_info(comm: *const c_void, world: *mut c_int, rank: *mut c_int, peer_memory: *mut c_int) -> c_int;
+    pub fn la_comm_barrier(comm: *mut c_void) -> c_int;
+    pub fn la_partition(n: usize, world: c_int, rank: c_int, lo: *mut usize, hi: *mut usize);
+    pub fn la_sum_vec_sharded(comm: *mut c_void, dtype: c_int, data_local: *const c_void, n_local: usize, out_host: *mut c_void, stream: Stream) -> c_int;
+    pub fn la_dot_vec_vec_sharded(comm: *mut c_void, dtype: c_int, a_local: *const c_void, b_local: *const c_void, n_local: usize, out_host: *mut c_void, stream: Stream) -> c_int;
+    pub fn la_eq_vec_sharded(comm: *mut c_void, dtype: c_int, a_local: *const c_void, b_local: *const c_void, n_local: usize, equal_host: *mut c_int, stream: Stream) -> c_int;
+    pub fn la_mul_vec_mat_sharded(comm: *mut c_void, dtype: c_int, c: *mut c_void, v_local: *const c_void, m_local: *const c_void, rows_local: usize, cols: usize, stream: Stream) -> c_int;
+    pub fn la_transpose_sharded(comm: *mut c_void, dtype: c_int, out_local: *mut c_void, in_local: *const c_void, rows: usize, cols: usize, stream: Stream) -> c_int;
+    pub fn la_mul_mat_mat_host_sharded(comm: *mut c_void, dtype: c_int, c_host_local: *mut c_void, a_host_local: *const c_void, b_host: *const c_void, m: usize, k: usize, n: usize) -> c_int;
     pub fn la_transpose(dtype: c_int, out: *mut c_void, input: *const c_void, rows: usize, cols: usize, stream: Stream) -> c_int;
     pub fn la_user_kernel_create(dtype: c_int, source: *const c_char, kernel_name: *const c_char, kernel: *mut *mut c_void) -> c_int;
     pub fn la_user_kernel_launch(kernel: *mut c_void, global_size: usize, arg_values: *mut *mut c_void, stream: Stream) -> c_int;

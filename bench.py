@@ -618,7 +618,7 @@ def run_ours(args):
                             "achieved": round(2 * 2.0 * (n / world) * n * n / kernel_ms / 1e9, 1), "frac": round(2 * 2.0 * (n / world) * n * n / kernel_ms / 1e9 / tf32_peak, 4),
                             "algorithmic_TFLOP/s": round(2.0 * (n / world) * n * n / kernel_ms / 1e9, 1),
                             "note": "CUDA events around each launch of the kernel on its own stream, inside the timed region (rank 0)"}),
-                        "traffic": ncu_traffic("profiles/r1_gemm_3xtf32_8192_ncu_full.txt", "gemm_3xtf32_2cta_kernel")}
+                        "traffic": ncu_traffic("profiles/r2_gemm_3xtf32_8192_ncu_full.txt", "gemm_3xtf32_2cta_kernel")}
             engine_name = "tcgen05 split-f32 (hi*hi as tf32, cross terms as bf16; cta_group::2 CTA pairs, TMA, chunked FP32 accumulation; same f32 gate as SIMT)"
             launches = 3
         else:

@@ -58,7 +58,7 @@ def test_integer_8192_square(la):              # configs[4]: i32 elementwise + G
     del T, t
     # GEMM: Freivalds, exact mod 2^32: C x == A (B x) for random x (device GEMV cross-checks the GEMM) ...
     C = A * B
-    for seed in range(4):
+    for seed in range(32):                      # 32 random vectors, exact mod 2^32
         x = la.Vector.from_vec(np.random.default_rng(seed).integers(-2**31, 2**31 - 1, n, dtype=np.int32))
         assert la.mul_transpose_mat(x, C) == la.mul_transpose_mat(la.mul_transpose_mat(x, B), A)
     # ... and 64 sampled entries against the host
@@ -92,6 +92,18 @@ def test_f32_gemm_8192(la, mode):              # the headline config, on both f3
     for r in (0, n - 1):
         truth = A2[r] @ B2.astype(np.float64)
         assert np.linalg.norm(C[r * n:(r + 1) * n] - truth) / np.linalg.norm(truth) <= 1e-5
+    # ... and through the gate of tests/test_gpu_parity.py at factor 1, at the headline size: four full rows (32768 outputs)
+    # against the reference's own k-ascending order (oracle, both contraction modes) on the same rows
+    import oracle
+    P = oracle.port()
+    rows = [0, 1, n // 2, n - 1]
+    ar = np.ascontiguousarray(a.reshape(n, n)[rows]).reshape(-1)
+    truth = (A2[rows] @ B2.astype(np.float64)).reshape(-1)
+    scale = (np.abs(A2[rows]) @ np.abs(B2.astype(np.float64))).reshape(-1)
+    e_ref = max(float((np.abs(P.mul_mat_mat(ar, b, len(rows), n, n, fma=f).astype(np.float64) - truth) / scale).max()) for f in (False, True))
+    ours = np.concatenate([C[r * n:(r + 1) * n] for r in rows]).astype(np.float64)
+    e_ours = float((np.abs(ours - truth) / scale).max())
+    assert e_ours <= max(e_ref, 2.0 ** -22), (mode, e_ours, e_ref)
 
 
 def test_gemm_16384_banded_tile_order(la):     # C3's largest size; above M = 8192 the tensor engines walk the tiles in bands

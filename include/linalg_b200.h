@@ -189,7 +189,8 @@ la_status la_vec_allreduce(int dtype, void* out_dev, size_t n, void* const* peer
  * la_mul_mat_mat_host_sharded to a plain per-rank upload of B, and la_transpose_sharded returns LA_ERR_UNSUPPORTED.
  * All la_comm_* / la_*_sharded calls are collectives: every rank makes the same calls in the same order with the same
  * global shapes.  Results are identical on every rank and deterministic (partials combined in rank order with the
- * element type's own arithmetic).  At most 16 ranks.  One thread per communicator at a time.  A rank that never shows
+ * element type's own arithmetic).  At most 16 ranks.  One thread per communicator at a time, and one stream for its
+ * stream-ordered calls (v x M, transpose): the ranks meet in small kernels on that stream, not on the host.  A rank that never shows
  * up makes the others' kernels trap after a bounded wait rather than hang. */
 typedef struct la_comm la_comm;
 typedef int (*la_exchange_fn)(void* user, const void* send, void* recv, size_t bytes);

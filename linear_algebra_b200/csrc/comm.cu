@@ -16,6 +16,9 @@
 //   M x M on host buffers   every rank uploads 1/world of B over its own PCIe link, fetches the other slices from the peers'
 //                      staging buffers over NVLink, then streams its rows of A and C (gemm_host.cu)
 //   == / fallbacks     one byte / one element per rank through the exchange callback
+// Where ranks have to meet inside an operation (before and after the transpose's peer stores, around the gather of B) they do so
+// in a small kernel ON the stream (peer_barrier_kernel, p2p.cu): no host synchronisation and no callback on the data path.
+// All sharded calls of one communicator must be issued from one thread, and the stream-ordered ones on one stream.
 // No collective library is involved and no TMA multicast: peers' memory is only touched by ordinary loads, stores and copies.
 // Every rank must call the sharded entry points in the same order with the same global shapes (they are collectives).
 // Results are deterministic and identical on every rank (rank-ordered combination with the element type's own arithmetic).
@@ -28,6 +31,8 @@
 
 la_status la_fused_reduce(int dtype, bool dot, const void* a, const void* b, size_t n, void* out_dev, unsigned long long* done_flag,
                           void* const* peer_mailboxes, int world, int rank, unsigned long long seq, void* stream);      // p2p.cu
+la_status la_peer_barrier(void* const* peer_mailboxes, int world, int rank, unsigned long long seq, cudaStream_t st);    // p2p.cu
+la_status la_mul_mat_mat_host_dev_b(int dtype, void* C_host, const void* A_host, const void* B_dev, cudaEvent_t b_ready, size_t M, size_t K, size_t N);   // gemm_host.cu
 
 namespace {
 
@@ -48,6 +53,7 @@ struct la_comm {
     size_t vec_half = 0;
     unsigned long long seq = 0;
     unsigned long long* res_host = nullptr; unsigned long long* res_dev = nullptr;     // zero-copy: [0] value, [1] sequence number of the round it belongs to
+    cudaStream_t side = nullptr; cudaEvent_t side_done = nullptr, main_done = nullptr;  // the gather of B runs beside the uploads of A
     std::string note;
 };
 
@@ -111,6 +117,9 @@ la_status export_collective(la_comm* c, Exported& e, size_t bytes, bool* ok) {
     return LA_OK;
 }
 
+// Stream-ordered barrier between the ranks (peer memory; p2p.cu) -- no host round trip, unlike barrier() above.
+la_status stream_barrier(la_comm* c, cudaStream_t st) { return la_peer_barrier(c->box.ptr, c->world, c->rank, ++c->seq, st); }
+
 la_status check_comm(const la_comm* c, const char* who) {
     if (!c) return la_fail(LA_ERR_ARG, "%s: comm is NULL", who);
     int dev = -1; LA_CUDA(cudaGetDevice(&dev));
@@ -171,6 +180,8 @@ extern "C" la_status la_comm_destroy(la_comm* c) {
     if (c->world > 1) barrier(c);                          // peers are done with this rank's buffers
     unexport(c, c->box); unexport(c, c->vec); unexport(c, c->stage);
     if (c->res_host) cudaFreeHost(c->res_host);
+    if (c->side) cudaStreamDestroy(c->side);
+    if (c->side_done) cudaEventDestroy(c->side_done);
     (void)cudaGetLastError();
     delete c;
     return LA_OK;
@@ -339,9 +350,12 @@ extern "C" la_status la_transpose_sharded(la_comm* c, int dtype, void* out_local
     const size_t es = la_dtype_size(dtype);
     cudaStream_t st = (cudaStream_t)stream;
     const size_t max_cols = (cols_g + c->world - 1) / c->world;
-    LA_CUDA(cudaStreamSynchronize(st));                     // my earlier copy out of the staging buffer is done ...
-    LA_TRY(ensure_stage(c, max_cols * rows_g * es, "la_transpose_sharded"));
-    LA_TRY(barrier(c));                                     // ... and so is everybody else's: the staging buffers may be overwritten
+    if (c->stage.bytes < max_cols * rows_g * es) {          // (same decision on every rank: it depends on the global shape only)
+        LA_CUDA(cudaStreamSynchronize(st));
+        LA_TRY(ensure_stage(c, max_cols * rows_g * es, "la_transpose_sharded"));
+    }
+    // Everything below is stream-ordered; the ranks meet in two barriers ON the stream (p2p.cu), not on the host.
+    LA_TRY(stream_barrier(c, st));                          // every rank's earlier copy out of its staging buffer is done: they may be overwritten
     const size_t rows_p = hi_p - lo_p;
     if (rows_p) {
         PeerPtrs pp; for (int p = 0; p < COMM_MAX_WORLD; ++p) pp.p[p] = c->stage.ptr[p];
@@ -356,8 +370,7 @@ extern "C" la_status la_transpose_sharded(la_comm* c, int dtype, void* out_local
         }
         LA_LAUNCH_CHECK();
     }
-    LA_CUDA(cudaStreamSynchronize(st));                     // my stores have landed in the peers' memory ...
-    LA_TRY(barrier(c));                                     // ... and everybody's in mine
+    LA_TRY(stream_barrier(c, st));                          // my stores have landed in the peers' memory and everybody's in mine
     if (chi > clo) LA_CUDA(cudaMemcpyAsync(out_local, c->stage.ptr[c->rank], (chi - clo) * rows_g * es, cudaMemcpyDeviceToDevice, st));
     return LA_OK;
 }
@@ -373,19 +386,23 @@ extern "C" la_status la_mul_mat_mat_host_sharded(la_comm* c, int dtype, void* C_
     const size_t rows = hi - lo, es = la_dtype_size(dtype);
     if (c->world == 1 || !c->p2p || K == 0 || N == 0 || K % (size_t)c->world != 0)
         return la_mul_mat_mat_host(dtype, C_host_local, A_host_local, B_host, rows, K, N);       // every rank uploads all of its B
-    cudaStream_t st = (cudaStream_t)0;
-    LA_CUDA(cudaStreamSynchronize(st));
-    LA_TRY(ensure_stage(c, K * N * es, "la_mul_mat_mat_host_sharded"));
-    LA_TRY(barrier(c));                                     // nobody still reads a slice of an earlier B from my staging buffer
+    if (c->stage.bytes < K * N * es) LA_TRY(ensure_stage(c, K * N * es, "la_mul_mat_mat_host_sharded"));
+    if (!c->side) {
+        LA_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+        LA_CUDA(cudaEventCreateWithFlags(&c->side_done, cudaEventDisableTiming));
+    }
+    // The gather of B runs on a stream of its own, beside the uploads of A that la_mul_mat_mat_host_dev_b starts at once; its
+    // compute stream waits for `side_done` before it touches B.  Barriers are kernels on that stream (no host round trip).
+    cudaStream_t st = c->side;
+    LA_TRY(stream_barrier(c, st));                          // nobody still reads a slice of an earlier B from my staging buffer
     const size_t slice = (K / (size_t)c->world) * N * es;
     char* mine = (char*)c->stage.ptr[c->rank];
     LA_CUDA(cudaMemcpyAsync(mine + c->rank * slice, (const char*)B_host + c->rank * slice, slice, cudaMemcpyHostToDevice, st));
-    LA_CUDA(cudaStreamSynchronize(st));
-    LA_TRY(barrier(c));                                     // every slice is on its owner's GPU
+    LA_TRY(stream_barrier(c, st));                          // every slice is on its owner's GPU
     for (int k = 1; k < c->world; ++k) {                    // start with the next rank, so the pulls spread over the peers
         const int p = (c->rank + k) % c->world;
         LA_CUDA(cudaMemcpyAsync(mine + p * slice, (const char*)c->stage.ptr[p] + p * slice, slice, cudaMemcpyDefault, st));
     }
-    LA_CUDA(cudaStreamSynchronize(st));
-    return la_mul_mat_mat_host(dtype, C_host_local, A_host_local, mine, rows, K, N);
+    LA_CUDA(cudaEventRecord(c->side_done, st));
+    return la_mul_mat_mat_host_dev_b(dtype, C_host_local, A_host_local, mine, c->side_done, rows, K, N);
 }

@@ -70,7 +70,10 @@ struct DrainStreams {
 
 }  // namespace
 
-static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N, bool allow_tensor, bool* redo) {
+// `b_ready` != NULL: B_host is a DEVICE buffer of this GPU that is complete once that event has happened (la_mul_mat_mat_host_sharded
+// gathers it over NVLink on another stream); it is used in place, and the uploads of A start at once, in the shadow of the gather.
+static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, const void* B_host, size_t M, size_t K, size_t N, bool allow_tensor, bool* redo,
+                                cudaEvent_t b_ready = nullptr) {
     *redo = false;
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     HostGemmStreams* hs; LA_TRY(host_streams(&hs));
@@ -94,13 +97,14 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
 
     DevBuf B(hs->cmp), Abuf0(hs->cmp), Abuf1(hs->cmp), Cbuf0(hs->cmp), Cbuf1(hs->cmp), bt_hi(hs->cmp), bt_lo(hs->cmp), a_hi0(hs->cmp), a_lo0(hs->cmp), a_hi1(hs->cmp), a_lo1(hs->cmp);
     DrainStreams drain{hs};
-    LA_TRY(B.alloc(K * N * es));
+    if (!b_ready) LA_TRY(B.alloc(K * N * es));
+    const void* Bp = b_ready ? B_host : B.p;
     LA_TRY(Abuf0.alloc(rb * K * es)); LA_TRY(Abuf1.alloc(rb * K * es));
     LA_TRY(Cbuf0.alloc(rb * N * es)); LA_TRY(Cbuf1.alloc(rb * N * es));
     void* Ab[2] = {Abuf0.p, Abuf1.p}; void* Cb[2] = {Cbuf0.p, Cbuf1.p};
 
     // tensor engine for f32 when the mode and the shapes allow: B is split once, up front
-    bool tensor = want_tensor && la_tc_shape_ok(Ab[0], B.p, Cb[0], rb, K, N);
+    bool tensor = want_tensor && la_tc_shape_ok(Ab[0], Bp, Cb[0], rb, K, N);
     float* ah[2] = {nullptr, nullptr}; float* al[2] = {nullptr, nullptr};
     volatile unsigned* flag_host = nullptr; unsigned* flag = nullptr;
     if (tensor) {
@@ -115,10 +119,14 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     LA_CUDA(cudaStreamWaitEvent(hs->in, hs->b_up, 0));
     LA_CUDA(cudaStreamWaitEvent(hs->out, hs->b_up, 0));
 
-    LA_CUDA(cudaMemcpyAsync(B.p, B_host, K * N * es, cudaMemcpyDefault, hs->in));
-    LA_CUDA(cudaEventRecord(hs->b_up, hs->in));
-    LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->b_up, 0));
-    if (tensor) LA_TRY(la_tc_split_bt((float*)bt_hi.p, (float*)bt_lo.p, (const float*)B.p, K, N, flag, hs->cmp));
+    if (b_ready) {
+        LA_CUDA(cudaStreamWaitEvent(hs->cmp, b_ready, 0));
+    } else {
+        LA_CUDA(cudaMemcpyAsync(B.p, B_host, K * N * es, cudaMemcpyDefault, hs->in));
+        LA_CUDA(cudaEventRecord(hs->b_up, hs->in));
+        LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->b_up, 0));
+    }
+    if (tensor) LA_TRY(la_tc_split_bt((float*)bt_hi.p, (float*)bt_lo.p, (const float*)Bp, K, N, flag, hs->cmp));
     if (dbg) fprintf(stderr, "[hostgemm] setup enqueued at %.3f ms (tensor=%d rb=%zu nblocks=%zu)\n", ms_since(), (int)tensor, rb, nblocks);
 
     for (size_t i = 0; i < nblocks; ++i) {
@@ -139,7 +147,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
         } else {
             // (a ragged tail block of a tensor-engine product goes to the SIMT engine: la_gemm_3xtf32 would
             //  reset the range flag this pass is still collecting)
-            LA_TRY(la_mul_mat_mat_impl(dtype, Cb[b], Ab[b], B.p, rows, K, N, hs->cmp, (tensor || !allow_tensor) ? LA_GEMM_SIMT : mode));
+            LA_TRY(la_mul_mat_mat_impl(dtype, Cb[b], Ab[b], Bp, rows, K, N, hs->cmp, (tensor || !allow_tensor) ? LA_GEMM_SIMT : mode));
         }
         LA_CUDA(cudaEventRecord(hs->cmp_done[b], hs->cmp));
         // download
@@ -163,5 +171,14 @@ extern "C" la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_
     bool redo = false;
     LA_TRY(host_gemm_pass(dtype, C_host, A_host, B_host, M, K, N, true, &redo));
     if (redo) LA_TRY(host_gemm_pass(dtype, C_host, A_host, B_host, M, K, N, false, &redo));
+    return LA_OK;
+}
+
+// comm.cu: the same streamed product against a B that is (or is about to be, `b_ready`) resident on this GPU.
+la_status la_mul_mat_mat_host_dev_b(int dtype, void* C_host, const void* A_host, const void* B_dev, cudaEvent_t b_ready, size_t M, size_t K, size_t N) {
+    if (M == 0 || N == 0) return LA_OK;
+    bool redo = false;
+    LA_TRY(host_gemm_pass(dtype, C_host, A_host, B_dev, M, K, N, true, &redo, b_ready));
+    if (redo) LA_TRY(host_gemm_pass(dtype, C_host, A_host, B_dev, M, K, N, false, &redo, b_ready));
     return LA_OK;
 }

@@ -147,6 +147,26 @@ vector_allreduce_kernel(T* __restrict__ out, size_t n, PeerTable vecs, size_t pa
     }
 }
 
+// Barrier between the ranks ON THE STREAM: thread p announces round `seq` to peer p and waits for peer p's announcement.  Work
+// queued before it on this stream (stores into peers' memory included) has completed before any peer sees the announcement;
+// work queued behind it starts after every rank has arrived.  Rows [4, 6) of the mailbox, one per parity of seq.
+__global__ void __launch_bounds__(32)
+peer_barrier_kernel(PeerTable boxes, int world, int rank, unsigned long long seq) {
+    const int par = (int)(seq & 1ull);
+    if ((int)threadIdx.x < world) {
+        __threadfence_system();
+        MailSlot* dst = boxes.box[threadIdx.x] + (4 + par) * P2P_MAX_WORLD + rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&dst->seq), "l"(seq) : "memory");
+        const MailSlot* src = boxes.box[rank] + (4 + par) * P2P_MAX_WORLD + threadIdx.x;
+        unsigned spins = 0;
+        unsigned long long seen;
+        do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(&src->seq) : "memory");
+            if (seen != seq && ++spins > (1u << 28)) __trap();
+        } while (seen != seq);
+    }
+}
+
 la_status fused_entry(int dtype, bool dot, const void* a, const void* b, size_t n, void* out_dev, unsigned long long* done_flag, void* const* peer_mailboxes, int world, int rank,
                       unsigned long long seq, void* stream) {
     if (!la_valid_dtype(dtype)) return la_fail(LA_ERR_ARG, "unknown dtype %d", dtype);
@@ -184,8 +204,16 @@ la_status la_fused_reduce(int dtype, bool dot, const void* a, const void* b, siz
     return fused_entry(dtype, dot, a, b, n, out_dev, done_flag, peer_mailboxes, world, rank, seq, stream);
 }
 
+la_status la_peer_barrier(void* const* peer_mailboxes, int world, int rank, unsigned long long seq, cudaStream_t st) {
+    PeerTable pt;
+    for (int p = 0; p < P2P_MAX_WORLD; ++p) pt.box[p] = p < world ? (MailSlot*)peer_mailboxes[p] : nullptr;
+    peer_barrier_kernel<<<1, 32, 0, st>>>(pt, world, rank, seq);
+    LA_LAUNCH_CHECK();
+    return LA_OK;
+}
+
 // ---------------------------------------------------------------- mailbox plumbing (cudaIpc)
-extern "C" size_t la_p2p_mailbox_bytes(void) { return 4 * P2P_MAX_WORLD * sizeof(MailSlot); }   // [0,2): scalar rounds, [2,4): vector-ready flags
+extern "C" size_t la_p2p_mailbox_bytes(void) { return 6 * P2P_MAX_WORLD * sizeof(MailSlot); }   // [0,2): scalar rounds, [2,4): vector-ready flags, [4,6): stream barriers
 extern "C" size_t la_p2p_handle_bytes(void) { return sizeof(cudaIpcMemHandle_t); }
 
 // Allocates an exportable device buffer (zeroed; plain cudaMalloc so that cudaIpc can export it) and writes its

@@ -37,6 +37,29 @@ METRIC = "f32_gemm_gflops_8192"
 UNIT = "GFLOP/s"
 
 
+def bind_near_gpu(local):
+    """Run this rank on the CPU cores next to its GPU (NVML's ideal affinity), BEFORE any pinned buffer is allocated, so that
+    the page-locked host buffers land on the GPU's own NUMA node.  What `numactl` / a job launcher would do; with 8 ranks
+    streaming host buffers at once the far socket otherwise carries half of the traffic.  Returns a note for the bench line."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(local)
+        bus = "%08X:%02X:%02X.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return "rank bound to the %d cores next to its GPU (NVML affinity)" % len(cpus)
+    except Exception as e:  # noqa: BLE001
+        return "not bound (%s)" % str(e)[:80]
+    return "not bound"
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -464,6 +487,7 @@ def run_ours(args):
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    numa_note = bind_near_gpu(local) if os.environ.get("LA_BENCH_BIND", "1") != "0" else "not bound (LA_BENCH_BIND=0)"
     la.init(local)
     lib = la._lib
     parity = None
@@ -646,7 +670,8 @@ def run_ours(args):
                        "M": n, "K": n, "N": n, "rows_per_gpu": rows, "l2": "operands 768 MB >> 126 MB L2 (no flush needed)",
                        "engine": engine_name, "engine_flag": args.engine},
             "clocks": clocks,
-            "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int((rows * n + n * n) * 4), "d2h_bytes_per_step": int(rows * n * 4),
+            "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int((rows * n + n * n // world) * 4), "d2h_bytes_per_step": int(rows * n * 4),
+                    "bytes_note": "per rank: its rows of A and its 1/N of B up (the other slices of B arrive over NVLink), its rows of C down", "host": numa_note,
                     "steps": e2e_steps, "api": "mul_host(pinned A, pinned B) -> pinned C  (la_mul_mat_mat_host: row-block streaming, copies overlap the multiply)",
                     "three_call": {"value": round(three_value, 1), "api": "Matrix.from_vec(pinned) x2 -> A * B -> to_vec(pinned)"}},
             "gpu_launches": launches * args.steps,

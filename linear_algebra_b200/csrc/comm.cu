@@ -25,6 +25,7 @@
 #include "common.cuh"
 #include <atomic>
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -386,6 +387,9 @@ extern "C" la_status la_mul_mat_mat_host_sharded(la_comm* c, int dtype, void* C_
     const size_t rows = hi - lo, es = la_dtype_size(dtype);
     if (c->world == 1 || !c->p2p || K == 0 || N == 0 || K % (size_t)c->world != 0)
         return la_mul_mat_mat_host(dtype, C_host_local, A_host_local, B_host, rows, K, N);       // every rank uploads all of its B
+    static const bool dbg = getenv("LA_DEBUG_HOSTGEMM") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto ms_since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
     if (c->stage.bytes < K * N * es) LA_TRY(ensure_stage(c, K * N * es, "la_mul_mat_mat_host_sharded"));
     if (!c->side) {
         LA_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
@@ -404,5 +408,12 @@ extern "C" la_status la_mul_mat_mat_host_sharded(la_comm* c, int dtype, void* C_
         LA_CUDA(cudaMemcpyAsync(mine + p * slice, (const char*)c->stage.ptr[p] + p * slice, slice, cudaMemcpyDefault, st));
     }
     LA_CUDA(cudaEventRecord(c->side_done, st));
-    return la_mul_mat_mat_host_dev_b(dtype, C_host_local, A_host_local, mine, c->side_done, rows, K, N);
+    if (dbg) {
+        fprintf(stderr, "[hostgemm rank %d] gather of B enqueued at %.3f ms\n", c->rank, ms_since());
+        cudaStreamSynchronize(st);
+        fprintf(stderr, "[hostgemm rank %d] gather of B complete at %.3f ms (debug mode waits here)\n", c->rank, ms_since());
+    }
+    const la_status rs = la_mul_mat_mat_host_dev_b(dtype, C_host_local, A_host_local, mine, c->side_done, rows, K, N);
+    if (dbg) fprintf(stderr, "[hostgemm rank %d] done at %.3f ms\n", c->rank, ms_since());
+    return rs;
 }

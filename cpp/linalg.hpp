@@ -272,6 +272,27 @@ class Matrix {                                                      // matrix.rs
         if (!ok) throw Panic("Failed to read all data from file");
         return from_vec(v, hdr[1], hdr[2]);
     }
+    // One B, many products (la_gemm_prepare_b; no counterpart in the reference): `a.mul_prepared(b.prepare())` == `a * b`, bit for
+    // bit, with the part of the product that only depends on b done once.  The handle borrows b: b must outlive it unchanged.
+    class Prepared {
+      public:
+        explicit Prepared(const Matrix& b) : rows_(b.rows_), cols_(b.cols_) { check(la_gemm_prepare_b(Parameter<T>::DTYPE, b.data_.ptr_, b.rows_, b.cols_, nullptr, &h_)); }
+        Prepared(const Prepared&) = delete;
+        Prepared& operator=(const Prepared&) = delete;
+        Prepared(Prepared&& o) noexcept : h_(o.h_), rows_(o.rows_), cols_(o.cols_) { o.h_ = nullptr; }
+        ~Prepared() { if (h_) la_gemm_prepared_free(h_); }
+      private:
+        la_gemm_prepared* h_ = nullptr; size_t rows_, cols_;
+        friend class Matrix;
+    };
+    Prepared prepare() const { return Prepared(*this); }
+    Matrix mul_prepared(const Prepared& b) const {
+        assert_eq(cols_, b.rows_);
+        Matrix c = uninitialized(rows_, b.cols_);
+        check(la_mul_mat_mat_prepared(c.data_.ptr_, data_.ptr_, b.h_, rows_, nullptr));
+        check(la_stream_sync(nullptr));
+        return c;
+    }
     Matrix transpose() const {                                      // not in the reference (north star)
         Matrix r = uninitialized(cols_, rows_);
         check(la_transpose(Parameter<T>::DTYPE, r.data_.ptr_, data_.ptr_, rows_, cols_, nullptr)); check(la_stream_sync(nullptr)); return r;

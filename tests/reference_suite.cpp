@@ -148,11 +148,27 @@ static void user_kernels() {                     // lib.rs:156-171 + vector.rs:8
     CHECK(panics([&] { Vector<TestType>::from_for_each2(a, Vector<TestType>::from_vec({1}), blend); }));
 }
 
+static void prepared_b() {                       // no counterpart in tests.rs: la_gemm_prepare_b gives the same bits as `*`
+    const size_t M = 512, K = 1024, N = 512;
+    std::vector<float> a(M * K), b(K * N);
+    for (size_t i = 0; i < a.size(); ++i) a[i] = (float)((int)(i * 2654435761u % 2001) - 1000) / 1000.0f;
+    for (size_t i = 0; i < b.size(); ++i) b[i] = (float)((int)(i * 40503u % 1999) - 999) / 999.0f;
+    auto A = Matrix<float>::from_vec(a, M, K); auto B = Matrix<float>::from_vec(b, K, N);
+    auto P = B.prepare();
+    CHECK(A.mul_prepared(P) == A * B);
+    std::vector<TestType> ai(M * K), bi(K * N);
+    for (size_t i = 0; i < ai.size(); ++i) ai[i] = (TestType)(i * 2654435761u);
+    for (size_t i = 0; i < bi.size(); ++i) bi[i] = (TestType)(i * 40503u + 7u);
+    auto Ai = Matrix<TestType>::from_vec(ai, M, K); auto Bi = Matrix<TestType>::from_vec(bi, K, N);
+    auto Pi = Bi.prepare();
+    CHECK(Ai.mul_prepared(Pi) == Ai * Bi);
+}
+
 int main() {
     try {
         check(la_init(0));
         f32_vec_mat_mul(); vec_eq(); vec_sum(); vec_vec_dot(); mat_eq(); vec_mat_mul(); mat_mat_mul(); vec_transpose_mat_mul();
-        vec_add(); vec_mul_scl(); save_load_vec(); save_load_mat(); normalize_vec(); length_vec(); vec_clone(); panics_like_the_reference(); user_kernels();
+        vec_add(); vec_mul_scl(); save_load_vec(); save_load_mat(); normalize_vec(); length_vec(); vec_clone(); panics_like_the_reference(); user_kernels(); prepared_b();
     } catch (const std::exception& e) { std::printf("EXCEPTION: %s\n", e.what()); return 2; }
     std::printf(failures ? "%d checks failed\n" : "all reference tests passed (%d failures)\n", failures);
     return failures ? 1 : 0;

@@ -533,8 +533,41 @@ def run_ours(args):
     while not sampler.samples and time.time() < wait_until:
         step(); la.synchronize()
     barrier()
-    e0, e1 = la.Event(), la.Event()
+    import ctypes as _ct
+    # Steady state of the sharded product (SURVEY.md section 8(e): "B broadcast once; report steady-state and cold separately"):
+    # B is replicated and does not change between products, so its share of the pre-pass is done once (la_gemm_prepare_b)
+    # and every step is la_mul_mat_mat_prepared -- bit-identical results.  `value` stays the COLD figure.  The steady steps are
+    # timed in two blocks, one before and one after the cold region, so that a GPU settling into another power state during
+    # the run biases neither figure against the other.
+    hnd = _ct.c_void_p()
+    lib.call("la_gemm_prepare_b", 8, B.data.ptr, n, n, None, _ct.byref(hnd))
+
+    def steady_step():
+        lib.call("la_mul_mat_mat_prepared", C.data.ptr, A.data.ptr, hnd, rows, None)
+
+    def time_steady():
+        for _ in range(3):
+            steady_step()
+        barrier()
+        lib.lib.la_gemm_kernel_timing(1)
+        s0, s1 = la.Event(), la.Event()
+        s0.record()
+        for _ in range(args.steps):
+            steady_step()
+        s1.record()
+        total = s0.elapsed_ms(s1)
+        kms, kn = _ct.c_float(0), _ct.c_int(0)
+        lib.lib.la_gemm_kernel_time_ms(_ct.byref(kms), _ct.byref(kn))
+        lib.lib.la_gemm_kernel_timing(0)
+        barrier()
+        return total, ((kms.value / kn.value) if kn.value else None)
+
     t0 = time.time()
+    steady_a, steady_kernel_a = time_steady()
+    for _ in range(3):
+        step()
+    barrier()
+    e0, e1 = la.Event(), la.Event()
     lib.lib.la_gemm_kernel_timing(1)                # brackets every launch of the dominant (tensor GEMM) kernel with events on its stream
     step_ev = [la.Event() for _ in range(args.steps)]
     e0.record()
@@ -544,7 +577,6 @@ def run_ours(args):
     e1.record()
     ms_total = e0.elapsed_ms(e1)
     per_step = [(e0 if i == 0 else step_ev[i - 1]).elapsed_ms(step_ev[i]) for i in range(args.steps)]
-    import ctypes as _ct
     _kms, _kn = _ct.c_float(0), _ct.c_int(0)
     lib.lib.la_gemm_kernel_time_ms(_ct.byref(_kms), _ct.byref(_kn))
     lib.lib.la_gemm_kernel_timing(0)
@@ -554,30 +586,9 @@ def run_ours(args):
 
     engine_used = lib.lib.la_gemm_last_engine()     # 1 = TMA SIMT, 2 = tcgen05 3xTF32
 
-    # Steady state of the sharded product (SURVEY.md section 8(e): "B broadcast once; report steady-state and cold separately"):
-    # B is replicated and does not change between products, so its share of the pre-pass is done once (la_gemm_prepare_b)
-    # and every step is la_mul_mat_mat_prepared -- bit-identical results.  `value` above stays the COLD figure.
-    hnd = _ct.c_void_p()
-    lib.call("la_gemm_prepare_b", 8, B.data.ptr, n, n, None, _ct.byref(hnd))
-
-    def steady_step():
-        lib.call("la_mul_mat_mat_prepared", C.data.ptr, A.data.ptr, hnd, rows, None)
-
-    for _ in range(3):
-        steady_step()
-    barrier()
-    lib.lib.la_gemm_kernel_timing(1)
-    s0, s1 = la.Event(), la.Event()
-    s0.record()
-    for _ in range(args.steps):
-        steady_step()
-    s1.record()
-    steady_total = s0.elapsed_ms(s1)
-    _sms, _sn = _ct.c_float(0), _ct.c_int(0)
-    lib.lib.la_gemm_kernel_time_ms(_ct.byref(_sms), _ct.byref(_sn))
-    lib.lib.la_gemm_kernel_timing(0)
-    steady_kernel_ms = (_sms.value / _sn.value) if _sn.value else None
-    barrier()
+    steady_b, steady_kernel_b = time_steady()
+    steady_total = 0.5 * (steady_a + steady_b)
+    steady_kernel_ms = (0.5 * (steady_kernel_a + steady_kernel_b)) if (steady_kernel_a and steady_kernel_b) else None
     t2 = time.time()
     lib.call("la_gemm_prepared_free", hnd)
     clocks = sampler.window(t0, t2)                  # the cold and the steady timed regions, back to back
@@ -613,9 +624,9 @@ def run_ours(args):
 
     if dist is not None:
         import torch
-        t = torch.tensor([ms_total, e2e_ms, three_ms, steady_total], device="cuda", dtype=torch.float64)
+        t = torch.tensor([ms_total, e2e_ms, three_ms, steady_total, steady_a, steady_b], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, e2e_ms, three_ms, steady_total = float(t[0]), float(t[1]), float(t[2]), float(t[3])
+        ms_total, e2e_ms, three_ms, steady_total, steady_a, steady_b = (float(x) for x in t)
     ms_step = ms_total / args.steps
     steady_step_ms = steady_total / args.steps
     flop = 2.0 * n * n * n                         # whole job: all ranks' row blocks together
@@ -644,7 +655,7 @@ def run_ours(args):
                             "note": "CUDA events around each launch of the kernel on its own stream, inside the timed region (rank 0)"}),
                         "traffic": ncu_traffic("profiles/r2_gemm_3xtf32_8192_ncu_full.txt", "gemm_3xtf32_2cta_kernel")}
             engine_name = "tcgen05 split-f32 (hi*hi as tf32, cross terms as bf16; cta_group::2 CTA pairs, TMA, chunked FP32 accumulation; same f32 gate as SIMT)"
-            launches = 3
+            launches = 2                            # split_both_kernel + gemm_3xtf32_2cta_kernel per cold step
         else:
             roofline = {"bound": "fp32-fma (SIMT; MEASURED_PEAKS.json has no FP32 figure)", "achieved": round(per_gpu_tflops, 2),
                         "peak": round(simt_peak, 2), "unit": "TFLOP/s", "frac": round(per_gpu_tflops / simt_peak, 4),
@@ -658,6 +669,7 @@ def run_ours(args):
         steady_value = flop / steady_step_ms / 1e6
         roofline["steady_prepared_b"] = {
             "value": round(steady_value, 1), "unit": UNIT, "ms_per_step": round(steady_step_ms, 4),
+            "ms_per_step_before_and_after_the_cold_region": [round(steady_a / args.steps, 4), round(steady_b / args.steps, 4)],
             "frac": (round(2 * steady_value / world / 1e3 / tf32_peak, 4) if engine_used == 2 else round(steady_value / world / 1e3 / simt_peak, 4)),
             "kernel_share_of_step": (round(steady_kernel_ms / steady_step_ms, 4) if steady_kernel_ms else None),
             "note": "same products through la_gemm_prepare_b (once, outside) + la_mul_mat_mat_prepared: the replicated B's split/transpose planes are reused, results bit-identical; `value` of this line is the COLD figure with B's pre-pass inside every step"}

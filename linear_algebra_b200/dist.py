@@ -186,14 +186,22 @@ def _pad(b, n):
 
 
 def _device_scalar(a, b):
-    """sum (b is None) / dot over all ranks: one la_*_sharded call (one fused launch per rank, result on the host)."""
+    """sum (b is None) / dot over all ranks: one la_*_sharded call (one fused launch per rank, result on the host).  The few
+    microseconds of Python around the call are what the ranks drift apart by between rounds, so the path is kept short."""
     m, comm, dt = a._mod(), a.comm, a.local.dtype
-    out = np.zeros(1, dtype=dt.np)
+    h = comm.lacomm(m)
+    out = getattr(comm, "_scalar_out", None)
+    if out is None:
+        out = comm._scalar_out = np.zeros(1, dtype=np.uint64)
+        comm._scalar_ptr = out.ctypes.data
+    lib = m._lib.lib
     if b is None:
-        m._lib.call("la_sum_vec_sharded", comm.lacomm(m), dt.code, a.local.ptr, a.local.len(), out.ctypes.data, None)
+        st = lib.la_sum_vec_sharded(h, dt.code, a.local.ptr, a.local.len(), comm._scalar_ptr, None)
     else:
-        m._lib.call("la_dot_vec_vec_sharded", comm.lacomm(m), dt.code, a.local.ptr, b.local.ptr, a.local.len(), out.ctypes.data, None)
-    return out[0]
+        st = lib.la_dot_vec_vec_sharded(h, dt.code, a.local.ptr, b.local.ptr, a.local.len(), comm._scalar_ptr, None)
+    if st:
+        m._lib.check(st)
+    return out.view(dt.np)[0].copy() if dt.size == 8 else np.frombuffer(out.tobytes()[:dt.size], dtype=dt.np)[0]
 
 
 def dot(a, b):

@@ -205,18 +205,25 @@ def run_reference_arm(args):
 
 # ----------------------------------------------------------------------------- our arm
 def timed_stats(la, fn, iters=10, warmup=3):
-    """Per-launch device times: an event between consecutive calls on the launching stream.  SURVEY.md section 8(d):
-    >= 3 warm-ups, best and median of >= 10."""
+    """Device times from events on the launching stream.  SURVEY.md section 8(d): >= 3 warm-ups, best and median of >= 10.
+    A sample is one launch for kernels of a millisecond or more; shorter kernels are timed in back-to-back batches of k
+    launches (k chosen so that a batch lasts ~1 ms) and a sample is the batch average, so that the few microseconds an event
+    record costs between two launches do not count as kernel time."""
     for _ in range(warmup):
         fn()
     la.synchronize()
+    p0, p1 = la.Event(), la.Event()
+    p0.record(); fn(); p1.record()
+    once = max(p0.elapsed_ms(p1), 1e-3)
+    batch = int(max(1, min(64, round(1.0 / once))))
     ev = [la.Event() for _ in range(iters + 1)]
     ev[0].record()
     for i in range(iters):
-        fn()
+        for _ in range(batch):
+            fn()
         ev[i + 1].record()
-    ms = [ev[i].elapsed_ms(ev[i + 1]) for i in range(iters)]
-    return {"best": min(ms), "median": statistics.median(ms), "mean": sum(ms) / len(ms), "n": iters}
+    ms = [ev[i].elapsed_ms(ev[i + 1]) / batch for i in range(iters)]
+    return {"best": min(ms), "median": statistics.median(ms), "mean": sum(ms) / len(ms), "n": iters * batch, "launches_per_sample": batch}
 
 
 def timed(la, fn, iters, warmup=3):
@@ -236,7 +243,8 @@ def extras(la, hbm_peak, peak_src):
         """st = timed_stats(...): GB/s from the MEDIAN launch, the best beside it."""
         gbs = nbytes / st["median"] / 1e6
         out[name] = {"ms": round(st["median"], 4), "best_ms": round(st["best"], 4), "GB/s": round(gbs, 1), "best_GB/s": round(nbytes / st["best"] / 1e6, 1),
-                     "frac_of_measured_hbm": round(gbs / hbm_peak, 3), "frac_of_nominal_8TBs": round(gbs / 8000.0, 3), "launches": st["n"]}
+                     "frac_of_measured_hbm": round(gbs / hbm_peak, 3), "frac_of_nominal_8TBs": round(gbs / 8000.0, 3), "launches": st["n"],
+                     "launches_per_sample": st["launches_per_sample"]}
 
     for opname, op in (("add", 0), ("sub", 1), ("mul", 2)):
         rec("ew_%s_f32_2^28" % opname, timed_stats(la, lambda: lib.call("la_ew_vec_vec", 8, op, C.ptr, A.ptr, B.ptr, n, None), 10), 12 * n)

@@ -12,7 +12,10 @@ def run(R, C, code=5, name="i32", reps=20):
     sz = lib.la_dtype_size(code)
     X = la.Vector.uninitialized(R * C, name); Z = la.Vector.uninitialized(R * C, name)
     v = np.array([3], la.parameter(name).np)
-    L.call("la_fill", code, X.ptr, v.ctypes.data, R * C, None)
+    if os.environ.get("LA_RANDOM"):
+        L.call("la_synth", code, X.ptr, 0x5EED, R * C, None)          # random words: HBM runs slower on them than on a constant fill
+    else:
+        L.call("la_fill", code, X.ptr, v.ctypes.data, R * C, None)
     for _ in range(3):
         L.call("la_transpose", code, Z.ptr, X.ptr, R, C, None)
     la.synchronize()

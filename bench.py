@@ -698,7 +698,7 @@ def run_ours(args):
                          "dot_f32_2^28": "dot", "sum_f32_2^28": "sum", "dot_f32_2^30": "dot_2^30", "sum_f32_2^30": "sum_2^30",
                          "mat_x_vec_f32_32768^2": "matvec", "vec_x_mat_f32_32768^2": "vecmat", "transpose_i32_8192^2": "transpose_i32",
                          "ew_add_i32_8192^2": "i32_add", "ew_sub_i32_8192^2": "i32_sub", "ew_mul_i32_8192^2": "i32_mul"}
-                roofline["hbm"] = {"_columns": ["GB/s (median launch)", "frac of measured copy peak %.1f" % hbm_peak, "GB/s (best launch)"],
+                roofline["hbm"] = {"_columns": ["GB/s (median sample)", "frac of measured copy peak %.1f" % hbm_peak, "GB/s (best sample)"],
                                    **{v: [ex[k]["GB/s"], ex[k]["frac_of_measured_hbm"], ex[k]["best_GB/s"]] for k, v in short.items() if k in ex}}
                 sw = ex.get("gemm_f32_sweep", {})
                 if "8192" in sw:

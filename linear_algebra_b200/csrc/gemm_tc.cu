@@ -1,10 +1,11 @@
-// csrc/gemm_tc.cu -- split-f32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32; what LA_GEMM_AUTO picks from 512^3 up).
+// csrc/gemm_tc.cu -- split-f32 tensor-core engine for f32 Matrix x Matrix (LA_GEMM_3XTF32; what LA_GEMM_AUTO picks from 512^3
+// multiply-adds up when K >= 256).
 //
 // Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other arithmetic: every f32
 // operand is split x = hi + lo with hi = tf32(x) (round to nearest), and each product is formed as hi*hi + hi*lo + lo*hi
 // on the 5th-generation tensor cores with FP32 accumulation in tensor memory:
-//   K < 256     three tcgen05.mma kind::tf32 per k-step ("3xTF32"), lo = tf32(x - hi);
-//   K >= 256    hi*hi as kind::tf32, the two cross terms (2^-11 of the weight) as kind::f16 bf16 MMAs at twice the rate
+//   K < 1024    three tcgen05.mma kind::tf32 per k-step ("3xTF32"), lo = tf32(x - hi);
+//   K >= 1024   hi*hi as kind::tf32, the two cross terms (2^-11 of the weight) as kind::f16 bf16 MMAs at twice the rate
 //               on the planes bf16(hi) and bf16(x - hi): 2 tensor time units per product instead of 3.
 // The dropped lo*lo term is below 2^-22 relative.  Accumulation runs in chains of 32 .. 256 k inside the tensor cores
 // (their FP32 accumulation truncates) and in FP32 registers across chains.  Results stay inside the f32 bar of DESIGN.md
@@ -28,7 +29,7 @@
 // Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-pass detects anything
 // outside [2^-100, 2^100] (or NaN) and the call then runs the SIMT engine over the same C, so the tensor engine never
 // changes the result class of a product.
-// Roofline: tensor pipe, 3 (K < 256) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
+// Roofline: tensor pipe, 3 (K < 1024) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
 // at 90 % of that floor with the L2 -> SM path (11.6 TB/s of operand loads at 8192^3) close to its own limit, see the
 // note in the producer loop.
 #include <cuda_bf16.h>

@@ -163,7 +163,9 @@ extern "C" la_status la_comm_create(int world, int rank, la_exchange_fn exchange
     memset(rh, 0, 64);
     c->res_host = (unsigned long long*)rh;
     void* rd = nullptr; cudaHostGetDevicePointer(&rd, rh, 0); c->res_dev = (unsigned long long*)rd;
-    if (world > 1) {
+    if (world > 1 && getenv("LA_COMM_NO_PEER_MEMORY")) {      // test hook: behave as on a box without peer access (same on every rank)
+        c->note = "peer memory switched off by LA_COMM_NO_PEER_MEMORY";
+    } else if (world > 1) {
         bool ok = false;
         la_status s = export_collective(c, c->box, la_p2p_mailbox_bytes(), &ok);
         if (s == LA_OK && ok) { c->vec_half = size_t(4) << 20; s = export_collective(c, c->vec, 2 * c->vec_half, &ok); }

@@ -70,7 +70,8 @@ int main(int argc, char** argv) {
     CHECK(la_comm_create(g_world, g_rank, file_exchange, nullptr, &comm));
     int w = 0, r = 0, peer = 0; CHECK(la_comm_info(comm, &w, &r, &peer));
     EXPECT(w == g_world && r == g_rank, "la_comm_info");
-    EXPECT(peer == 1, "peer memory path active");
+    const bool no_peer = getenv("LA_COMM_NO_PEER_MEMORY") != nullptr;       // second run of the test: the fallbacks through the callback
+    EXPECT(peer == (no_peer ? 0 : 1), "peer memory path as expected");
 
     // ---- sum / dot, i32 (bit-exact mod 2^32) and f32
     const size_t n = (1u << 20) + 77;
@@ -118,7 +119,8 @@ int main(int argc, char** argv) {
         size_t clo, chi; la_partition(cols, g_world, g_rank, &clo, &chi);
         void* T = nullptr; CHECK(la_malloc(&T, (chi - clo) * rows * 4));
         std::vector<int32_t> tgot((chi - clo) * rows);
-        for (int round = 0; round < 2; ++round) {
+        if (no_peer) EXPECT(la_transpose_sharded(comm, LA_I32, T, M, rows, cols, nullptr) == LA_ERR_UNSUPPORTED, "transpose needs peer memory");
+        for (int round = 0; round < 2 && !no_peer; ++round) {
             CHECK(la_transpose_sharded(comm, LA_I32, T, M, rows, cols, nullptr));
             CHECK(la_download(tgot.data(), T, tgot.size() * 4, nullptr));
             bool same = true;
@@ -126,6 +128,23 @@ int main(int argc, char** argv) {
             EXPECT(same, "sharded transpose, i32");
         }
         CHECK(la_free(M)); CHECK(la_free(V)); CHECK(la_free(C)); CHECK(la_free(T));
+    }
+    // ---- v x M wider than the exported vector buffers (2 x 4 MiB at creation): they are grown, collectively
+    {
+        const size_t rows = 16 * (size_t)g_world + 3, cols = (1u << 20) + 8;
+        const auto m = ints(rows * cols, 9), v = ints(rows, 10);
+        size_t rlo, rhi; la_partition(rows, g_world, g_rank, &rlo, &rhi);
+        std::vector<uint32_t> want(cols, 0);
+        for (size_t rr = 0; rr < rows; ++rr) for (size_t c = 0; c < cols; ++c) want[c] += (uint32_t)v[rr] * (uint32_t)m[rr * cols + c];
+        void* M = to_device(m.data() + rlo * cols, (rhi - rlo) * cols); void* V = to_device(v.data() + rlo, rhi - rlo);
+        void* C = nullptr; CHECK(la_malloc(&C, cols * 4));
+        std::vector<uint32_t> got(cols);
+        for (int round = 0; round < 2; ++round) {
+            CHECK(la_mul_vec_mat_sharded(comm, LA_I32, C, V, M, rhi - rlo, cols, nullptr));
+            CHECK(la_download(got.data(), C, cols * 4, nullptr));
+            EXPECT(memcmp(got.data(), want.data(), cols * 4) == 0, "sharded v x M wider than the initial exchange buffers");
+        }
+        CHECK(la_free(M)); CHECK(la_free(V)); CHECK(la_free(C));
     }
     // ---- M x M on host buffers, rows of A and C sharded, i32
     {

@@ -22,7 +22,10 @@ def test_comm_program_compiles(tmp_path):
 
 
 @pytest.mark.gpu
-def test_sharded_entry_points_from_cpp_processes(tmp_path):
+@pytest.mark.parametrize("peer_memory", [True, False])
+def test_sharded_entry_points_from_cpp_processes(tmp_path, peer_memory):
+    """peer_memory False: LA_COMM_NO_PEER_MEMORY makes la_comm_create behave as on a box without peer access, so the fallbacks
+    through the exchange callback (and the refusal of the sharded transpose) are exercised too."""
     import ctypes
     from linear_algebra_b200 import _lib
     n = ctypes.c_int(0)
@@ -32,7 +35,11 @@ def test_sharded_entry_points_from_cpp_processes(tmp_path):
     world = 2 if n.value < 4 else 4
     exe = build(tmp_path)
     scratch = tmp_path / "xchg"; scratch.mkdir()
-    procs = [subprocess.Popen([exe, str(r), str(world), str(scratch)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(world)]
+    env = dict(os.environ)
+    env.pop("LA_COMM_NO_PEER_MEMORY", None)
+    if not peer_memory:
+        env["LA_COMM_NO_PEER_MEMORY"] = "1"
+    procs = [subprocess.Popen([exe, str(r), str(world), str(scratch)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env) for r in range(world)]
     outs = [p.communicate(timeout=300) for p in procs]
     for r, (p, (out, err)) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, "rank %d: %s %s" % (r, out[-2000:], err[-2000:])

@@ -408,6 +408,14 @@ def extras_multi(la, comm, hbm_peak):
     rec("sum_f32_2^28_sharded", wall(lambda: A.sum(), 20), 4 * n, device_ms(lambda: A.sum(), 20))
     rec("add_f32_2^28_sharded", wall(lambda: A + B, 20), 12 * n)
     del A, B
+    # BASELINE.json configs[2]: dot / sum over the 2^30 elements of a 32768 x 32768 f32 operand, sharded
+    n30 = 1 << 30
+    lo, hi = ladist.partition(n30, world, rank)
+    A = ladist.ShardedVector(comm, la.Vector.synth(0x5EED0005 + rank, hi - lo, "f32"), n30)
+    B = ladist.ShardedVector(comm, la.Vector.synth(0x5EED1005 + rank, hi - lo, "f32"), n30)
+    rec("dot_f32_2^30_sharded", wall(lambda: ladist.dot(A, B), 20), 8 * n30, device_ms(lambda: ladist.dot(A, B), 20))
+    rec("sum_f32_2^30_sharded", wall(lambda: A.sum(), 20), 4 * n30, device_ms(lambda: A.sum(), 20))
+    del A, B
     r = 32768
     rlo, rhi = ladist.partition(r, world, rank)
     M = ladist.ShardedMatrix(comm, la.Matrix(la.Vector.synth(0x5EED0002 + rank, (rhi - rlo) * r, "f32"), rhi - rlo, r), r)

@@ -250,6 +250,8 @@ def extras(la, hbm_peak, peak_src):
         rec("ew_%s_f32_2^28" % opname, timed_stats(la, lambda: lib.call("la_ew_vec_vec", 8, op, C.ptr, A.ptr, B.ptr, n, None), 10), 12 * n)
     rec("ew_add_assign_f32_2^28", timed_stats(la, lambda: lib.call("la_ew_assign_vec_vec", 8, 0, C.ptr, B.ptr, n, None), 10), 12 * n)
     rec("scale_f32_2^28", timed_stats(la, lambda: lib.call("la_ew_vec_scl", 8, 2, C.ptr, A.ptr, two.ctypes.data, n, None), 10), 8 * n)
+    rec("clone_f32_2^28", timed_stats(la, lambda: lib.call("la_copy", C.ptr, A.ptr, 4 * n, None), 10), 8 * n)        # Vector::clone (vector.rs:700-708)
+    rec("fill_f32_2^28", timed_stats(la, lambda: lib.call("la_fill", 8, C.ptr, one.ctypes.data, n, None), 10), 4 * n)   # Vector::new (vector.rs:30-34): writes only
     eqflag = ctypes.c_int(0)
     lib.call("la_copy", C.ptr, A.ptr, 4 * n, None)                 # equal operands: the whole of both vectors is read, the answer is "equal"
     rec("eq_f32_2^28", timed_stats(la, lambda: lib.call("la_eq_vec", 8, A.ptr, C.ptr, n, ctypes.byref(eqflag), None), 10), 8 * n)
@@ -706,7 +708,7 @@ def run_ours(args):
                 ex = extras(la, hbm_peak, peak_src)
                 line["extra"] = ex
                 # the whole metric in keys the driver's record keeps: vector-op HBM figures, SIMT engine, sweep, C0
-                short = {"ew_add_f32_2^28": "add", "ew_sub_f32_2^28": "sub", "ew_mul_f32_2^28": "mul", "ew_add_assign_f32_2^28": "add_assign", "scale_f32_2^28": "scale", "eq_f32_2^28": "eq",
+                short = {"ew_add_f32_2^28": "add", "ew_sub_f32_2^28": "sub", "ew_mul_f32_2^28": "mul", "ew_add_assign_f32_2^28": "add_assign", "scale_f32_2^28": "scale", "eq_f32_2^28": "eq", "clone_f32_2^28": "clone", "fill_f32_2^28": "fill",
                          "dot_f32_2^28": "dot", "sum_f32_2^28": "sum", "dot_f32_2^30": "dot_2^30", "sum_f32_2^30": "sum_2^30",
                          "mat_x_vec_f32_32768^2": "matvec", "vec_x_mat_f32_32768^2": "vecmat", "transpose_i32_8192^2": "transpose_i32",
                          "ew_add_i32_8192^2": "i32_add", "ew_sub_i32_8192^2": "i32_sub", "ew_mul_i32_8192^2": "i32_mul"}

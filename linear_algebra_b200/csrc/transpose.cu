@@ -225,7 +225,7 @@ la_status transpose_tma_launch(void* out, const void* in, size_t R, size_t C, cu
 // TROWS x TCOLS input tile (dynamic shared memory, padded rows).
 template <typename E, int TROWS, int TCOLS>
 __global__ void __launch_bounds__(TR_THREADS)
-transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x, unsigned tiles_y, unsigned band) {
+transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, size_t C, unsigned tiles_x, unsigned tiles_y, unsigned band, int no_turn) {
     using P = Pack<E>;
     constexpr int V = P::N;               // elements per 16-byte packet
     constexpr int VPR_IN = TCOLS / V;     // packets per input tile row
@@ -248,6 +248,20 @@ transpose_pack_kernel(E* __restrict__ out, const E* __restrict__ in, size_t R, s
         const int r = idx / VPR_IN, q = idx % VPR_IN;
         if (r0 + r < R && c0 + (size_t)q * V < C)
             in_p[j] = ld_stream(reinterpret_cast<const P*>(in + (r0 + r) * C + c0 + (size_t)q * V));
+    }
+    if (no_turn) {
+        // MEASUREMENT ONLY (la_transpose_set_mode(3)): the same global reads and the same global writes -- every tile lands where
+        // its transpose belongs -- without the turn through shared memory (the output is then wrong inside each tile).  What this
+        // runs at is what the memory system gives this access pattern; the difference to the real kernel is the cost of the turn.
+        if constexpr (TROWS == TCOLS) {
+#pragma unroll
+            for (int j = 0; j < LOADS; ++j) {
+                const int idx = threadIdx.x + j * TR_THREADS;
+                const int r = idx / VPR_IN, q = idx % VPR_IN;
+                if (c0 + r < C && r0 + (size_t)q * V < R) st_stream(reinterpret_cast<P*>(out + (c0 + r) * R + r0 + (size_t)q * V), in_p[j]);
+            }
+        }
+        return;
     }
     // ... then scatter them into the tile
 #pragma unroll
@@ -553,7 +567,7 @@ la_status transpose_pack_launch(E* out, const E* in, size_t R, size_t C, cudaStr
     auto kern = transpose_pack_kernel<E, TROWS, TCOLS>;
     constexpr size_t smem = (size_t)TROWS * (TCOLS + 1) * sizeof(E);
     if (smem > 48 * 1024) LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)(gx * gy), TR_THREADS, smem, st>>>(out, in, R, C, (unsigned)gx, (unsigned)gy, g_tr_band > 0 ? (unsigned)g_tr_band : 0u);
+    kern<<<(unsigned)(gx * gy), TR_THREADS, smem, st>>>(out, in, R, C, (unsigned)gx, (unsigned)gy, g_tr_band > 0 ? (unsigned)g_tr_band : 0u, g_tr_mode == 3 ? 1 : 0);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }

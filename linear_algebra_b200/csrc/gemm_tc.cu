@@ -689,6 +689,7 @@ split_transpose_kernel(float* __restrict__ bt_hi, float* __restrict__ bt_lo, con
         const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
         in[j] = (k0 + r < K && n0 + q * 4 < N) ? __ldcs(reinterpret_cast<const float4*>(B + (k0 + r) * N + n0 + q * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    __syncwarp();                            // all four loads are issued before the first shared-memory store
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
@@ -736,6 +737,7 @@ split_both_kernel(float* __restrict__ a_hi, float* __restrict__ a_lo, const floa
             const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
             in[j] = (k0 + r < K && n0 + q * 4 < N) ? __ldcs(reinterpret_cast<const float4*>(B + (k0 + r) * N + n0 + q * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        __syncwarp();                        // all four loads are issued before the first shared-memory store (ptxas otherwise sinks the last one below it)
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;

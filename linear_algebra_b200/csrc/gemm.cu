@@ -54,31 +54,19 @@ gemm_generic_kernel(T* __restrict__ C, const T* __restrict__ A, const T* __restr
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = Acc(0);
 
-    // A tile: 64 rows x 16 k -> As[k][m];  B tile: 16 k x 64 cols -> Bs[k][n]; four elements of each per thread.  The tile of
-    // the NEXT k-step is fetched into registers before the current one is multiplied, so the global loads are in flight
-    // during the arithmetic (and all eight are issued together: left to the straight-line form, the compiler alternated
-    // load / shared-memory store and every load's latency was exposed).
-    constexpr int PER = GG_BM * GG_BK / GG_THREADS;          // 4
-    T ra[PER], rb[PER];
-    auto fetch = [&](size_t k0) {
-#pragma unroll
-        for (int j = 0; j < PER; ++j) {
-            const int idx = threadIdx.x + j * GG_THREADS;
-            const int m = idx / GG_BK, ka = idx % GG_BK, kb = idx / GG_BN, n = idx % GG_BN;
-            ra[j] = (m0 + m < M && k0 + ka < K) ? A[(m0 + m) * K + k0 + ka] : T(0);
-            rb[j] = (k0 + kb < K && n0 + n < N) ? B[(k0 + kb) * N + n0 + n] : T(0);
-        }
-    };
-    fetch(0);
     for (size_t k0 = 0; k0 < K; k0 += GG_BK) {
+        // A tile: 64 rows x 16 k  -> As[k][m];  B tile: 16 k x 64 cols -> Bs[k][n]
 #pragma unroll
-        for (int j = 0; j < PER; ++j) {
-            const int idx = threadIdx.x + j * GG_THREADS;
-            As[idx % GG_BK][idx / GG_BK] = ra[j];
-            Bs[idx / GG_BN][idx % GG_BN] = rb[j];
+        for (int idx = threadIdx.x; idx < GG_BM * GG_BK; idx += GG_THREADS) {
+            const int m = idx / GG_BK, k = idx % GG_BK;
+            As[k][m] = (m0 + m < M && k0 + k < K) ? A[(m0 + m) * K + k0 + k] : T(0);
+        }
+#pragma unroll
+        for (int idx = threadIdx.x; idx < GG_BK * GG_BN; idx += GG_THREADS) {
+            const int k = idx / GG_BN, n = idx % GG_BN;
+            Bs[k][n] = (k0 + k < K && n0 + n < N) ? B[(k0 + k) * N + n0 + n] : T(0);
         }
         __syncthreads();
-        if (k0 + GG_BK < K) fetch(k0 + GG_BK);
 #pragma unroll
         for (int k = 0; k < GG_BK; ++k) {
             T a[4], b[4];

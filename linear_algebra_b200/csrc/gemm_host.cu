@@ -21,6 +21,7 @@ la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size
 la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st);
 la_status la_tc_run(float* C, const float* a_hi, const float* a_lo, const float* bt_hi, const float* bt_lo, size_t M, size_t K, size_t N, cudaStream_t st);
 bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_t K, size_t N);
+bool la_tc_a_direct(size_t K);
 
 namespace {
 
@@ -143,7 +144,7 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
         // wait inside the pipeline.  (If it trips, the whole product is redone in plain f32.)
         if (tensor && rows >= 128 && rows % 4 == 0) {
             LA_TRY(la_tc_split_a(ah[b], al[b], (const float*)Ab[b], rows, K, flag, hs->cmp));
-            LA_TRY(la_tc_run((float*)Cb[b], ah[b], al[b], (const float*)bt_hi.p, (const float*)bt_lo.p, rows, K, N, hs->cmp));
+            LA_TRY(la_tc_run((float*)Cb[b], la_tc_a_direct(K) ? (const float*)Ab[b] : ah[b], al[b], (const float*)bt_hi.p, (const float*)bt_lo.p, rows, K, N, hs->cmp));
         } else {
             // (a ragged tail block of a tensor-engine product goes to the SIMT engine: la_gemm_3xtf32 would
             //  reset the range flag this pass is still collecting)

@@ -647,6 +647,15 @@ __device__ __forceinline__ void split_one(float x, float& hi, float& lo, bool& b
     bad |= !(ax <= 1.2676506e30f) || (ax < 7.8886091e-31f && ax != 0.0f);      // outside [2^-100, 2^100] (or NaN)
 }
 
+// "A direct" (experiment, la_gemm_tc_set_a_direct): the tensor cores take a tf32 operand from the upper 19 bits of an f32 word, so
+// the hi plane of a K-major operand can be the operand itself -- no hi plane is written -- provided lo is taken against the
+// TRUNCATED value: hi = x with its low 13 mantissa bits cleared, lo = x - hi (exact, 0 <= lo/x < 2^-10).
+__device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+__device__ __forceinline__ bool out_of_split_range(float x) {
+    const float ax = fabsf(x);
+    return !(ax <= 1.2676506e30f) || (ax < 7.8886091e-31f && ax != 0.0f);      // outside [2^-100, 2^100] (or NaN)
+}
+
 // Cross-term planes of the tf32 + 2 x bf16 engine: bf16(hi) and bf16(x - hi), four values = 8 bytes each.
 __device__ __forceinline__ uint2 pack_bf16x4(float a, float b, float c, float d) {
     const __nv_bfloat162 p0 = __floats2bfloat162_rn(a, b), p1 = __floats2bfloat162_rn(c, d);
@@ -655,7 +664,7 @@ __device__ __forceinline__ uint2 pack_bf16x4(float a, float b, float c, float d)
 // BF16X: the `lo` plane (4 bytes per element) holds two bf16 planes instead, [bf16(hi) | bf16(x - hi)], n elements each.
 template <bool BF16X>
 __global__ void __launch_bounds__(256)
-split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4, unsigned* flag) {
+split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ x, size_t n4, unsigned* flag, int direct) {
     const size_t stride = (size_t)gridDim.x * 256;
     bool bad = false;
     uint2* hb = reinterpret_cast<uint2*>(lo);
@@ -663,8 +672,13 @@ split_tf32_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* _
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += stride) {
         const float4 v = __ldcs(reinterpret_cast<const float4*>(x) + i);
         float4 h, l;
-        split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
-        __stcs(reinterpret_cast<float4*>(hi) + i, h);
+        if (BF16X && direct) {
+            h = make_float4(trunc_tf32(v.x), trunc_tf32(v.y), trunc_tf32(v.z), trunc_tf32(v.w));
+            bad |= out_of_split_range(v.x) | out_of_split_range(v.y) | out_of_split_range(v.z) | out_of_split_range(v.w);
+        } else {
+            split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
+            __stcs(reinterpret_cast<float4*>(hi) + i, h);
+        }
         if constexpr (BF16X) {
             __stcs(hb + i, pack_bf16x4(h.x, h.y, h.z, h.w));
             __stcs(lb + i, pack_bf16x4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
@@ -726,7 +740,7 @@ template <bool BF16X>
 __global__ void __launch_bounds__(256)
 split_both_kernel(float* __restrict__ a_hi, float* __restrict__ a_lo, const float* __restrict__ A, size_t a_n4,
                   float* __restrict__ bt_hi, float* __restrict__ bt_lo, const float* __restrict__ B, size_t K, size_t N, unsigned tiles_n, unsigned b_tiles,
-                  unsigned* flag) {
+                  unsigned* flag, int direct) {
     __shared__ float tile[64][65];
     bool bad = false;
     if (blockIdx.x < b_tiles) {
@@ -769,8 +783,13 @@ split_both_kernel(float* __restrict__ a_hi, float* __restrict__ a_lo, const floa
         for (size_t i = (size_t)(blockIdx.x - b_tiles) * 256 + threadIdx.x; i < a_n4; i += stride) {
             const float4 v = __ldcs(reinterpret_cast<const float4*>(A) + i);
             float4 h, l;
-            split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
-            __stcs(reinterpret_cast<float4*>(a_hi) + i, h);
+            if (BF16X && direct) {
+                h = make_float4(trunc_tf32(v.x), trunc_tf32(v.y), trunc_tf32(v.z), trunc_tf32(v.w));
+                bad |= out_of_split_range(v.x) | out_of_split_range(v.y) | out_of_split_range(v.z) | out_of_split_range(v.w);
+            } else {
+                split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
+                __stcs(reinterpret_cast<float4*>(a_hi) + i, h);
+            }
             if constexpr (BF16X) {
                 __stcs(hb + i, pack_bf16x4(h.x, h.y, h.z, h.w));
                 __stcs(lb + i, pack_bf16x4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
@@ -957,6 +976,9 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
 // tf32 MMAs.
 int g_tc_variant = 0;
 int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross terms, 1 bf16 cross terms whenever K % 8 == 0
+int g_tc_adirect = 0;           // la_gemm_tc_set_a_direct: A's hi plane is A itself (tensor cores truncate), see trunc_tf32
+bool la_tc_cross_bf16(size_t K);
+bool tc_a_direct(size_t K) { return g_tc_adirect != 0 && g_tc_variant == 0 && la_tc_cross_bf16(K); }
 bool la_tc_cross_bf16(size_t K) {
     if (K % 8 != 0 || g_tc_cross == 0 || g_tc_variant != 0) return false;
     return g_tc_cross > 0 || K >= 1024;
@@ -996,6 +1018,8 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
 
 }  // namespace
 
+bool la_tc_a_direct(size_t K) { return tc_a_direct(K); }      // also asked by gemm_host.cu
+
 extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA_OK; }     // tuning hook
 // Tile order of the tensor engines.  In m-major order one wave of 74 CTA pairs spans every tile row, so each wave streams
 // all of A's planes from HBM: 8.75 GB of DRAM reads for the 1 GB of operand planes at 8192^3 (ncu), 3.5 TB/s demanded at
@@ -1022,6 +1046,7 @@ extern "C" la_status la_gemm_kernel_time_ms(float* total_ms, int* launches) {
 }
 extern "C" la_status la_gemm_tc_set_persistent(int on) { g_tc_persist = on; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_tc_set_chunk(int kb) { g_tc_chunk = kb; return LA_OK; }       // tuning hook
+extern "C" la_status la_gemm_tc_set_a_direct(int on) { g_tc_adirect = on; return LA_OK; }   // tuning hook (experiment): A read in place as its own hi plane
 extern "C" la_status la_gemm_tc_set_cross(int mode) { g_tc_cross = mode; return LA_OK; }   // tuning hook: -1 by K, 0 tf32 cross terms, 1 bf16
 extern "C" la_status la_gemm_tc_set_tile_n(int bn) { g_tc_bn = (bn == 224 || bn == 192 || bn == 256) ? bn : 0; return LA_OK; }   // tuning hook
 extern "C" la_status la_gemm_set_stream_tail(int mode) { g_tc_stream = mode; return LA_OK; }   // tuning hook: -1 auto, 0 off, 1 on
@@ -1030,8 +1055,8 @@ extern "C" la_status la_gemm_set_raster(int group) { g_raster_group = group; ret
 // Pieces shared by la_gemm_3xtf32 and the host-streaming GEMM (gemm_host.cu).
 la_status la_tc_split_a(float* a_hi, float* a_lo, const float* A, size_t M, size_t K, unsigned* flag, cudaStream_t st) {
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
-    if (la_tc_cross_bf16(K)) split_tf32_kernel<true><<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag);
-    else                     split_tf32_kernel<false><<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag);
+    if (la_tc_cross_bf16(K)) split_tf32_kernel<true><<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag, la_tc_a_direct(K) ? 1 : 0);
+    else                     split_tf32_kernel<false><<<(unsigned)info->sm_count * 8, 256, 0, st>>>(a_hi, a_lo, A, M * K / 4, flag, 0);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
@@ -1052,8 +1077,8 @@ la_status la_tc_split_both(float* a_hi, float* a_lo, const float* A, size_t M, f
     if (a_blocks > (size_t)info->sm_count * 8) a_blocks = (size_t)info->sm_count * 8;
     if (tk * tn + a_blocks > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "3xTF32 pre-pass: B is too large");
     const unsigned grid = (unsigned)(tk * tn + a_blocks);
-    if (la_tc_cross_bf16(K)) split_both_kernel<true><<<grid, 256, 0, st>>>(a_hi, a_lo, A, a_n4, bt_hi, bt_lo, B, K, N, (unsigned)tn, (unsigned)(tk * tn), flag);
-    else                     split_both_kernel<false><<<grid, 256, 0, st>>>(a_hi, a_lo, A, a_n4, bt_hi, bt_lo, B, K, N, (unsigned)tn, (unsigned)(tk * tn), flag);
+    if (la_tc_cross_bf16(K)) split_both_kernel<true><<<grid, 256, 0, st>>>(a_hi, a_lo, A, a_n4, bt_hi, bt_lo, B, K, N, (unsigned)tn, (unsigned)(tk * tn), flag, la_tc_a_direct(K) ? 1 : 0);
+    else                     split_both_kernel<false><<<grid, 256, 0, st>>>(a_hi, a_lo, A, a_n4, bt_hi, bt_lo, B, K, N, (unsigned)tn, (unsigned)(tk * tn), flag, 0);
     LA_LAUNCH_CHECK();
     return LA_OK;
 }
@@ -1109,7 +1134,7 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
     // exponents -- the caller runs the plain f32 engine next in the stream, which overwrites whatever this launch left in C.
     cudaEvent_t split_done; LA_TRY(la_stream_event(st, &split_done));
     LA_CUDA(cudaEventRecord(split_done, st));
-    LA_TRY(la_tc_run(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st));
+    LA_TRY(la_tc_run(C, la_tc_a_direct(K) ? A : a_hi, a_lo, b_hi, b_lo, M, K, N, st));
     LA_CUDA(cudaEventSynchronize(split_done));
     if (*flag_host) return LA_OK;
     *handled = true;

@@ -9,6 +9,7 @@ import linear_algebra_b200 as la
 la.init(0); lib = la._lib.lib
 P = oracle.port()
 if os.environ.get("LA_CHUNK"): lib.la_gemm_tc_set_chunk(int(os.environ["LA_CHUNK"]))
+if os.environ.get("LA_ADIRECT"): lib.la_gemm_tc_set_a_direct(int(os.environ["LA_ADIRECT"]))
 if os.environ.get("LA_CROSS"): lib.la_gemm_tc_set_cross(int(os.environ["LA_CROSS"]))
 Ks = [int(x) for x in sys.argv[1:]] or [64, 96, 128, 160, 192, 224, 256, 320, 384, 512, 1024]
 M = N = int(os.environ.get("LA_MN", "4096"))

@@ -29,8 +29,6 @@ int la_gemm_last_padded(void);
 la_status la_gemm_tc_set_variant(int variant);     /* 0 CTA pairs (default); 5 / 3 one CTA per tile with / without B multicast; 1 / 2 single accumulation chain (drifts: reference only) */
 la_status la_gemm_tc_set_persistent(int on);       /* persistent grid of sm_count / 2 CTA pairs; bit-identical results */
 la_status la_gemm_tc_set_chunk(int k_blocks);      /* k-blocks of 32 per accumulation chain inside the tensor cores; 0 = by K */
-la_status la_gemm_tc_set_pipeline(int mode);       /* pre-pass on a helper stream BESIDE the product, which waits per k segment for the strips it loads: -1 by K (default), 0 never, 1 always; bit-identical results */
-la_status la_gemm_tc_last_stall(void* stream, unsigned* out7); /* diagnostic: the note a bounded wait of the pipelined form left in the stream's mapped host words before it trapped (word 1 = 0: none) */
 la_status la_gemm_tc_set_a_direct(int on);         /* EXPERIMENT: A is read in place as its own hi plane (hardware truncation to tf32), lo taken against the truncated value */
 la_status la_gemm_tc_set_cross(int mode);          /* cross terms: -1 by K, 0 tf32, 1 bf16 (below K = 1024 gated at twice the reference order's error) */
 la_status la_gemm_tc_set_tile_n(int bn);           /* pair tile width 256 / 224 / 192; 0 = by wave count; bit-identical results with the K-split off */

@@ -51,8 +51,6 @@ constexpr size_t LA_TC_AUTO_MIN_K = LA_GEMM_AUTO_MIN_K;      // include/linalg_b
 la_status la_host_flag(cudaStream_t stream, volatile unsigned** host_ptr, unsigned** dev_ptr);
 // One event (no timing) per (device, stream), for waiting on a point inside a chain of launches.
 la_status la_stream_event(cudaStream_t stream, cudaEvent_t* event);
-// helper stream beside `stream` (non-blocking) with its fork / join events (runtime.cu)
-la_status la_side_stream(cudaStream_t stream, cudaStream_t* side, cudaEvent_t* fork, cudaEvent_t* join);
 
 // What la_gemm_prepare_b keeps about a B that many products will share (include/linalg_b200.h): the caller's B itself (the SIMT
 // and generic engines read it as it is) and, where the tensor engines apply, their pre-processed forms of it.  The planes

@@ -410,52 +410,6 @@ __device__ __forceinline__ bool tc_segment(const TcPlan& p, int item, int seg, i
     return c_begin < c_end;
 }
 
-// The pre-pass BESIDE the product ("pipelined" form, la_gemm_3xtf32): the split planes are written by split_pipe_kernel on a
-// helper stream while this kernel already runs, and the TMA producer of a CTA waits, per k segment, until the strips it is
-// about to load are complete.  Counters (zeroed before both launches):
-//   ready_a[block * segs + s]  += 1 per finished 16-row strip of A's 128-row block `block`, columns of segment s   (8 = done)
-//   ready_b[group * segs + s]  += 1 per finished 64 x 64 tile of B's 64-column group `group`, k range of segment s (seg_tiles = done)
-// A null pointer means that operand's planes were complete before the launch (a prepared B).
-struct TcPipe {
-    const unsigned* ready_a;
-    const unsigned* ready_b;
-    int segs, seg_tiles;          // k segments; 64-k tiles per segment (the last segment is padded with no-op tiles)
-    int a_blocks, b_groups;       // 128-row blocks of A, 64-column groups of B
-    unsigned* note;               // mapped host words for pipe_stall_note (may be null)
-};
-constexpr int TC_PIPE_A_STRIPS = 32;       // 4-row strips per 128-row block of A (16 KB of input each at 1024 columns per segment)
-
-// A wait that ran into its bound leaves a note in the stream's mapped host words before it traps (read back by la_gemm_tc_last_stall):
-// [1] = tag, [2] = block, [3] / [4] = two values of the waiter's choice, [5] = value seen, [6] = value wanted.
-__device__ __noinline__ void pipe_stall_note(unsigned* note, unsigned tag, unsigned a, unsigned b, unsigned seen, unsigned want) {
-    if (note) {
-        volatile unsigned* n = note;
-        n[2] = blockIdx.x; n[3] = a; n[4] = b; n[5] = seen; n[6] = want; n[1] = tag;
-        __threadfence_system();
-    }
-    __trap();
-}
-__device__ __forceinline__ void pipe_wait(const unsigned* counter, unsigned want, unsigned* note, unsigned tag, unsigned a, unsigned b) {      // bounded: traps instead of hanging
-    for (uint32_t spin = 0;; ++spin) {
-        unsigned v;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-        if (v >= want) return;
-        __nanosleep(100);
-        if (spin > (1u << 22)) pipe_stall_note(note, tag, a, b, v, want);
-    }
-}
-__device__ __forceinline__ void mbar_wait_noted(uint64_t* bar, uint32_t parity, unsigned* note, unsigned tag, unsigned a) {
-    uint32_t done = 0;
-    for (uint32_t spin = 0; !done; ++spin) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-        if (!done && spin > (1u << 22)) pipe_stall_note(note, tag, a, spin, 0u, parity);
-    }
-}
-
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {       // kind::f16: D = f32, A = B = bf16, both K-major
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
@@ -469,15 +423,12 @@ __device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t a_desc, 
 // BN: columns of the pair's tile (a multiple of 32 up to 256): 256 unless another width packs the waves better (tc_launch_2cta)
 // BF16X: the two cross terms hi*lo and lo*hi as bf16 MMAs (twice the tf32 rate) on bf16(hi), bf16(x - hi) planes: the
 // `lo` maps then describe the bf16(hi) planes and the `x` maps the bf16(x - hi) planes; 64-byte rows, SWIZZLE_64B.
-// PIPE: the pipelined form above -- producer waits on `pipe`, and the kernel is built for 144 registers per thread at launch
-// (epilogue warps 192 after setmaxnreg instead of 232: they drain 32 accumulator columns per tensor-memory load instead of
-// 64), which leaves 10 240 registers and 35 KB of shared memory per SM: room for one 256-thread block of the pre-pass
-// beside each CTA.  Same instruction order per output element, so both forms give the same bits.
-template <int BN, bool BF16X, bool PIPE>
-__device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, const CUtensorMap* map_a_hi, const CUtensorMap* map_a_lo,
-                                                      const CUtensorMap* map_b_hi, const CUtensorMap* map_b_lo,
-                                                      const CUtensorMap* map_a_x, const CUtensorMap* map_b_x,
-                                                      int M, int N, const TcPlan& plan, const TcPipe& pipe) {
+template <int BN, bool BF16X>
+__global__ void __launch_bounds__(TC3_THREADS, 1)
+gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
+                        const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
+                        const __grid_constant__ CUtensorMap map_a_x, const __grid_constant__ CUtensorMap map_b_x,
+                        int M, int N, const TcPlan plan) {
     constexpr int STAGES = TC3_STAGES;
     constexpr int HC = BN / 2;                                   // B rows held by each CTA = accumulator columns drained by each epilogue half
     static_assert(BN % 32 == 0 && BN >= 64 && BN <= 256, "pair tile width");
@@ -525,31 +476,16 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
                     la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
                     const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * BN;
                     const int kb_end = min(ce * plan.chunk_kb, num_kb);
-                    int seg_ready = -1;                               // PIPE: k segment whose strips are known to be complete
                     for (int kb = cb * plan.chunk_kb; kb < kb_end; ++kb, ++it) {
-                        if constexpr (PIPE) {
-                            const int seg = kb / (2 * pipe.seg_tiles);              // 64-k tiles -> k-blocks of 32
-                            if (seg != seg_ready) {
-                                const int blk = tile_m * 2 + (int)crank;
-                                if (pipe.ready_a && blk < pipe.a_blocks) pipe_wait(pipe.ready_a + (size_t)blk * pipe.segs + seg, TC_PIPE_A_STRIPS, pipe.note, 1u, (unsigned)blk, (unsigned)seg);
-                                if (pipe.ready_b) {
-                                    const int c0 = n0 + (int)crank * HC;
-                                    const int g_end = min((c0 + HC + 63) / 64, pipe.b_groups);
-                                    for (int g = c0 / 64; g < g_end; ++g) pipe_wait(pipe.ready_b + (size_t)g * pipe.segs + seg, (unsigned)pipe.seg_tiles, pipe.note, 2u, (unsigned)g, (unsigned)seg);
-                                }
-                                asm volatile("fence.proxy.async.global;" ::: "memory");      // generic-proxy writes of the pre-pass -> TMA reads
-                                seg_ready = seg;
-                            }
-                        }
                         const int s = it % STAGES;
                         const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
-                        if constexpr (PIPE) mbar_wait_noted(&empty_bar[s], ph ^ 1u, pipe.note, 3u, (unsigned)it); else mbar_wait(&empty_bar[s], ph ^ 1u);
+                        mbar_wait(&empty_bar[s], ph ^ 1u);
                         uint8_t* st = ring_ptr + (size_t)s * TC3_STAGE_BYTES;
                         if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * (2u * TC3_TILE + 2u * HC * TC_BK * 4u));     // my slabs + the peer's
-                        tma_load_2d_2sm(st, map_a_hi, &full_bar[s], kb * TC_BK, m0);
-                        tma_load_2d_2sm(st + TC3_TILE, map_a_lo, &full_bar[s], kb * TC_BK, m0);
-                        tma_load_2d_2sm(st + 2 * TC3_TILE, map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
-                        tma_load_2d_2sm(st + 3 * TC3_TILE, map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                        tma_load_2d_2sm(st, &map_a_hi, &full_bar[s], kb * TC_BK, m0);
+                        tma_load_2d_2sm(st + TC3_TILE, &map_a_lo, &full_bar[s], kb * TC_BK, m0);
+                        tma_load_2d_2sm(st + 2 * TC3_TILE, &map_b_hi, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                        tma_load_2d_2sm(st + 3 * TC3_TILE, &map_b_lo, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
                         // (With bf16 cross terms the kernel runs at 90 % of its tensor-time floor (8192^3: 2.96 ms against
                         //  2.67) while pulling 34.4 GB per launch through L2 -> SM = 11.6 TB/s, close to what the L2 slices
                         //  deliver chip-wide.  Experiments: a 2-stage ring costs 22 %; prefetching boxes into L2 ahead of the
@@ -557,8 +493,8 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
                         //  bound of what multicasting A across a 4-CTA cluster could save -- gains only 3 %.  So the operand
                         //  path is near its limit but not the binding one; what is left is per-tile ramp-up and drain.)
                         if constexpr (BF16X) {      // the second bf16 plane of each operand, in the upper half of its 16 KB slot
-                            tma_load_2d_2sm(st + TC3_TILE + TC3_TILE / 2, map_a_x, &full_bar[s], kb * TC_BK, m0);
-                            tma_load_2d_2sm(st + 3 * TC3_TILE + TC3_TILE / 2, map_b_x, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
+                            tma_load_2d_2sm(st + TC3_TILE + TC3_TILE / 2, &map_a_x, &full_bar[s], kb * TC_BK, m0);
+                            tma_load_2d_2sm(st + 3 * TC3_TILE + TC3_TILE / 2, &map_b_x, &full_bar[s], kb * TC_BK, n0 + (int)crank * HC);
                         }
                     }
                 }
@@ -572,7 +508,7 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
             for (int c = cb; c < ce; ++c, ++cc) {
                 const int b = cc & 1;
                 const uint32_t use = (uint32_t)(cc >> 1);
-                if constexpr (PIPE) mbar_wait_noted(&acc_empty_bar[b], (use & 1u) ^ 1u, pipe.note, 4u, (unsigned)cc); else mbar_wait(&acc_empty_bar[b], (use & 1u) ^ 1u);
+                mbar_wait(&acc_empty_bar[b], (use & 1u) ^ 1u);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t tmem_d = tmem_base + (uint32_t)(b * 256);
                 int kb = c * plan.chunk_kb;
@@ -580,7 +516,7 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
                 for (int first = 1; kb < kb_end; ++kb, ++it) {
                     const int s = it % STAGES;
                     const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
-                    if constexpr (PIPE) mbar_wait_noted(&full_bar[s], ph, pipe.note, 5u, (unsigned)it); else mbar_wait(&full_bar[s], ph);
+                    mbar_wait(&full_bar[s], ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     if (elect_one()) {
                         const uint32_t st = ring + (uint32_t)s * TC3_STAGE_BYTES;
@@ -620,8 +556,7 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
         }
     } else {
         // ---------------- epilogue warps 0..7 (both CTAs; each drains its own tensor memory)
-        if constexpr (PIPE) asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");
-        else                asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
         const int quad = warp & 3, half = warp >> 2;
         float acc[HC];
         int cc = 0;
@@ -632,19 +567,9 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
         for (int c = cb; c < ce; ++c, ++cc) {
             const int b = cc & 1;
             const uint32_t use = (uint32_t)(cc >> 1);
-            if constexpr (PIPE) mbar_wait_noted(&acc_full_bar[b], use & 1u, pipe.note, 6u, (unsigned)cc); else mbar_wait(&acc_full_bar[b], use & 1u);
+            mbar_wait(&acc_full_bar[b], use & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * 256 + half * HC);
-            if constexpr (PIPE) {
-#pragma unroll
-                for (int j = 0; j < HC / 32; ++j) {
-                    uint32_t v0[32];
-                    tmem_ld32(taddr + j * 32, v0);
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) acc[j * 32 + i] += __uint_as_float(v0[i]);
-                }
-            } else {
 #pragma unroll
             for (int j = 0; j < HC / 64; ++j) {
                 uint32_t v0[32], v1[32];
@@ -664,7 +589,6 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc[o + i] += __uint_as_float(v0[i]);
-            }
             }
             if constexpr (HC % 32 == 16) {
                 constexpr int o = HC / 32 * 32;
@@ -705,24 +629,6 @@ __device__ __forceinline__ void gemm_3xtf32_2cta_body(float* __restrict__ C, con
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
     }
-}
-
-template <int BN, bool BF16X>
-__global__ void __launch_bounds__(TC3_THREADS, 1)
-gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
-                        const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
-                        const __grid_constant__ CUtensorMap map_a_x, const __grid_constant__ CUtensorMap map_b_x,
-                        int M, int N, const TcPlan plan) {
-    gemm_3xtf32_2cta_body<BN, BF16X, false>(C, &map_a_hi, &map_a_lo, &map_b_hi, &map_b_lo, &map_a_x, &map_b_x, M, N, plan, TcPipe{});
-}
-constexpr int TC3_PIPE_REGS = 144;         // per thread at launch: 384 x 144 = 55 296 of the SM's 65 536
-template <int BN, bool BF16X>
-__global__ void __maxnreg__(TC3_PIPE_REGS)
-gemm_3xtf32_2cta_pipe_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_lo,
-                             const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo,
-                             const __grid_constant__ CUtensorMap map_a_x, const __grid_constant__ CUtensorMap map_b_x,
-                             int M, int N, const TcPlan plan, const TcPipe pipe) {
-    gemm_3xtf32_2cta_body<BN, BF16X, true>(C, &map_a_hi, &map_a_lo, &map_b_hi, &map_b_lo, &map_a_x, &map_b_x, M, N, plan, pipe);
 }
 
 // ------------------------------------------------------------------ pre-pass
@@ -895,167 +801,6 @@ split_both_kernel(float* __restrict__ a_hi, float* __restrict__ a_lo, const floa
     if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;
 }
 
-// The pre-pass in its pipelined form: ONE resident block per SM (so that a CTA of gemm_3xtf32_2cta_pipe_kernel fits beside it),
-// looping over work items in the order the product needs them, and counting every finished item on its TcPipe counter:
-//   A item (block, s, strip): rows 128 block + 4 strip .. +4, columns of k segment s (at most 1024) -> ready_a[block * segs + s]
-//   B item (group, s, kt)   : the 64 x 64 tile at k tile s * seg_tiles + kt, columns 64 group .. -> ready_b[group * segs + s]
-// Each item is 16 KB of input.  With one block per SM the usual cover for memory latency -- many blocks -- is gone, so the
-// input of item i+1 is fetched with cp.async into the second of two shared-memory stages while item i is split and stored:
-// no registers are held by loads in flight (the block has 40 per thread).
-// Order: [for every segment s: the A blocks of the first band, then the B groups of the first wave] (the first wave of tiles can
-// start on segment 0 while segment 1 is being split), then the remaining B groups one wave's span at a time, then the
-// remaining A blocks.  The planes are bit for bit what split_tf32_kernel and split_transpose_kernel write.
-struct TcPipeWork {
-    const float* A; float* a_hi; float* a_lo; int M;
-    const float* B; float* bt_hi; float* bt_lo;       // B == nullptr: only A is split (B prepared earlier)
-    size_t K, N;
-    unsigned* ready_a; unsigned* ready_b;
-    int segs, seg_tiles, tiles_k;
-    int a_blocks, b_groups;
-    int a_first, span;                                // A blocks of the first band; B groups per wave
-    unsigned* flag;
-};
-
-struct TcPipeItem { int kind, a, b, seg; };           // kind 0: A (a = block, b = strip); 1: B (a = group, b = k tile in the segment); 2: nothing
-
-__device__ __forceinline__ TcPipeItem pipe_item(const TcPipeWork& w, long long item, int g0, long long p1_a, long long p1_b, long long p1, long long per_span, long long p2) {
-    TcPipeItem it;
-    const int S = w.segs, ST = w.seg_tiles;
-    if (item < p1) {
-        it.seg = (int)(item / (p1_a + p1_b));
-        const long long r = item % (p1_a + p1_b);
-        if (r < p1_a) { it.kind = 0; it.a = (int)(r / TC_PIPE_A_STRIPS); it.b = (int)(r % TC_PIPE_A_STRIPS); }
-        else          { it.kind = 1; it.b = (int)((r - p1_a) / g0); it.a = (int)((r - p1_a) % g0); }
-    } else if (item < p1 + p2) {
-        const long long i = item - p1;
-        const int j = (int)(i / per_span);
-        const long long r = i % per_span;
-        it.seg = (int)(r / ((long long)w.span * ST));
-        const int r2 = (int)(r % ((long long)w.span * ST));
-        it.kind = 1; it.b = r2 / w.span; it.a = g0 + j * w.span + r2 % w.span;
-        if (it.a >= w.b_groups) it.kind = 2;
-    } else {
-        const long long i = item - p1 - p2;
-        it.kind = 0; it.a = w.a_first + (int)(i / (S * TC_PIPE_A_STRIPS)); it.seg = (int)((i / TC_PIPE_A_STRIPS) % S); it.b = (int)(i % TC_PIPE_A_STRIPS);
-    }
-    return it;
-}
-
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* src, bool valid) {      // 16 bytes, zero-filled when !valid
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(src), "r"(valid ? 16 : 0) : "memory");
-}
-
-// Stage layout.  A item: float4 j * 256 + tid = row j of the strip, columns 4 tid ...  B item: row r (k) of 64 floats, its 16-byte
-// chunk q stored at chunk q ^ ((r >> 2) & 15), so that the transposed reads (16 different k groups per warp) spread over the banks.
-__device__ __forceinline__ void pipe_fetch(const TcPipeWork& w, const TcPipeItem& it, float* stage, int tid) {
-    if (it.kind == 0) {
-        const size_t c0 = (size_t)it.seg * w.seg_tiles * 64;
-        const int cols4 = c0 < w.K ? (int)((min(w.K, c0 + (size_t)w.seg_tiles * 64) - c0) / 4) : 0;
-        const int row0 = it.a * 128 + it.b * 4;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const bool ok = tid < cols4 && row0 + j < w.M;
-            cp_async16(stage + (j * 256 + tid) * 4, ok ? (const void*)(w.A + (size_t)(row0 + j) * w.K + c0 + 4 * tid) : (const void*)w.A, ok);
-        }
-    } else if (it.kind == 1) {
-        const size_t k0 = ((size_t)it.seg * w.seg_tiles + it.b) * 64, n0 = (size_t)it.a * 64;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int idx = tid + j * 256, r = idx / 16, q = idx % 16;
-            const bool ok = k0 + r < w.K && n0 + q * 4 < w.N;
-            cp_async16(stage + r * 64 + ((q ^ ((r >> 2) & 15)) << 2), ok ? (const void*)(w.B + (k0 + r) * w.N + n0 + q * 4) : (const void*)w.B, ok);
-        }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-}
-
-template <bool BF16X>
-__global__ void __maxnreg__(40)
-split_pipe_kernel(const TcPipeWork w) {
-    __shared__ __align__(16) float stage[2][64 * 64];
-    const int tid = threadIdx.x;
-    bool bad = false;
-    const int S = w.segs, ST = w.seg_tiles;
-    const int g0 = w.B ? min(w.span, w.b_groups) : 0;                                   // groups of the first wave
-    const long long p1_a = (long long)w.a_first * TC_PIPE_A_STRIPS, p1_b = (long long)g0 * ST;
-    const long long p1 = (p1_a + p1_b) * S;
-    const int spans = (w.B && w.b_groups > g0) ? (w.b_groups - g0 + w.span - 1) / w.span : 0;
-    const long long per_span = (long long)w.span * ST * S;
-    const long long p2 = (long long)spans * per_span;
-    const long long total = p1 + p2 + (long long)(w.a_blocks - w.a_first) * S * TC_PIPE_A_STRIPS;
-    long long item = blockIdx.x;
-    if (item < total) pipe_fetch(w, pipe_item(w, item, g0, p1_a, p1_b, p1, per_span, p2), stage[0], tid);
-    for (int buf = 0; item < total; item += gridDim.x, buf ^= 1) {
-        const TcPipeItem it = pipe_item(w, item, g0, p1_a, p1_b, p1, per_span, p2);
-        if (item + gridDim.x < total) pipe_fetch(w, pipe_item(w, item + gridDim.x, g0, p1_a, p1_b, p1, per_span, p2), stage[buf ^ 1], tid);
-        else asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group 1;" ::: "memory");      // this item's stage has landed (for this thread's copies)
-        __syncthreads();                                           // ... and for everybody's
-        const float* st = stage[buf];
-        unsigned* counter = nullptr;
-        if (it.kind == 0) {
-            counter = w.ready_a + (size_t)it.a * S + it.seg;
-            const size_t c0 = (size_t)it.seg * ST * 64;
-            const int cols4 = c0 < w.K ? (int)((min(w.K, c0 + (size_t)ST * 64) - c0) / 4) : 0;
-            const int row0 = it.a * 128 + it.b * 4;
-            uint2* hb = reinterpret_cast<uint2*>(w.a_lo);
-            uint2* lb = hb + (size_t)w.M * w.K / 4;
-            if (tid < cols4) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (row0 + j < w.M) {
-                        const float4 v = *reinterpret_cast<const float4*>(st + (j * 256 + tid) * 4);
-                        const size_t at4 = ((size_t)(row0 + j) * w.K + c0) / 4 + tid;
-                        float4 h, l;
-                        split_one(v.x, h.x, l.x, bad); split_one(v.y, h.y, l.y, bad); split_one(v.z, h.z, l.z, bad); split_one(v.w, h.w, l.w, bad);
-                        __stcs(reinterpret_cast<float4*>(w.a_hi) + at4, h);
-                        if constexpr (BF16X) {
-                            __stcs(hb + at4, pack_bf16x4(h.x, h.y, h.z, h.w));
-                            __stcs(lb + at4, pack_bf16x4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w));
-                        } else {
-                            __stcs(reinterpret_cast<float4*>(w.a_lo) + at4, l);
-                        }
-                    }
-                }
-            }
-        } else if (it.kind == 1) {
-            counter = w.ready_b + (size_t)it.a * S + it.seg;
-            const size_t K = w.K, N = w.N;
-            const size_t k0 = ((size_t)it.seg * ST + it.b) * 64, n0 = (size_t)it.a * 64;
-            if (k0 < K) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int idx = tid + j * 256, cc = idx / 16, q = idx % 16;      // Bt row n0 + cc, columns k0 + 4 q ...: rows 4q .. 4q+3 of the stage, column cc
-                    const float* col = st + (q * 4) * 64 + ((((cc >> 2) ^ q) & 15) << 2) + (cc & 3);
-                    const float x0 = col[0], x1 = col[64], x2 = col[128], x3 = col[192];
-                    float4 h, l;
-                    split_one(x0, h.x, l.x, bad); split_one(x1, h.y, l.y, bad); split_one(x2, h.z, l.z, bad); split_one(x3, h.w, l.w, bad);
-                    if (n0 + cc < N && k0 + q * 4 < K) {
-                        const size_t at = (n0 + cc) * K + k0 + q * 4;
-                        __stcs(reinterpret_cast<float4*>(w.bt_hi + at), h);
-                        if constexpr (BF16X) {
-                            uint2* hb = reinterpret_cast<uint2*>(w.bt_lo);
-                            __stcs(hb + at / 4, pack_bf16x4(h.x, h.y, h.z, h.w));
-                            __stcs(hb + (N * K + at) / 4, pack_bf16x4(x0 - h.x, x1 - h.y, x2 - h.z, x3 - h.w));
-                        } else {
-                            __stcs(reinterpret_cast<float4*>(w.bt_lo + at), l);
-                        }
-                    }
-                }
-            }
-        }
-        // publish: the stores of all threads, then one release by thread 0 (the consumer reads the planes with TMA: async proxy).
-        // The barrier also frees this stage for the fetch of the item after next.
-        __syncthreads();
-        if (tid == 0 && counter) {
-            asm volatile("fence.proxy.async.global;" ::: "memory");
-            __threadfence();
-            atomicAdd(counter, 1u);
-        }
-    }
-    if (__syncthreads_or(bad) && tid == 0) *(volatile unsigned*)w.flag = 1u;
-}
-
 // rows x K row-major f32, box = box_rows x 32 (128 bytes), 128-byte swizzle
 la_status tc_make_map(CUtensorMap* map, const float* base, size_t rows, size_t K, int box_rows) {
     EncodeTiledFn enc; LA_TRY(tc_get_encode(&enc));
@@ -1139,18 +884,8 @@ static double tc_cost(long long tiles, long long pairs, int bn, bool can_split) 
     return ((double)waves + last) * (double)bn / 256.0;
 }
 
-// What la_gemm_3xtf32 hands down for the pipelined form: the pre-pass' work description (completed here, where the tile order is
-// known), the helper stream it runs on and the event recorded behind it.
-struct TcPipeHost {
-    TcPipeWork work;
-    cudaStream_t side;
-    cudaEvent_t split_done;
-    bool no_prepass;            // measurement (la_gemm_tc_set_pipeline(2)): the planes are complete already, only the kernel built for the pipelined form runs
-};
-
 template <int BN, bool BF16X>
-la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs,
-                            TcPipeHost* ph = nullptr) {
+la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs) {
     CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x;
     LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN / 2));
     if (BF16X) {        // the lo planes hold [bf16(hi) | bf16(x - hi)]
@@ -1162,16 +897,7 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
         ma_x = ma_lo; mb_x = mb_lo;
     }
     auto kern = gemm_3xtf32_2cta_kernel<BN, BF16X>;
-    auto kern_pipe = gemm_3xtf32_2cta_pipe_kernel<BN, BF16X>;
-    if (ph) {
-        // both kernels of the pipelined form ask for the same (largest) shared-memory configuration of the SM: blocks of two
-        // kernels only share an SM when they agree on it
-        LA_CUDA(cudaFuncSetAttribute(kern_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
-        LA_CUDA(cudaFuncSetAttribute(kern_pipe, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-        LA_CUDA(cudaFuncSetAttribute(split_pipe_kernel<BF16X>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-    } else {
-        LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
-    }
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
     const size_t ptm = (M + 255) / 256, tn = (N + BN - 1) / BN;
     const long long tiles = (long long)(ptm * tn);
 
@@ -1221,10 +947,7 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     }
     long long items = plan.dp_items + plan.stream_items;
     plan.persist = 0;
-    // The pipelined form always runs a persistent grid: with every CTA of the product resident from the start, none is left
-    // pending ahead of the pre-pass' blocks in the hardware's block queue (pending CTAs of an earlier-launched grid are
-    // handed out first, and the resident ones would spin on a pre-pass that never gets an SM).
-    if ((g_tc_persist != 0 || (ph && !ph->no_prepass)) && items > pairs) { plan.persist = (int)pairs; items = pairs; }
+    if (g_tc_persist != 0 && items > pairs) { plan.persist = (int)pairs; items = pairs; }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(2 * items)); cfg.blockDim = dim3(TC3_THREADS); cfg.dynamicSmemBytes = TC3_SMEM_BYTES; cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -1236,27 +959,7 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
         if (!g_tc_ev_made) { for (auto& e : g_tc_ev) { LA_CUDA(cudaEventCreate(&e[0])); LA_CUDA(cudaEventCreate(&e[1])); } g_tc_ev_made = true; }
         LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][0], st));
     }
-    if (ph && ph->no_prepass) {
-        LA_CUDA(cudaLaunchKernelEx(&cfg, kern_pipe, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan, TcPipe{}));
-    } else if (ph) {
-        // the pre-pass first (host order = the order a serialising tool would run them in), on the helper stream
-        TcPipeWork& w = ph->work;
-        const long long rows_band = (plan.raster_group <= 0 || plan.raster_group >= plan.pair_tiles_m) ? plan.pair_tiles_m : plan.raster_group;
-        const long long first = tiles < pairs ? tiles : pairs;
-        const long long cols_w = (first + rows_band - 1) / rows_band;                       // tile columns the first wave touches
-        w.a_first = (int)std::min<long long>(w.a_blocks, 2 * rows_band);
-        w.span = (int)std::max<long long>(1, std::min<long long>(w.b_groups, (cols_w * BN + 63) / 64));
-        LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
-        split_pipe_kernel<BF16X><<<(unsigned)info->sm_count, 256, 0, ph->side>>>(w);
-        LA_LAUNCH_CHECK();
-        LA_CUDA(cudaEventRecord(ph->split_done, ph->side));
-        TcPipe pipe = {};
-        pipe.ready_a = w.ready_a; pipe.ready_b = w.B ? w.ready_b : nullptr;
-        pipe.segs = w.segs; pipe.seg_tiles = w.seg_tiles; pipe.a_blocks = w.a_blocks; pipe.b_groups = w.b_groups; pipe.note = w.flag;
-        LA_CUDA(cudaLaunchKernelEx(&cfg, kern_pipe, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan, pipe));
-    } else {
-        LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan));
-    }
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan));
     if (timed) { LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][1], st)); ++g_tc_timed; }
     return LA_OK;
 }
@@ -1272,7 +975,6 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
 // bf16 form sits at 0.8 - 0.9 of the reference order's error, at K = 512 at 0.6 - 0.85: too close to the unrelaxed gate); shorter products keep three
 // tf32 MMAs.
 int g_tc_variant = 0;
-int g_tc_pipe = -1;            // la_gemm_tc_set_pipeline
 int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross terms, 1 bf16 cross terms whenever K % 8 == 0
 int g_tc_adirect = 0;           // la_gemm_tc_set_a_direct: A's hi plane is A itself (tensor cores truncate), see trunc_tf32
 bool la_tc_cross_bf16(size_t K);
@@ -1285,7 +987,7 @@ bool la_tc_cross_bf16(size_t K) {
 // Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,
 // 1024 x 8192 x 8192, is 128 tiles = 1.73 waves -> 2 wave-times at width 256, but 148 tiles = exactly 2 waves of 0.875 at 224
 // (measured 0.666 -> 0.645 ms).
-la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, TcPipeHost* ph = nullptr) {
+la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     const long long pairs = info->sm_count / 2;                 // CTA pairs in flight (one per SM pair)
     const long long ptm = (long long)((M + 255) / 256);
@@ -1301,15 +1003,15 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
     }
     if (la_tc_cross_bf16(K)) {
         switch (bn) {
-        case 224: return tc_launch_2cta_bn<224, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs, ph);
-        case 192: return tc_launch_2cta_bn<192, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs, ph);
-        default:  return tc_launch_2cta_bn<256, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs, ph);
+        case 224: return tc_launch_2cta_bn<224, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+        case 192: return tc_launch_2cta_bn<192, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+        default:  return tc_launch_2cta_bn<256, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
         }
     }
     switch (bn) {
-    case 224: return tc_launch_2cta_bn<224, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs, ph);
-    case 192: return tc_launch_2cta_bn<192, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs, ph);
-    default:  return tc_launch_2cta_bn<256, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs, ph);
+    case 224: return tc_launch_2cta_bn<224, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    case 192: return tc_launch_2cta_bn<192, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
+    default:  return tc_launch_2cta_bn<256, false>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
     }
 }
 
@@ -1319,14 +1021,6 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
 bool la_tc_a_direct(size_t K) { return tc_a_direct(K); }      // also asked by gemm_host.cu
 
 extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA_OK; }     // tuning hook
-// Diagnostic: the note a bounded wait of the pipelined form left before it trapped (7 words; word 1 = 0: none), for `stream`.
-static volatile unsigned* g_tc_note_host = nullptr;     // host view of the words the last pipelined launch could leave its note in
-extern "C" la_status la_gemm_tc_last_stall(void* stream, unsigned* out7) {
-    (void)stream;                                       // no CUDA call here: after a trap the context only returns errors
-    for (int i = 0; i < 7; ++i) out7[i] = g_tc_note_host ? g_tc_note_host[i] : 0u;
-    return LA_OK;
-}
-extern "C" la_status la_gemm_tc_set_pipeline(int v) { g_tc_pipe = v; return LA_OK; }       // tuning hook: pre-pass beside the product (-1 auto, 0 off, 1 on)
 // Tile order of the tensor engines.  In m-major order one wave of 74 CTA pairs spans every tile row, so each wave streams
 // all of A's planes from HBM: 8.75 GB of DRAM reads for the 1 GB of operand planes at 8192^3 (ncu), 3.5 TB/s demanded at
 // M = 16384, where the kernel then waits on HBM (16384^3 f32 42.6 ms).  Bands of 8 tile rows keep a wave on ~17 row/column
@@ -1419,76 +1113,20 @@ bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_
              M >= (1u << 31) || N >= (1u << 31) || K >= (1u << 31));
 }
 
-// Pipelined pre-pass (la_gemm_tc_set_pipeline: -1 by the rule below, 0 never, 1 wherever the kernels exist).  The product kernel's
-// CTAs and the pre-pass' blocks must be able to share an SM -- the product's CTAs spin on what the pre-pass produces -- so the
-// form is only used when one CTA of each fits an SM together, checked once from the kernels' own attributes.
-static bool tc_pipe_fits() {
-    static int fits = -1;
-    static std::mutex mu;
-    std::lock_guard<std::mutex> lk(mu);
-    if (fits >= 0) return fits == 1;
-    fits = 0;
-    int dev = 0, regs_sm = 0, smem_sm = 0, smem_reserved = 0;
-    cudaFuncAttributes g = {}, p = {};
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&smem_reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev) != cudaSuccess ||
-        cudaFuncGetAttributes(&g, gemm_3xtf32_2cta_pipe_kernel<256, true>) != cudaSuccess ||
-        cudaFuncGetAttributes(&p, split_pipe_kernel<true>) != cudaSuccess) { (void)cudaGetLastError(); return false; }
-    const long long regs = (long long)((g.numRegs + 7) / 8 * 8) * TC3_THREADS + (long long)((p.numRegs + 7) / 8 * 8) * 256;
-    const long long smem = (long long)TC3_SMEM_BYTES + (long long)g.sharedSizeBytes + (long long)p.sharedSizeBytes + 2LL * smem_reserved;
-    if (regs <= regs_sm && smem <= smem_sm) fits = 1;
-    return fits == 1;
-}
-static bool tc_pipelined(size_t K) {
-    if (g_tc_pipe == 0 || g_tc_pipe == 2 || g_tc_variant != 0 || tc_a_direct(K)) return false;
-    if (g_tc_pipe < 0 && K < 1024) return false;          // short accumulation chains: the drain of 64 columns per load matters there
-    return tc_pipe_fits();
-}
-
 // `prep`: planes of B^T made earlier by la_tc_prepare_b (la_gemm_prepare_b), or NULL to split B here.
 la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep) {
     *handled = false;
     if (!la_tc_shape_ok(A, B, C, M, K, N)) return LA_OK;      // the SIMT engine takes it
     if (prep && (!prep->tc_hi || prep->tc_cross_bf16 != la_tc_cross_bf16(K))) prep = nullptr;     // no planes, or made under other tuning settings
     const size_t a_elems = M * K, b_elems = prep ? 0 : K * N;
-    const size_t pipe_segs = std::max<size_t>(8, (K + 1023) / 1024);
-    const size_t counter_bytes = (((M + 127) / 128 + (N + 63) / 64) * pipe_segs * sizeof(unsigned) + 255) / 256 * 256;     // TcPipe counters (pipelined form)
-    void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 2 * b_elems) * sizeof(float) + counter_bytes, &scratch));
+    void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 2 * b_elems) * sizeof(float), &scratch));
     volatile unsigned* flag_host; unsigned* flag;               // zero-copy flag word of this stream
     LA_TRY(la_host_flag(st, &flag_host, &flag));
     float* a_hi = (float*)((char*)scratch + LA_SCRATCH_ZEROED);
     float* a_lo = a_hi + a_elems;
     const float* b_hi = prep ? prep->tc_hi : a_lo + a_elems;    // B^T (N x K), split
     const float* b_lo = prep ? prep->tc_lo : b_hi + b_elems;
-    unsigned* counters = reinterpret_cast<unsigned*>(a_lo + a_elems + 2 * b_elems);
     *flag_host = 0u;                                            // no kernel of this stream that writes it is in flight (each call waits below)
-    if (tc_pipelined(K)) {
-        g_tc_note_host = flag_host; flag_host[1] = 0u;
-        // Pipelined form: the pre-pass runs on a helper stream BESIDE the product, which waits per k segment for the strips it loads.
-        TcPipeHost ph = {};
-        TcPipeWork& w = ph.work;
-        w.A = A; w.a_hi = a_hi; w.a_lo = a_lo; w.M = (int)M;
-        w.B = prep ? nullptr : B; w.bt_hi = const_cast<float*>(b_hi); w.bt_lo = const_cast<float*>(b_lo);
-        w.K = K; w.N = N; w.flag = flag;
-        w.tiles_k = (int)((K + 63) / 64);
-        w.seg_tiles = std::min(16, (w.tiles_k + 7) / 8);          // 8 k segments, more when K > 8192: an A item is 4 rows of at most 1024 columns
-        w.segs = (w.tiles_k + w.seg_tiles - 1) / w.seg_tiles;
-        w.a_blocks = (int)((M + 127) / 128); w.b_groups = (int)((N + 63) / 64);
-        w.ready_a = counters; w.ready_b = counters + (size_t)w.a_blocks * w.segs;
-        cudaEvent_t fork;
-        LA_TRY(la_side_stream(st, &ph.side, &fork, &ph.split_done));
-        LA_CUDA(cudaMemsetAsync(counters, 0, counter_bytes, st));
-        LA_CUDA(cudaEventRecord(fork, st));                     // the helper stream starts behind everything queued on `st` so far
-        LA_CUDA(cudaStreamWaitEvent(ph.side, fork, 0));
-        LA_TRY(tc_launch_2cta(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, &ph));
-        LA_CUDA(cudaStreamWaitEvent(st, ph.split_done, 0));     // join: whatever follows on `st` also follows the pre-pass
-        LA_CUDA(cudaEventSynchronize(ph.split_done));
-        if (*flag_host) return LA_OK;
-        *handled = true;
-        return LA_OK;
-    }
     if (prep) LA_TRY(la_tc_split_a(a_hi, a_lo, A, M, K, flag, st));
     else      LA_TRY(la_tc_split_both(a_hi, a_lo, A, M, const_cast<float*>(b_hi), const_cast<float*>(b_lo), B, K, N, flag, st));
     // Were all operands inside the range the split is faithful for?  The product is launched straight behind the pre-pass, so
@@ -1496,8 +1134,7 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
     // exponents -- the caller runs the plain f32 engine next in the stream, which overwrites whatever this launch left in C.
     cudaEvent_t split_done; LA_TRY(la_stream_event(st, &split_done));
     LA_CUDA(cudaEventRecord(split_done, st));
-    if (g_tc_pipe == 2 && g_tc_variant == 0) { TcPipeHost ph = {}; ph.no_prepass = true; LA_TRY(tc_launch_2cta(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, &ph)); }
-    else LA_TRY(la_tc_run(C, la_tc_a_direct(K) ? A : a_hi, a_lo, b_hi, b_lo, M, K, N, st));
+    LA_TRY(la_tc_run(C, la_tc_a_direct(K) ? A : a_hi, a_lo, b_hi, b_lo, M, K, N, st));
     LA_CUDA(cudaEventSynchronize(split_done));
     if (*flag_host) return LA_OK;
     *handled = true;

@@ -48,8 +48,6 @@ struct DeviceState {
     std::map<cudaStream_t, cudaEvent_t> events;                  // per stream: one timing-less event
     std::map<cudaStream_t, cudaEvent_t> user_streams;            // streams made by la_stream_create, each with the event la_malloc / la_free order it by
     cudaEvent_t legacy_event = nullptr;                          // recorded on the legacy stream by la_malloc
-    struct Side { cudaStream_t stream = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
-    std::map<cudaStream_t, Side> side;                           // per stream: a helper stream + the events that fork to / join from it
 };
 std::mutex g_mu;
 std::map<int, DeviceState*> g_devices;
@@ -138,26 +136,6 @@ la_status la_stream_event(cudaStream_t stream, cudaEvent_t* event) {
     cudaEvent_t& slot = st->events[stream];
     if (!slot) LA_CUDA(cudaEventCreateWithFlags(&slot, cudaEventDisableTiming));
     *event = slot;
-    return LA_OK;
-}
-
-// A helper stream for work that runs BESIDE a kernel of `stream` (the tensor engine's pre-pass next to the product that consumes
-// it): non-blocking, so the legacy stream's implicit ordering does not serialise the two; the caller forks with `fork`
-// (record on `stream`, wait on the helper) and joins with `join` (record on the helper, wait on `stream`).
-la_status la_side_stream(cudaStream_t stream, cudaStream_t* side, cudaEvent_t* fork, cudaEvent_t* join) {
-    DeviceState* st = nullptr;
-    LA_TRY(device_state(&st));
-    std::lock_guard<std::mutex> lk(g_mu);
-    DeviceState::Side& slot = st->side[stream];
-    if (!slot.stream) {
-        // highest priority: its blocks are handed out ahead of the pending blocks of whatever runs on `stream`
-        int least = 0, greatest = 0;
-        LA_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
-        LA_CUDA(cudaStreamCreateWithPriority(&slot.stream, cudaStreamNonBlocking, greatest));
-        LA_CUDA(cudaEventCreateWithFlags(&slot.fork, cudaEventDisableTiming));
-        LA_CUDA(cudaEventCreateWithFlags(&slot.join, cudaEventDisableTiming));
-    }
-    *side = slot.stream; *fork = slot.fork; *join = slot.join;
     return LA_OK;
 }
 
@@ -295,12 +273,6 @@ extern "C" la_status la_stream_destroy(void* stream) {
                 cudaStreamSynchronize((cudaStream_t)stream);
                 cudaFree(it->second.first);
                 st->scratch.erase(it);
-            }
-            auto sd = st->side.find((cudaStream_t)stream);
-            if (sd != st->side.end()) {
-                cudaStreamSynchronize(sd->second.stream);
-                cudaStreamDestroy(sd->second.stream); cudaEventDestroy(sd->second.fork); cudaEventDestroy(sd->second.join);
-                st->side.erase(sd);
             }
             auto us = st->user_streams.find((cudaStream_t)stream);
             if (us != st->user_streams.end()) {

@@ -16,17 +16,21 @@ used for one thing only -- the byte all-gather that la_comm_create takes as its 
   M x M on host buffers      la_mul_mat_mat_host_sharded: 1/world of B per PCIe link, slices over NVLink
   transpose                  la_transpose_sharded: pieces stored straight into the owners' memory
 
-`Comm` wraps the process group; `local` is the module providing Vector/Matrix.  The CPU tests (tests/test_dist_gloo.py)
-inject a numpy stand-in under gloo: for that case only, this file carries a host-side restatement of the partition /
-exchange / rank-ordered-combination logic, so the shapes and orders can be checked without a GPU."""
+`Comm` wraps the process group; `local` is the module providing Vector/Matrix.  This file holds bookkeeping only (who owns which
+range, which entry point to call): it contains no arithmetic and no exchange of its own.  The CPU tests (tests/test_dist_gloo.py)
+drive the same bookkeeping under gloo with a numpy stand-in module that brings its own `ShardedEngine` (tests/fake_local.py: a host
+model of the rank-ordered combinations); with the real module every cross-rank step is a la_*_sharded call."""
+import ctypes
+
 import numpy as np
 
 
 def partition(n, world, rank):
-    """Contiguous block partition of range(n): the first n % world ranks get one extra element."""
-    base, extra = divmod(int(n), int(world))
-    lo = rank * base + min(rank, extra)
-    return lo, lo + base + (1 if rank < extra else 0)
+    """la_partition (csrc/comm.cu): contiguous blocks, the first n % world ranks get one extra element."""
+    from . import _lib
+    lo, hi = ctypes.c_size_t(), ctypes.c_size_t()
+    _lib.lib.la_partition(int(n), int(world), int(rank), ctypes.byref(lo), ctypes.byref(hi))
+    return lo.value, hi.value
 
 
 class Comm:
@@ -51,13 +55,16 @@ class Comm:
         self.dist.barrier(group=self.group)
 
     # ---- the communicator below the C ABI (csrc/comm.cu)
-    def on_device(self, m):
-        """True when `m` is the real module on GPUs: the la_*_sharded entry points do the work."""
-        return self.backend == "nccl" and hasattr(m, "_lib")
+    def engine(self, m):
+        """Who performs the cross-rank steps for local module `m`: liblinalg_b200 for the real module, the stand-in's own
+        ShardedEngine otherwise (CPU tests)."""
+        cache = self.__dict__.setdefault("_engines", {})
+        if id(m) not in cache:
+            cache[id(m)] = _DeviceEngine(self, m) if hasattr(m, "_lib") else m.ShardedEngine(self)
+        return cache[id(m)]
 
     def lacomm(self, m):
         """Lazily: la_comm_create with a callback that all-gathers bytes over the process group."""
-        import ctypes
         h = getattr(self, "_la", None)
         if h is None:
             def xchg(_user, send, recv, nbytes):
@@ -84,15 +91,36 @@ class Comm:
             self._la = None
 
 
-def combine_scalars(parts, np_dtype):
-    """Rank-ordered sum of per-rank partials with the element type's own arithmetic (integers
-    wrap, f32 rounds after every add): what a single device would produce from those partials."""
-    dt = np.dtype(np_dtype)
-    acc = dt.type(0)
-    with np.errstate(over="ignore"):
-        for p in parts:
-            acc = dt.type(acc + np.frombuffer(p, dtype=dt, count=1)[0])
-    return acc
+class _DeviceEngine:
+    """Cross-rank steps with the real module: one la_*_sharded call each (csrc/comm.cu).  The few microseconds of Python around a
+    call are what the ranks drift apart by between rounds, so the scalar path is kept short."""
+
+    def __init__(self, comm, m):
+        self.comm, self.m, self.h = comm, m, comm.lacomm(m)
+        self.out = np.zeros(1, dtype=np.uint64)
+        self.out_ptr = self.out.ctypes.data
+
+    def scalar(self, a, b):
+        """sum of a (b is None) or dot(a, b) over all ranks."""
+        lib, dt = self.m._lib.lib, a.dtype
+        if b is None:
+            st = lib.la_sum_vec_sharded(self.h, dt.code, a.ptr, a.len(), self.out_ptr, None)
+        else:
+            st = lib.la_dot_vec_vec_sharded(self.h, dt.code, a.ptr, b.ptr, a.len(), self.out_ptr, None)
+        if st:
+            self.m._lib.check(st)
+        return self.out.view(dt.np)[0].copy()        # the value sits in the low bytes of the 8-byte word
+
+    def eq(self, a, b):
+        eq = ctypes.c_int(0)
+        self.m._lib.call("la_eq_vec_sharded", self.h, a.dtype.code, a.ptr, b.ptr, a.len(), ctypes.byref(eq), None)
+        return bool(eq.value)
+
+    def vec_mat(self, v, mat, cols):
+        out = self.m.Vector.uninitialized(cols, v.dtype)
+        self.m._lib.call("la_mul_vec_mat_sharded", self.h, v.dtype.code, out.ptr, v.ptr, mat.data.ptr, mat.get_row_count(), cols, None)
+        self.m.synchronize()
+        return out
 
 
 class ShardedVector:
@@ -146,23 +174,14 @@ class ShardedVector:
 
     # one exchange: a single element per rank, combined in rank order
     def sum(self):
-        if self.comm.on_device(self._mod()):
-            return _device_scalar(self, None)
-        part = self.local.sum()
-        return combine_scalars(self.comm.all_gather_host(np.asarray(part).tobytes()), self.local.dtype.np)
+        return self.comm.engine(self._mod()).scalar(self.local, None)
 
     def __eq__(self, other):
         if not isinstance(other, ShardedVector):
             return NotImplemented
-        same_shape = self.global_len == other.global_len and self.local.dtype.code == other.local.dtype.code
-        m = self._mod()
-        if same_shape and self.comm.on_device(m):
-            import ctypes
-            eq = ctypes.c_int(0)
-            m._lib.call("la_eq_vec_sharded", self.comm.lacomm(m), self.local.dtype.code, self.local.ptr, other.local.ptr, self.local.len(), ctypes.byref(eq), None)
-            return bool(eq.value)
-        mine = bool(same_shape and self.local == other.local)
-        return all(p == b"\x01" for p in self.comm.all_gather_host(b"\x01" if mine else b"\x00"))
+        if self.global_len != other.global_len or self.local.dtype.code != other.local.dtype.code:
+            return False                    # global properties: every rank decides the same without an exchange
+        return self.comm.engine(self._mod()).eq(self.local, other.local)
 
     __hash__ = None
 
@@ -185,31 +204,9 @@ def _pad(b, n):
     return b + b"\x00" * (n - len(b))
 
 
-def _device_scalar(a, b):
-    """sum (b is None) / dot over all ranks: one la_*_sharded call (one fused launch per rank, result on the host).  The few
-    microseconds of Python around the call are what the ranks drift apart by between rounds, so the path is kept short."""
-    m, comm, dt = a._mod(), a.comm, a.local.dtype
-    h = comm.lacomm(m)
-    out = getattr(comm, "_scalar_out", None)
-    if out is None:
-        out = comm._scalar_out = np.zeros(1, dtype=np.uint64)
-        comm._scalar_ptr = out.ctypes.data
-    lib = m._lib.lib
-    if b is None:
-        st = lib.la_sum_vec_sharded(h, dt.code, a.local.ptr, a.local.len(), comm._scalar_ptr, None)
-    else:
-        st = lib.la_dot_vec_vec_sharded(h, dt.code, a.local.ptr, b.local.ptr, a.local.len(), comm._scalar_ptr, None)
-    if st:
-        m._lib.check(st)
-    return out.view(dt.np)[0].copy() if dt.size == 8 else np.frombuffer(out.tobytes()[:dt.size], dtype=dt.np)[0]
-
-
 def dot(a, b):
     a._co(b)
-    if a.comm.on_device(a._mod()):
-        return _device_scalar(a, b)
-    part = a._mod().dot(a.local, b.local)
-    return combine_scalars(a.comm.all_gather_host(np.asarray(part).tobytes()), a.local.dtype.np)
+    return a.comm.engine(a._mod()).scalar(a.local, b.local)
 
 
 class ShardedMatrix:
@@ -267,7 +264,7 @@ def transpose(sm):
     rows_g, cols_g = sm.global_rows, sm.col_count
     if comm.world == 1:
         return ShardedMatrix(comm, sm.local.transpose(), cols_g, sm._m)
-    assert comm.on_device(m), "the sharded transpose runs on GPUs (la_transpose_sharded)"
+    assert hasattr(m, "_lib"), "the sharded transpose runs on GPUs (la_transpose_sharded)"
     lo, hi = partition(cols_g, comm.world, comm.rank)
     out = m.Matrix.uninitialized(hi - lo, rows_g, sm.local.dtype)
     m._lib.call("la_transpose_sharded", comm.lacomm(m), sm.local.dtype.code, out.data.ptr, sm.local.data.ptr, rows_g, cols_g, None)
@@ -290,7 +287,7 @@ def mul_host(comm, a_shard_host, b_host, a_rows_global, k, n, out=None, local_mo
     assert a.size == rows * k and b.size == k * n
     if out is None:
         out = np.empty(rows * n, dtype=a.dtype)
-    if comm.world == 1 or not comm.on_device(m):
+    if comm.world == 1:
         m._lib.call("la_mul_mat_mat_host", dt.code, out.ctypes.data, a.ctypes.data, b.ctypes.data, rows, k, n)
         return out
     m._lib.call("la_mul_mat_mat_host_sharded", comm.lacomm(m), dt.code, out.ctypes.data, a.ctypes.data, b.ctypes.data, a_rows_global, k, n)
@@ -305,28 +302,12 @@ def mul_transpose_mat(vector, sharded_m):
 
 
 def _sharded_vec_mat(sv, sm):
-    """v x M with v and M co-sharded by rows: local full-length partial, then one all_gather and
-    rank-ordered adds.  Returns a replicated plain Vector of `cols` elements."""
+    """v x M with v and M co-sharded by rows: every rank's full-length partial, added in rank order (la_mul_vec_mat_sharded).
+    Returns a replicated plain Vector of `cols` elements."""
     assert sv.global_len == sm.global_rows, "assertion failed: `(left == right)` left: `%d`, right: `%d`" % (sv.global_len, sm.global_rows)
-    m = sm._mod()
-    comm = sv.comm
-    if comm.world == 1:
+    if sv.comm.world == 1:
         return sv.local * sm.local
-    if comm.on_device(m):
-        dtp = sv.local.dtype
-        out = m.Vector.uninitialized(sm.col_count, dtp)
-        m._lib.call("la_mul_vec_mat_sharded", comm.lacomm(m), dtp.code, out.ptr, sv.local.ptr, sm.local.data.ptr, sm.local.get_row_count(), sm.col_count, None)
-        m.synchronize()
-        return out
-    partial = sv.local * sm.local
-    # host path (gloo / CPU tests)
-    parts = comm.all_gather_host(partial.to_vec().tobytes())
-    dt = partial.dtype.np
-    acc = np.frombuffer(parts[0], dtype=dt).copy()
-    with np.errstate(over="ignore"):
-        for p in parts[1:]:
-            acc = (acc + np.frombuffer(p, dtype=dt)).astype(dt)
-    return m.Vector.from_vec(acc, partial.dtype)
+    return sv.comm.engine(sm._mod()).vec_mat(sv.local, sm.local, sm.col_count)
 
 
 def _default_local():

@@ -1,6 +1,8 @@
 """A numpy stand-in for linear_algebra_b200's Vector/Matrix, used ONLY by tests/test_dist_gloo.py
-to drive the sharding / exchange logic of linear_algebra_b200/dist.py on CPU under gloo.  It is
-test scaffolding, not a fallback: the product never imports it."""
+to drive the sharding bookkeeping of linear_algebra_b200/dist.py on CPU under gloo, together with a host model
+(`ShardedEngine`) of what liblinalg_b200's la_*_sharded entry points do across ranks: partials exchanged as bytes and
+combined in rank order with the element type's own arithmetic (csrc/comm.cu: combine_host and the fused kernels).
+It is test scaffolding, not a fallback: the product never imports it."""
 import numpy as np
 
 from linear_algebra_b200.traits import parameter
@@ -123,3 +125,40 @@ def mul_transpose_mat(v, m):
 
 def synchronize():
     pass
+
+
+def combine_scalars(parts, np_dtype):
+    """Rank-ordered sum of per-rank partials with the element type's own arithmetic (integers wrap, f32 rounds after every
+    add): what la_sum_vec_sharded / la_dot_vec_vec_sharded deliver on every rank."""
+    dt = np.dtype(np_dtype)
+    acc = dt.type(0)
+    with np.errstate(over="ignore"):
+        for p in parts:
+            acc = dt.type(acc + np.frombuffer(p, dtype=dt, count=1)[0])
+    return acc
+
+
+class ShardedEngine:
+    """Host model of the cross-rank steps (linear_algebra_b200/dist.py asks the local module for it when that module is not
+    the real one)."""
+
+    def __init__(self, comm):
+        self.comm = comm
+
+    def scalar(self, a, b):
+        part = a.sum() if b is None else dot(a, b)
+        return combine_scalars(self.comm.all_gather_host(np.asarray(part).tobytes()), a.dtype.np)
+
+    def eq(self, a, b):
+        mine = bool(a == b)
+        return all(p == b"\x01" for p in self.comm.all_gather_host(b"\x01" if mine else b"\x00"))
+
+    def vec_mat(self, v, mat, cols):
+        partial = v * mat
+        parts = self.comm.all_gather_host(partial.to_vec().tobytes())
+        dt = partial.dtype.np
+        acc = np.frombuffer(parts[0], dtype=dt).copy()
+        with np.errstate(over="ignore"):
+            for p in parts[1:]:
+                acc = (acc + np.frombuffer(p, dtype=dt)).astype(dt)
+        return Vector.from_vec(acc, partial.dtype)

@@ -1,7 +1,7 @@
-"""World-size-2 gloo tests (CPU) of the multi-GPU host logic in linear_algebra_b200/dist.py:
-row-block partitioning, the byte-level exchanges and the rank-ordered combination.  The local
-per-rank arithmetic is a numpy stand-in (tests/fake_local.py); on GPUs the same code drives the
-CUDA kernels (tests/test_gpu_dist.py)."""
+"""World-size-2 gloo tests (CPU) of the multi-GPU bookkeeping in linear_algebra_b200/dist.py: row-block partitioning
+(la_partition), which shard goes where, the byte all-gather that la_comm_create takes as its exchange callback.  The per-rank
+arithmetic and the rank-ordered combinations are a numpy stand-in (tests/fake_local.py: Vector / Matrix / ShardedEngine); on
+GPUs the same bookkeeping drives liblinalg_b200's la_*_sharded entry points (tests/test_gpu_dist.py, tests/test_gpu_comm_cpp.py)."""
 import os
 import socket
 import sys
@@ -23,8 +23,9 @@ def test_partition_covers_everything_once():
             assert max(sizes) - min(sizes) <= 1
 
 
-def test_combine_scalars_wraps_and_keeps_rank_order():
-    from linear_algebra_b200.dist import combine_scalars
+def test_the_host_model_combines_in_rank_order_with_the_element_types_arithmetic():
+    sys.path.insert(0, HERE)
+    from fake_local import combine_scalars
     parts = [np.uint8(200).tobytes(), np.uint8(100).tobytes()]
     assert combine_scalars(parts, np.uint8) == np.uint8(44)
     f = [np.float32(1e8).tobytes(), np.float32(1.0).tobytes(), np.float32(-1e8).tobytes()]

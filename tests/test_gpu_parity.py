@@ -659,6 +659,32 @@ def test_matmat_tensor_engine_on_structured_data(la):
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
+def test_matmat_tensor_engine_a_read_in_place_stays_inside_the_gate(la):
+    """la_gemm_tc_set_a_direct (an experiment, off by default): A is read in place as its own hi plane -- the tensor
+    cores truncate the f32 word to tf32 -- and its lo part is taken against the truncated value.  Less accurate than the rounded
+    split (measured 1.2 - 1.4 x its error) but still inside the unrelaxed gate wherever the engine uses bf16 cross terms
+    (K >= 1024); below that the flag has no effect.  The prepared-B path must agree with the direct call bit for bit."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    lib.la_gemm_tc_set_a_direct(1)
+    try:
+        for M, K, N in ((512, 1024, 384), (388, 2052, 260), (256, 4096, 512)):
+            a = gen.values("f32", M * K, 73); b = gen.values("f32", K * N, 74)
+            check_f32_gemm(la, a, b, M, K, N, ("A in place", M, K, N), 1.0)
+            assert lib.la_gemm_last_engine() == 2
+            A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+            assert same((A * B).to_vec(), A.mul_prepared(B.prepare()).to_vec()), (M, K, N)
+        M, K, N = 512, 256, 384                       # tf32 cross terms: the flag changes nothing
+        a = gen.values("f32", M * K, 75); b = gen.values("f32", K * N, 76)
+        A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+        with_flag = (A * B).to_vec()
+        lib.la_gemm_tc_set_a_direct(0)
+        assert same(with_flag, (A * B).to_vec())
+    finally:
+        lib.la_gemm_tc_set_a_direct(0)
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
 @pytest.mark.parametrize("bn", [224, 192])
 def test_matmat_3xtf32_narrower_tiles_change_nothing(la, bn):
     """la_gemm_tc_set_tile_n: pair tiles 256 x 224 / 256 x 192 (picked when they pack the waves better, e.g. the 8-GPU shard

@@ -54,7 +54,7 @@ struct la_comm {
     size_t vec_half = 0;
     unsigned long long seq = 0;
     unsigned long long* res_host = nullptr; unsigned long long* res_dev = nullptr;     // zero-copy: [0] value, [1] sequence number of the round it belongs to
-    cudaStream_t side = nullptr; cudaEvent_t side_done = nullptr, main_done = nullptr;  // the gather of B runs beside the uploads of A
+    cudaStream_t side = nullptr; cudaEvent_t side_done = nullptr;                       // the gather of B runs beside the uploads of A
     std::string note;
 };
 
@@ -77,22 +77,31 @@ la_status agree(la_comm* c, bool mine, bool* all) {
 }
 la_status barrier(la_comm* c) { bool all; return agree(c, true, &all); }
 
-void unexport(la_comm* c, Exported& e) {
-    for (int p = 0; p < c->world; ++p) {
-        if (!e.ptr[p]) continue;
-        if (p == c->rank) cudaFree(e.ptr[p]); else cudaIpcCloseMemHandle(e.ptr[p]);
-        e.ptr[p] = nullptr;
-    }
+// Giving up an exported buffer has two halves: unmapping the peers' buffers here, and freeing this rank's own -- which the peers
+// must have unmapped first.  The collective paths (a buffer being replaced, la_comm_destroy) put a barrier between the two;
+// unexport() is the immediate form for the error paths, where no further exchange can be relied on.
+void close_imports(la_comm* c, Exported& e) {
+    for (int p = 0; p < c->world; ++p)
+        if (p != c->rank && e.ptr[p]) { cudaIpcCloseMemHandle(e.ptr[p]); e.ptr[p] = nullptr; }
+    (void)cudaGetLastError();
+}
+void free_own(la_comm* c, Exported& e) {
+    if (e.ptr[c->rank]) { cudaFree(e.ptr[c->rank]); e.ptr[c->rank] = nullptr; }
     e.bytes = 0;
     (void)cudaGetLastError();
 }
+void unexport(la_comm* c, Exported& e) { close_imports(c, e); free_own(c, e); }
 
 // Collective: every rank creates a zeroed buffer of `bytes`, the cudaIpc handles go round, every rank maps the others'.  Every
 // rank issues the same sequence of exchanges whatever fails locally, and all ranks end with the same answer in *ok.
 la_status export_collective(la_comm* c, Exported& e, size_t bytes, bool* ok) {
     LA_CUDA(cudaDeviceSynchronize());
     LA_TRY(barrier(c));                                   // nobody is still reading the buffers about to be replaced
-    unexport(c, e);
+    if (e.bytes) {
+        close_imports(c, e);
+        LA_TRY(barrier(c));                               // every peer has unmapped this rank's old buffer
+        free_own(c, e);
+    }
     void* mine = nullptr;
     cudaIpcMemHandle_t h; memset(&h, 0, sizeof(h));
     bool fine = cudaMalloc(&mine, bytes) == cudaSuccess && cudaMemset(mine, 0, bytes) == cudaSuccess && cudaIpcGetMemHandle(&h, mine) == cudaSuccess;
@@ -181,7 +190,9 @@ extern "C" la_status la_comm_destroy(la_comm* c) {
     if (!c) return LA_OK;
     cudaDeviceSynchronize();
     if (c->world > 1) barrier(c);                          // peers are done with this rank's buffers
-    unexport(c, c->box); unexport(c, c->vec); unexport(c, c->stage);
+    close_imports(c, c->box); close_imports(c, c->vec); close_imports(c, c->stage);
+    if (c->world > 1) barrier(c);                          // ... and have unmapped them
+    free_own(c, c->box); free_own(c, c->vec); free_own(c, c->stage);
     if (c->res_host) cudaFreeHost(c->res_host);
     if (c->side) cudaStreamDestroy(c->side);
     if (c->side_done) cudaEventDestroy(c->side_done);
@@ -282,6 +293,7 @@ extern "C" la_status la_mul_vec_mat_sharded(la_comm* c, int dtype, void* C, cons
     la_status s = rows_local ? la_mul_vec_mat(dtype, part, v_local, M_local, rows_local, cols, stream) : LA_OK;
     if (s == LA_OK && rows_local == 0 && cudaMemsetAsync(part, 0, bytes, st) != cudaSuccess) s = LA_ERR_CUDA;
     unsigned char* mine = (unsigned char*)malloc(bytes); unsigned char* all = (unsigned char*)malloc(bytes * c->world); unsigned char* sum = (unsigned char*)malloc(bytes);
+    if (s == LA_OK && (!mine || !all || !sum)) s = la_fail(LA_ERR_OOM, "la_mul_vec_mat_sharded: out of host memory for %zu bytes x %d ranks", bytes, c->world);
     if (s == LA_OK) s = la_download(mine, part, bytes, stream);
     if (s == LA_OK) s = xchg(c, mine, all, bytes);
     if (s == LA_OK) {

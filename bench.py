@@ -431,6 +431,42 @@ def extras_multi(la, comm, hbm_peak):
     sv = ladist.ShardedVector(comm, la.Vector.synth(0x5EED2002 + rank, rhi - rlo, "f32"), r)
     rec("mat_x_vec_f32_32768^2_sharded", wall(lambda: ladist.mul_transpose_mat(v, M), 10), 4 * (r * r + 2 * r))
     rec("vec_x_mat_f32_32768^2_sharded", wall(lambda: sv * M, 10), 4 * (r * r + 2 * r), device_ms(lambda: sv * M, 10))
+    # BASELINE.json configs[3] on N GPUs: the square f32 GEMM sweep, A / C row-block sharded, B replicated (no exchange on the
+    # data path): FP32 SIMT engine (the north star's), tensor engine cold and with B prepared.  Whole-job TFLOP/s, max over ranks.
+    lib = la._lib
+
+    def gemm_ms(fn, iters):
+        for _ in range(3):
+            fn()
+        la.synchronize(); comm.barrier()
+        e0, e1 = la.Event(), la.Event()
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record(); la.synchronize()
+        t = torch.tensor([e0.elapsed_ms(e1) / iters], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        return float(t[0])
+
+    sweep = {}
+    for nn in (2048, 4096, 8192, 16384):
+        rlo, rhi = ladist.partition(nn, world, rank)
+        rows_nn = rhi - rlo
+        P = la.Vector.synth(0x5EED0003 + rank, rows_nn * nn, "f32"); Q = la.Vector.synth(0x5EED1003, nn * nn, "f32"); R = la.Vector.uninitialized(rows_nn * nn, "f32")
+        row = {"rows_per_gpu": rows_nn}
+        for mode, label, iters in ((0, "simt", 5), (1, "tensor_cold", 10)):
+            lib.call("la_set_gemm_mode", mode)
+            ms = gemm_ms(lambda: lib.call("la_mul_mat_mat", 8, R.ptr, P.ptr, Q.ptr, rows_nn, nn, nn, None), iters)
+            row[label] = {"ms": round(ms, 4), "TFLOP/s": round(2.0 * nn ** 3 / ms / 1e9, 1)}
+        hnd = ctypes.c_void_p()
+        lib.call("la_gemm_prepare_b", 8, Q.ptr, nn, nn, None, ctypes.byref(hnd))
+        ms = gemm_ms(lambda: lib.call("la_mul_mat_mat_prepared", R.ptr, P.ptr, hnd, rows_nn, None), 10)
+        lib.call("la_gemm_prepared_free", hnd)
+        row["tensor_b_prepared"] = {"ms": round(ms, 4), "TFLOP/s": round(2.0 * nn ** 3 / ms / 1e9, 1)}
+        lib.call("la_set_gemm_mode", 2)
+        sweep[str(nn)] = row
+        del P, Q, R
+    out["gemm_f32_sweep_sharded"] = sweep
     out["_note"] = ("la_*_sharded entry points (csrc/comm.cu): exchange fused into the kernels -- partials stored into / read from the peers' cudaIpc-mapped buffers over NVLink, "
                     "rank-ordered (deterministic); `ms` = wall time of the blocking call with the scalar on the host (zero-copy word, no D2H copy), `kernel_ms` = CUDA events around the launch")
     return out
@@ -739,6 +775,10 @@ def run_ours(args):
             line["extra"] = em
             line["roofline"]["hbm_sharded"] = {"_columns": ["GB/s whole job (wall, scalar on the host)", "frac of N x measured copy peak", "GB/s kernel only (events)", "kernel frac"],
                                                **{k: [v["GB/s"], v["frac_of_measured_hbm_x_n"]] + ([v["kernel_GB/s"], v["kernel_frac_of_measured_hbm_x_n"]] if "kernel_GB/s" in v else []) for k, v in em.items() if isinstance(v, dict) and "GB/s" in v}}
+            sw = em.get("gemm_f32_sweep_sharded", {})
+            line["roofline"]["sweep_f32_sharded"] = {"_columns": ["simt TFLOP/s (whole job)", "simt frac of N x nominal FP32 peak", "tensor TFLOP/s (cold)", "tensor TFLOP/s (B prepared)"],
+                                                     "_note": "BASELINE.json configs[3] on %d GPUs (A / C row-block sharded, B replicated); taken after seconds of load: a GPU settles 5-10 %% below its first-50-ms rate" % world,
+                                                     **{k: [v["simt"]["TFLOP/s"], round(v["simt"]["TFLOP/s"] / (simt_peak * world), 3), v["tensor_cold"]["TFLOP/s"], v["tensor_b_prepared"]["TFLOP/s"]] for k, v in sw.items()}}
     if rank == 0 and parity is not None:
         line["parity_checked"] = parity
     if rank == 0:

@@ -324,10 +324,10 @@ def extras(la, hbm_peak, peak_src):
         lib.call("la_gemm_prepared_free", hnd)
         row["3xtf32_prepared_b"] = {"ms": round(st["median"], 4), "best_ms": round(st["best"], 4), "TFLOP/s": round(2.0 * nn ** 3 / st["median"] / 1e9, 2)}
         lib.call("la_set_gemm_mode", 2)
-        units = 2 if nn >= 1024 else 3         # K >= 1024: 1 tf32 MMA + 2 bf16 MMAs (half the time each) per product; below: 3 tf32 MMAs
+        units = 1.5 if nn >= 1024 else 3       # K >= 1024: three fp16 MMAs (half a tf32 MMA's time each) per product; below: 3 tf32 MMAs
         row["3xtf32"]["roofline"] = {"bound": "tensor", "achieved": round(units * row["3xtf32"]["TFLOP/s"], 1), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
                                       "frac": round(units * row["3xtf32"]["TFLOP/s"] / tf32_peak, 3),
-                                      "note": "achieved = tensor-core work issued in tf32-equivalent flops (%d per useful f32 flop; pre-pass included in the time); peak = measured bf16 / 2" % units}
+                                      "note": "achieved = tensor-core work issued in tf32-equivalent flops (%.1f per useful f32 flop; pre-pass included in the time); peak = measured bf16 / 2" % units}
         sweep[str(nn)] = row
         del P, Q, R
     out["gemm_f32_sweep"] = sweep
@@ -638,7 +638,9 @@ def run_ours(args):
     barrier()
     t1 = time.time()
 
-    engine_used = lib.lib.la_gemm_last_engine()     # 1 = TMA SIMT, 2 = tcgen05 3xTF32
+    engine_used = lib.lib.la_gemm_last_engine()     # 1 = TMA SIMT, 2 = tcgen05 split-f32
+    tc_form = lib.lib.la_gemm_tc_last_form()        # of the cold step just timed -- 1: f16-split form (three fp16 MMAs per product), 0: tf32 form (three tf32 MMAs)
+    tc_launches = lib.lib.la_gemm_tc_last_launches()
 
     time.sleep(1.0)                                     # same protocol as the headline region: GPU idle, then W warm-up steps, then K timed steps
     steady_total, steady_kernel_ms = time_steady()
@@ -692,23 +694,27 @@ def run_ours(args):
         per_gpu_tflops = value / world / 1e3
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         if engine_used == 2:
-            tf32_peak = peaks.get("bf16_tflops", 1590.0) / 2.0
-            tf32_sustained = peaks.get("bf16_tflops_sustained", 1400.0) / 2.0
-            # K = 8192: each product is 1 tf32 MMA (hi*hi) + 2 bf16 MMAs (hi*lo, lo*hi; half a tf32 MMA's time each)
-            #           = 2 tf32-equivalent flops of tensor-core work per useful f32 flop
-            roofline = {"bound": "tensor", "achieved": round(2 * per_gpu_tflops, 1), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
-                        "frac": round(2 * per_gpu_tflops / tf32_peak, 4), "frac_of_sustained_peak": round(2 * per_gpu_tflops / tf32_sustained, 4),
-                        "peak_source": "measured (MEASURED_PEAKS.json): bf16 burst %.1f / 2 (tf32 runs at half the bf16 rate)" % peaks.get("bf16_tflops", 1590.0),
-                        "achieved_note": "tensor-core work per second in tf32-equivalent flops: per useful f32 product 1 tf32 MMA + 2 bf16 MMAs at twice the rate = 2 units; the split pre-pass is inside the time",
+            mma16_peak = peaks.get("bf16_tflops", 1590.0)       # 16-bit MMA rate (fp16 = bf16); tf32 runs at half of it
+            mma16_sustained = peaks.get("bf16_tflops_sustained", 1400.0)
+            tf32_peak = mma16_peak / 2.0
+            # tensor-core work per useful f32 flop, in 16-bit MMA flops: f16-split form 3 (hi*hi, hs*ls, ls*hs, all fp16); tf32 form 3 tf32 MMAs = 6
+            work = 3.0 if tc_form == 1 else 6.0
+            roofline = {"bound": "tensor", "achieved": round(work * per_gpu_tflops, 1), "peak": round(mma16_peak, 1), "unit": "TFLOP/s",
+                        "frac": round(work * per_gpu_tflops / mma16_peak, 4), "frac_of_sustained_peak": round(work * per_gpu_tflops / mma16_sustained, 4),
+                        "peak_source": "measured (MEASURED_PEAKS.json): bf16 burst %.1f (fp16 MMAs run at the bf16 rate, tf32 at half of it)" % mma16_peak,
+                        "achieved_note": ("tensor-core work per second in 16-bit MMA flops: per useful f32 product three fp16 x fp16 MMAs (hi*hi, hs*ls, ls*hs) = 3 units; the pre-pass is inside the time"
+                                          if tc_form == 1 else "tensor-core work per second in 16-bit-equivalent MMA flops: per useful f32 product three tf32 MMAs at half the 16-bit rate = 6 units; the pre-pass is inside the time"),
+                        "useful_f32_frac_of_tf32_peak": round(per_gpu_tflops / tf32_peak, 4),
                         "kernel_only": (None if not kernel_ms else {
-                            "kernel": "gemm_3xtf32_2cta_kernel", "avg_launch_ms": round(kernel_ms, 4), "launches_timed": _kn.value,
+                            "kernel": "gemm_f16split_2cta_kernel" if tc_form == 1 else "gemm_3xtf32_2cta_kernel", "avg_launch_ms": round(kernel_ms, 4), "launches_timed": _kn.value,
                             "share_of_step": round(kernel_ms / ms_step, 4),
-                            "achieved": round(2 * 2.0 * (n / world) * n * n / kernel_ms / 1e9, 1), "frac": round(2 * 2.0 * (n / world) * n * n / kernel_ms / 1e9 / tf32_peak, 4),
+                            "achieved": round(work * 2.0 * (n / world) * n * n / kernel_ms / 1e9, 1), "frac": round(work * 2.0 * (n / world) * n * n / kernel_ms / 1e9 / mma16_peak, 4),
                             "algorithmic_TFLOP/s": round(2.0 * (n / world) * n * n / kernel_ms / 1e9, 1),
                             "note": "CUDA events around each launch of the kernel on its own stream, inside the timed region (rank 0)"}),
-                        "traffic": ncu_traffic("profiles/r2_gemm_3xtf32_8192_ncu_full.txt", "gemm_3xtf32_2cta_kernel")}
-            engine_name = "tcgen05 split-f32 (hi*hi as tf32, cross terms as bf16; cta_group::2 CTA pairs, TMA, chunked FP32 accumulation; same f32 gate as SIMT)"
-            launches = 2                            # split_both_kernel + gemm_3xtf32_2cta_kernel per cold step
+                        "traffic": ncu_traffic("profiles/r2_gemm_f16split_8192_ncu_full.txt", "gemm_f16split_2cta_kernel")}
+            engine_name = ("tcgen05 split-f32, f16 form (rows of A / columns of B scaled by powers of two; hi = fp16, residual lifted by 2^6 into fp16; three fp16 MMAs per product; cta_group::2 CTA pairs, TMA, chunked FP32 accumulation; same f32 gate as SIMT)"
+                           if tc_form == 1 else "tcgen05 split-f32, tf32 form (three tf32 MMAs per product)")
+            launches = tc_launches                              # pre-pass (2 launches), product, fix-ups of left-out elements (0 - 2) per cold step
         else:
             roofline = {"bound": "fp32-fma (SIMT; MEASURED_PEAKS.json has no FP32 figure)", "achieved": round(per_gpu_tflops, 2),
                         "peak": round(simt_peak, 2), "unit": "TFLOP/s", "frac": round(per_gpu_tflops / simt_peak, 4),
@@ -723,13 +729,13 @@ def run_ours(args):
         roofline["steady_prepared_b"] = {
             "value": round(steady_value, 1), "unit": UNIT, "ms_per_step": round(steady_step_ms, 4),
             "timed": "after the headline region and one idle second, with the same protocol (3 warm-up steps, then K timed steps): within ~50 ms of tensor load the GPU settles into a lower power state, so two regions are only comparable when both start from idle",
-            "frac": (round(2 * steady_value / world / 1e3 / tf32_peak, 4) if engine_used == 2 else round(steady_value / world / 1e3 / simt_peak, 4)),
+            "frac": (round(work * steady_value / world / 1e3 / mma16_peak, 4) if engine_used == 2 else round(steady_value / world / 1e3 / simt_peak, 4)),
             "kernel_share_of_step": (round(steady_kernel_ms / steady_step_ms, 4) if steady_kernel_ms else None),
             "note": "same products through la_gemm_prepare_b (once, outside) + la_mul_mat_mat_prepared: the replicated B's split/transpose planes are reused, results bit-identical; `value` of this line is the COLD figure with B's pre-pass inside every step"}
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32" if engine_used != 2 else "f32 (each product as hi*hi in tf32 + hi*lo + lo*hi in bf16 on the tensor cores, FP32 accumulate; gate: every output's error <= max(worst error of the reference's own k-ascending order on the same problem, 2^-22 sum|a||b|))",
+            "dtype": "f32" if engine_used != 2 else "f32 (each product as hi*hi + hi*lo + lo*hi of an fp16 hi / lifted-residual split on the tensor cores, FP32 accumulate; gate: every output's error <= max(worst error of the reference's own k-ascending order on the same problem, 2^-22 sum|a||b|))",
             "data": "synthetic",
             "config": {"workload": "f32 GEMM 8192x8192x8192, C = A x B, A/C row-block sharded over %d GPU(s), B replicated" % world,
                        "M": n, "K": n, "N": n, "rows_per_gpu": rows, "l2": "operands 768 MB >> 126 MB L2 (no flush needed)",

@@ -29,6 +29,9 @@ int la_gemm_last_padded(void);
 la_status la_gemm_tc_set_variant(int variant);     /* 0 CTA pairs (default); 5 / 3 one CTA per tile with / without B multicast; 1 / 2 single accumulation chain (drifts: reference only) */
 la_status la_gemm_tc_set_persistent(int on);       /* persistent grid of sm_count / 2 CTA pairs; bit-identical results */
 la_status la_gemm_tc_set_chunk(int k_blocks);      /* k-blocks of 32 per accumulation chain inside the tensor cores; 0 = by K */
+int la_gemm_tc_last_form(void);                    /* this thread's last f32 tensor-engine product: 0 tf32 form, 1 f16-split form */
+int la_gemm_tc_last_launches(void);                /* ... and the kernels it launched (pre-pass, product, fix-ups of left-out elements) */
+la_status la_gemm_tc_set_f16(int mode);            /* f16-split form of the engine (row / column scaled operands, hi = fp16, lo = bf16, three 16-bit MMAs per product): -1 by K (default: from K = 1024), 0 never, 1 wherever the shapes allow (K >= 256, K % 8 == 0) */
 la_status la_gemm_tc_set_a_direct(int on);         /* EXPERIMENT: A is read in place as its own hi plane (hardware truncation to tf32), lo taken against the truncated value */
 la_status la_gemm_tc_set_cross(int mode);          /* cross terms: -1 by K, 0 tf32, 1 bf16 (below K = 1024 gated at twice the reference order's error) */
 la_status la_gemm_tc_set_tile_n(int bn);           /* pair tile width 256 / 224 / 192; 0 = by wave count; bit-identical results with the K-split off */

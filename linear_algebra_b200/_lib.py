@@ -130,9 +130,9 @@ lib.la_dtype_size.restype = ctypes.c_size_t
 # tuning / introspection hooks (include/linalg_b200_tuning.h)
 TUNING = {
     "la_gemm_set_variant": [_I], "la_gemm_tc_set_variant": [_I], "la_gemm_tc_set_persistent": [_I], "la_gemm_tc_set_chunk": [_I],
-    "la_gemm_tc_set_cross": [_I], "la_gemm_tc_set_a_direct": [_I], "la_gemm_tc_set_tile_n": [_I], "la_gemm_set_stream_tail": [_I], "la_gemm_set_raster": [_I],
+    "la_gemm_tc_set_cross": [_I], "la_gemm_tc_set_a_direct": [_I], "la_gemm_tc_set_f16": [_I], "la_gemm_tc_set_tile_n": [_I], "la_gemm_set_stream_tail": [_I], "la_gemm_set_raster": [_I],
     "la_gemm_kernel_timing": [_I], "la_gemm_kernel_time_ms": [ctypes.POINTER(ctypes.c_float), _PI],
-    "la_gemm_last_engine": [], "la_gemm_last_padded": [],
+    "la_gemm_last_engine": [], "la_gemm_last_padded": [], "la_gemm_tc_last_form": [], "la_gemm_tc_last_launches": [],
     "la_transpose_set_variant": [_I], "la_transpose_set_band": [_I], "la_transpose_set_hints": [_I], "la_transpose_set_mode": [_I],
 }
 for _name, _args in TUNING.items():

@@ -60,6 +60,7 @@ struct la_gemm_prepared {
     size_t K = 0, N = 0;
     const void* B = nullptr;                 // caller's K x N matrix: must stay allocated and unchanged while the handle lives
     float* tc_hi = nullptr; float* tc_lo = nullptr; bool tc_cross_bf16 = false;    // f32: split planes of B^T (gemm_tc.cu); NULL when not applicable
+    void* f16_planes = nullptr; bool f16_b_tiny = false, f16_b_sparse = false;                           // f32, f16-split form: fp16 hi | bf16 hi | bf16 lo planes of the column-scaled B^T, then the column exponents and the list of left-out elements (one block)
     uint8_t* limb_planes = nullptr;          // 8/16/32-bit integers: byte planes of B^T (gemm_limb.cu); NULL when not applicable
 };
 

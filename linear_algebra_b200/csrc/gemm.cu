@@ -527,6 +527,7 @@ extern "C" la_status la_gemm_prepared_free(la_gemm_prepared* handle) {
     if (!handle) return LA_OK;
     // products that use the planes may still be queued: a plain cudaFree waits for the device
     if (handle->tc_hi) cudaFree(handle->tc_hi);         // (tc_lo is the second half of the same block)
+    if (handle->f16_planes) cudaFree(handle->f16_planes);       // (exponents and list live in the same block)
     if (handle->limb_planes) cudaFree(handle->limb_planes);
     (void)cudaGetLastError();
     delete handle;

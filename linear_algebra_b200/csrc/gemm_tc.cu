@@ -33,6 +33,7 @@
 // at 90 % of that floor with the L2 -> SM path (11.6 TB/s of operand loads at 8192^3) close to its own limit, see the
 // note in the producer loop.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include "tc_common.cuh"
 #include "../../include/linalg_b200_tuning.h"
 
@@ -631,6 +632,491 @@ gemm_3xtf32_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorM
     }
 }
 
+// ------------------------------------------------------------------ f16-split variant of the CTA-pair kernel
+// Same structure as gemm_3xtf32_2cta_kernel, other operand format.  Every row of A and every column of B is scaled by a power of
+// two so that its largest magnitude lies in [2^14, 2^15) (exact), and the scaled value is split x = hi + lo with hi = fp16(x) --
+// 11 significant bits, what tf32 keeps.  Three planes per operand, all fp16: hi, hs = hi * 2^-6 and ls = fp16(lo * 2^6) (the
+// residual lifted into fp16's range: 11 of its 13 bits survive, where bf16 keeps 8).  A product is three fp16 x fp16 MMAs at twice
+// the tf32 rate -- hi*hi, hs*ls, ls*hs, the two powers of two cancelling exactly -- so 1.5 tf32-equivalent units per product
+// instead of 2 (or 3 with tf32 cross terms), 6 bytes of planes per element instead of 8, and a per-product error of ~2^-23 |a||b|
+// (bf16 cross terms: ~2^-20, fine when many comparable terms average it out, above the gate for an output that is essentially
+// ONE product -- B = identity, a permutation, a diagonal).  (fp16 x bf16 in one instruction would need one plane less, but is an
+// illegal instruction on this GPU.)  Neither hs nor ls may lose bits to fp16's subnormal range, which is why elements 2^-23 and
+// more below their row's / column's maximum are kept out of the planes (f16_split_one).  A stage holds 32 k of the six planes (A's
+// 128 rows and half of B's columns: 8 KB each, 64-byte rows, SWIZZLE_64B), four stages.  The epilogue multiplies by
+// 2^(ea[row] + eb[col]).
+constexpr int F16_BK = 32;                                      // k per stage
+constexpr int F16_PLANE = 128 * F16_BK * 2;                     // one 128-row slab of one plane: 8 KB
+constexpr int F16_STAGE_BYTES = 6 * F16_PLANE;                  // 48 KB
+constexpr int F16_STAGES = 4;
+static_assert((size_t)F16_STAGES * F16_STAGE_BYTES + 1024 == TC3_SMEM_BYTES, "same shared-memory budget as the tf32 pair kernel");
+
+__host__ __device__ constexpr uint32_t umma_idesc_16(int M, int N, int a_bf16, int b_bf16) {      // kind::f16: D = f32, A / B = fp16 or bf16, K-major
+    return (1u << 4) | ((uint32_t)a_bf16 << 7) | ((uint32_t)b_bf16 << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(TC3_THREADS, 1)
+gemm_f16split_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtensorMap map_a_hi, const __grid_constant__ CUtensorMap map_a_hb, const __grid_constant__ CUtensorMap map_a_lb,
+                          const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_hb, const __grid_constant__ CUtensorMap map_b_lb,
+                          const int* __restrict__ ea, const int* __restrict__ eb, int M, int N, const TcPlan plan) {
+    constexpr int STAGES = F16_STAGES;
+    constexpr int HC = BN / 2;
+    static_assert(BN % 32 == 0 && BN >= 64 && BN <= 256, "pair tile width");
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ alignas(8) uint64_t full_bar[STAGES];
+    __shared__ alignas(8) uint64_t empty_bar[STAGES];
+    __shared__ alignas(8) uint64_t acc_full_bar[2];
+    __shared__ alignas(8) uint64_t acc_empty_bar[2];
+    __shared__ uint32_t tmem_base_slot;
+
+    const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* ring_ptr = smem_raw + (ring - smem_u32(smem_raw));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const int item = (int)(blockIdx.x >> 1);
+    const int num_kb = plan.num_kb;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+#pragma unroll
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full_bar[b], 1); mbar_init(&acc_empty_bar[b], 16); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 9) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 8) {
+            // ---------------- TMA producer (both CTAs)
+            if (lane == 0) {
+                int it = 0;
+                int tile, cb, ce;
+                for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg) {
+                    int tile_m, tile_n;
+                    la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
+                    const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * BN;
+                    const int kb_end = min(ce * plan.chunk_kb, num_kb);
+                    for (int kb = cb * plan.chunk_kb; kb < kb_end; ++kb, ++it) {
+                        const int s = it % STAGES;
+                        const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+                        mbar_wait(&empty_bar[s], ph ^ 1u);
+                        uint8_t* st = ring_ptr + (size_t)s * F16_STAGE_BYTES;
+                        if (crank == 0) mbar_expect_tx(&full_bar[s], 2u * (3u * F16_PLANE + 3u * HC * F16_BK * 2u));     // my slabs + the peer's
+                        tma_load_2d_2sm(st, &map_a_hi, &full_bar[s], kb * F16_BK, m0);
+                        tma_load_2d_2sm(st + F16_PLANE, &map_a_hb, &full_bar[s], kb * F16_BK, m0);
+                        tma_load_2d_2sm(st + 2 * F16_PLANE, &map_a_lb, &full_bar[s], kb * F16_BK, m0);
+                        tma_load_2d_2sm(st + 3 * F16_PLANE, &map_b_hi, &full_bar[s], kb * F16_BK, n0 + (int)crank * HC);
+                        tma_load_2d_2sm(st + 4 * F16_PLANE, &map_b_hb, &full_bar[s], kb * F16_BK, n0 + (int)crank * HC);
+                        tma_load_2d_2sm(st + 5 * F16_PLANE, &map_b_lb, &full_bar[s], kb * F16_BK, n0 + (int)crank * HC);
+                    }
+                }
+            }
+        } else if (warp == 9 && crank == 0) {
+            // ---------------- MMA issuer (leader CTA only)
+            constexpr uint32_t idesc_f16 = umma_idesc_16(256, BN, 0, 0);
+            int it = 0, cc = 0;
+            int tile, cb, ce;
+            for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg)
+            for (int c = cb; c < ce; ++c, ++cc) {
+                const int b = cc & 1;
+                const uint32_t use = (uint32_t)(cc >> 1);
+                mbar_wait(&acc_empty_bar[b], (use & 1u) ^ 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tmem_d = tmem_base + (uint32_t)(b * 256);
+                int kb = c * plan.chunk_kb;
+                const int kb_end = (kb + plan.chunk_kb < num_kb) ? kb + plan.chunk_kb : num_kb;
+                for (int first = 1; kb < kb_end; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+                    mbar_wait(&full_bar[s], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    if (elect_one()) {
+                        const uint32_t st = ring + (uint32_t)s * F16_STAGE_BYTES;
+                        const uint64_t a_hi = umma_desc_k_sw64(st), a_hb = umma_desc_k_sw64(st + F16_PLANE), a_lb = umma_desc_k_sw64(st + 2 * F16_PLANE);
+                        const uint64_t b_hi = umma_desc_k_sw64(st + 3 * F16_PLANE), b_hb = umma_desc_k_sw64(st + 4 * F16_PLANE), b_lb = umma_desc_k_sw64(st + 5 * F16_PLANE);
+#pragma unroll
+                        for (int kk = 0; kk < F16_BK / 16; ++kk) {               // 16 k = 32 bytes per instruction; same order of terms as the tf32 form
+                            const uint64_t adv = (uint64_t)((kk * 16 * 2) >> 4);
+                            umma_bf16_2sm(tmem_d, a_hb + adv, b_lb + adv, idesc_f16, (first && kk == 0) ? 0u : 1u);       // hs * ls
+                            umma_bf16_2sm(tmem_d, a_lb + adv, b_hb + adv, idesc_f16, 1u);                                  // ls * hs
+                        }
+#pragma unroll
+                        for (int kk = 0; kk < F16_BK / 16; ++kk) {
+                            const uint64_t adv = (uint64_t)((kk * 16 * 2) >> 4);
+                            umma_bf16_2sm(tmem_d, a_hi + adv, b_hi + adv, idesc_f16, 1u);
+                        }
+                        umma_commit_2sm(&empty_bar[s]);
+                        if (kb == kb_end - 1) umma_commit_2sm(&acc_full_bar[b]);
+                    }
+                    __syncwarp();
+                    first = 0;
+                }
+            }
+        }
+    } else {
+        // ---------------- epilogue warps 0..7 (both CTAs; each drains its own tensor memory)
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        const int quad = warp & 3, half = warp >> 2;
+        float acc[HC];
+        int cc = 0;
+        int tile, cb, ce;
+        for (int seg = 0; tc_segment(plan, item, seg, tile, cb, ce); ++seg) {
+#pragma unroll
+        for (int i = 0; i < HC; ++i) acc[i] = 0.f;
+        for (int c = cb; c < ce; ++c, ++cc) {
+            const int b = cc & 1;
+            const uint32_t use = (uint32_t)(cc >> 1);
+            mbar_wait(&acc_full_bar[b], use & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(b * 256 + half * HC);
+#pragma unroll
+            for (int j = 0; j < HC / 64; ++j) {
+                uint32_t v0[32], v1[32];
+                tmem_ld32(taddr + j * 64, v0);
+                tmem_ld32(taddr + j * 64 + 32, v1);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    acc[j * 64 + i] += __uint_as_float(v0[i]);
+                    acc[j * 64 + 32 + i] += __uint_as_float(v1[i]);
+                }
+            }
+            if constexpr (HC % 64 >= 32) {
+                constexpr int o = HC / 64 * 64;
+                uint32_t v0[32];
+                tmem_ld32(taddr + o, v0);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[o + i] += __uint_as_float(v0[i]);
+            }
+            if constexpr (HC % 32 == 16) {
+                constexpr int o = HC / 32 * 32;
+                uint32_t v0[16];
+                tmem_ld16(taddr + o, v0);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 16; ++i) acc[o + i] += __uint_as_float(v0[i]);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive_on_leader(&acc_empty_bar[b]);
+        }
+        int tile_m, tile_n;
+        la_raster_tile(tile, plan.pair_tiles_m, plan.tiles_n, plan.raster_group, tile_m, tile_n);
+        const int m0 = tile_m * 256 + (int)crank * 128, n0 = tile_n * BN;
+        const bool whole = (cb == 0 && ce == plan.num_chunks);
+        const int row = m0 + quad * 32 + lane;
+        if (row < M) {
+            const int er = __ldg(ea + row) + 127;                 // undo the scaling: x 2^(ea[row] + eb[col]), exact
+            float* crow = C + (size_t)row * N + n0 + half * HC;
+#pragma unroll
+            for (int q = 0; q < HC / 4; ++q) {
+                const int n = n0 + half * HC + q * 4;
+                if (n < N) {
+                    const int4 e4 = __ldg(reinterpret_cast<const int4*>(eb + n));
+                    const float4 v = make_float4(acc[q * 4] * __int_as_float((er + e4.x) << 23), acc[q * 4 + 1] * __int_as_float((er + e4.y) << 23),
+                                                 acc[q * 4 + 2] * __int_as_float((er + e4.z) << 23), acc[q * 4 + 3] * __int_as_float((er + e4.w) << 23));
+                    if (whole) __stcs(reinterpret_cast<float4*>(crow + q * 4), v);
+                    else atomicAdd(reinterpret_cast<float4*>(crow + q * 4), v);      // onto zeroed memory (tc_make_plan)
+                }
+            }
+        }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 9) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+    }
+}
+
+// ---- f16-split pre-pass.  Per row of A / column of B: m = max |x|; e = floor(log2 m) - 14, so that m * 2^-e lies in [2^14, 2^15)
+// (fp16's largest finite value is 65504); an all-zero row gets e = 0.  The flag is raised -- and the product then goes to the
+// tf32 form -- for non-finite values and for maxima outside [2^-40, 2^40] (the epilogue's 2^(ea + eb) must stay a normal float).
+// A non-zero element below 2^-8 after scaling (2^-23 of its row's / column's maximum) would lose bits of hs = hi * 2^-6 or of
+// ls = lo * 2^6 to fp16's subnormal range: such elements are left OUT of the planes (zeros) and noted in a list instead -- (row,
+// column, value), at most F16_TINY_CAP per operand, beyond that the flag -- and their products are added afterwards in plain f32
+// by f16_tiny_fix_kernel.  Uniform random data has one such element per 2^23 (8 in an 8192^2 operand); a matrix whose rows mix
+// scales that far apart has many, and goes to the tf32 form.
+// A second flag (word 1) asks for the exact engine: the split leaves an error of up to ~2^-21 |a||b| per PRODUCT (the dropped
+// lo*lo and the rounding of ls), which the gate's 2^-22 sum|a||b| only absorbs when an output is a sum of several comparable
+// products.  An output that is essentially one product -- a diagonal or one-hot operand, a row with one outlier -- is computed
+// exactly by the reference, so rows of A / columns of B with fewer than F16_MIN_COMPARABLE elements within 2^-6 of their maximum
+// send the product to the SIMT engine (for B counted per slice of rows: a sufficient condition).
+constexpr int F16_EXP_TARGET = 14;
+constexpr float F16_KEEP_MIN = 0.00390625f;      // 2^-8
+constexpr unsigned F16_TINY_CAP = 1024;
+constexpr float F16_COMPARABLE = 256.0f;         // 2^8 = 2^-6 of the smallest possible scaled maximum
+constexpr int F16_MIN_COMPARABLE = 16;
+struct F16Tiny { int row, col; float val; int pad; };
+struct F16TinyList { F16Tiny* items; unsigned* count; unsigned* any_host; };      // any_host: mapped host word, set to 1 when the list is not empty
+
+__device__ __forceinline__ int f16_exponent_of_max(float m, bool& bad) {          // m >= 0
+    if (m == 0.0f) return 0;
+    if (!(m >= 9.094947e-13f && m <= 1.0995116e12f)) { bad = true; return 0; }     // outside [2^-40, 2^40] or NaN / inf
+    return (int)((__float_as_uint(m) >> 23) & 0xffu) - 127 - F16_EXP_TARGET;
+}
+// row / col: position in the operand as the product sees it (A: row i, column k; B: row k, column n)
+__device__ __forceinline__ void f16_split_one(float x, float scale, int row, int col, const F16TinyList& tiny, __half& hi, __half& hs, __half& ls, bool& bad) {
+    float xs = x * scale;                                         // exact: a power of two
+    if (fabsf(xs) < F16_KEEP_MIN && x != 0.0f) {                  // noted, not split
+        const unsigned slot = atomicAdd(tiny.count, 1u);
+        if (slot < F16_TINY_CAP) { tiny.items[slot] = F16Tiny{row, col, x, 0}; if (slot == 0) *(volatile unsigned*)tiny.any_host = 1u; }
+        else bad = true;
+        xs = 0.0f;
+    }
+    hi = __float2half_rn(xs);
+    const float h = __half2float(hi);
+    hs = __float2half_rn(h * 0.015625f);                          // hi * 2^-6: exact (|hi| >= 2^-8, or 0)
+    ls = __float2half_rn((xs - h) * 64.0f);                       // (x - hi) * 2^6: at most 2^10, and 11 bits of it survive down to |x| = 2^-8
+    bad |= !(fabsf(x) <= 3.4028235e38f);                          // NaN / inf
+}
+__device__ __forceinline__ uint2 pack_half4(__half a, __half b, __half c, __half d) {
+    const __half2 p0 = __halves2half2(a, b), p1 = __halves2half2(c, d);
+    return make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+}
+struct F16PrepassA { __half* hi; __half* hb; __half* lo; int* ea; const float* A; unsigned rows; size_t K; F16TinyList tiny; };
+struct F16PrepassB { unsigned* colmax_part; const float* B; size_t K, N; unsigned col_blocks, slices; size_t rows_per_slice; unsigned* tiny_count; };
+
+// First launch of the pre-pass.  Blocks 0 .. a.rows-1: one row of A each -- pass 1 finds the row's maximum, pass 2 (the row is in
+// L2 / L1 by then) scales, splits and stores.  The blocks after them (b.col_blocks x b.slices; none when B is prepared): column
+// maxima of B over a slice of its rows, one partial row of maxima per slice (the bits of |x| compare like integers).
+__global__ void __launch_bounds__(256)
+f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
+    __shared__ float red[8];
+    __shared__ float row_scale;
+    __shared__ int row_comparable;
+    bool bad = false;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && b.tiny_count) *b.tiny_count = 0u;      // B's list is filled by the second launch
+    if (blockIdx.x < a.rows) {
+        const size_t row = blockIdx.x, K = a.K;
+        const float4* src = reinterpret_cast<const float4*>(a.A + row * K);
+        const int n4 = (int)(K / 4);
+        float m = 0.f;
+        for (int i = threadIdx.x; i < n4; i += 256) {
+            const float4 v = __ldg(src + i);
+            m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+            if (!(fabsf(v.x) <= 3.4028235e38f) || !(fabsf(v.y) <= 3.4028235e38f) || !(fabsf(v.z) <= 3.4028235e38f) || !(fabsf(v.w) <= 3.4028235e38f)) m = __int_as_float(0x7f800000);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t = red[0];
+#pragma unroll
+            for (int w = 1; w < 8; ++w) t = fmaxf(t, red[w]);
+            const int e = f16_exponent_of_max(t, bad);
+            a.ea[row] = e;
+            row_scale = __int_as_float((127 - e) << 23);
+        }
+        __syncthreads();
+        const float scale = row_scale;
+        int comparable = 0;
+        uint2* hp = reinterpret_cast<uint2*>(a.hi + row * K);
+        uint2* bp = reinterpret_cast<uint2*>(a.hb + row * K);
+        uint2* lp = reinterpret_cast<uint2*>(a.lo + row * K);
+        for (int i = threadIdx.x; i < n4; i += 256) {
+            const float4 v = __ldg(src + i);
+            __half h0, h1, h2, h3, b0, b1, b2, b3, l0, l1, l2, l3;
+            f16_split_one(v.x, scale, (int)row, 4 * i + 0, a.tiny, h0, b0, l0, bad); f16_split_one(v.y, scale, (int)row, 4 * i + 1, a.tiny, h1, b1, l1, bad);
+            f16_split_one(v.z, scale, (int)row, 4 * i + 2, a.tiny, h2, b2, l2, bad); f16_split_one(v.w, scale, (int)row, 4 * i + 3, a.tiny, h3, b3, l3, bad);
+            __stcs(hp + i, pack_half4(h0, h1, h2, h3));
+            __stcs(bp + i, pack_half4(b0, b1, b2, b3));
+            __stcs(lp + i, pack_half4(l0, l1, l2, l3));
+            comparable += (fabsf(v.x * scale) >= F16_COMPARABLE) + (fabsf(v.y * scale) >= F16_COMPARABLE) + (fabsf(v.z * scale) >= F16_COMPARABLE) + (fabsf(v.w * scale) >= F16_COMPARABLE);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) comparable += __shfl_xor_sync(0xffffffffu, comparable, o);
+        if (threadIdx.x == 0) row_comparable = 0;
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0 && comparable) atomicAdd(&row_comparable, comparable);
+        __syncthreads();
+        if (threadIdx.x == 0 && row_comparable > 0 && row_comparable < F16_MIN_COMPARABLE) *(volatile unsigned*)(flag + 1) = 1u;     // (0: an all-zero row)
+    } else {
+        const unsigned c = blockIdx.x - a.rows;
+        const size_t c4 = (size_t)(c % b.col_blocks) * 256 + threadIdx.x;          // float4 column index
+        const unsigned slice = c / b.col_blocks;
+        if (c4 * 4 < b.N) {
+            const size_t k0 = (size_t)slice * b.rows_per_slice, k1 = min(b.K, k0 + b.rows_per_slice);
+            unsigned m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+            size_t k = k0;
+            for (; k + 4 <= k1; k += 4) {                                             // four rows in flight
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = __ldcs(reinterpret_cast<const float4*>(b.B + (k + u) * b.N) + c4);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    m0 = max(m0, __float_as_uint(v[u].x) & 0x7fffffffu); m1 = max(m1, __float_as_uint(v[u].y) & 0x7fffffffu);
+                    m2 = max(m2, __float_as_uint(v[u].z) & 0x7fffffffu); m3 = max(m3, __float_as_uint(v[u].w) & 0x7fffffffu);
+                }
+            }
+            for (; k < k1; ++k) {
+                const float4 v = __ldcs(reinterpret_cast<const float4*>(b.B + k * b.N) + c4);
+                m0 = max(m0, __float_as_uint(v.x) & 0x7fffffffu); m1 = max(m1, __float_as_uint(v.y) & 0x7fffffffu);
+                m2 = max(m2, __float_as_uint(v.z) & 0x7fffffffu); m3 = max(m3, __float_as_uint(v.w) & 0x7fffffffu);
+            }
+            *reinterpret_cast<uint4*>(b.colmax_part + (size_t)slice * b.N + c4 * 4) = make_uint4(m0, m1, m2, m3);
+        }
+    }
+    if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;
+}
+
+// Second launch (not for a prepared B): B (K x N) -> Bt planes (N x K: fp16 hi, bf16 hi, bf16 lo) and eb[N].  64 x 64 tile through
+// shared memory as split_transpose_kernel does; the column exponents come from the partial maxima of the first launch.
+__global__ void __launch_bounds__(256)
+f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_hb, __half* __restrict__ bt_lo, int* __restrict__ eb,
+                           const unsigned* __restrict__ colmax_part, unsigned slices, const float* __restrict__ B, size_t K, size_t N, unsigned tiles_n,
+                           const F16TinyList tiny, unsigned* flag) {
+    __shared__ float tile[64][65];
+    __shared__ float col_scale[64];
+    const size_t k0 = (size_t)(blockIdx.x / tiles_n) * 64, n0 = (size_t)(blockIdx.x % tiles_n) * 64;
+    bool bad = false;
+    float4 in[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
+        in[j] = (k0 + r < K && n0 + q * 4 < N) ? __ldcs(reinterpret_cast<const float4*>(B + (k0 + r) * N + n0 + q * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncwarp();                            // all four loads are issued before anything else
+    if (threadIdx.x < 64) {
+        int e = 0;
+        if (n0 + threadIdx.x < N) {
+            unsigned m = 0;
+            for (unsigned sl = 0; sl < slices; ++sl) m = max(m, colmax_part[(size_t)sl * N + n0 + threadIdx.x]);
+            e = f16_exponent_of_max(__uint_as_float(m), bad);      // (a NaN / inf column maximum has all exponent bits set: flagged)
+            if (k0 == 0) {
+                eb[n0 + threadIdx.x] = e;
+                if (m != 0u && !bad) {                             // slices of rows that hold an element within 2^-6 of the column's scaled 2^14
+                    const float scale_n = __int_as_float((127 - e) << 23);
+                    unsigned with = 0;
+                    for (unsigned sl = 0; sl < slices; ++sl) with += __uint_as_float(colmax_part[(size_t)sl * N + n0 + threadIdx.x]) * scale_n >= F16_COMPARABLE;
+                    if (with < min((unsigned)F16_MIN_COMPARABLE, slices)) *(volatile unsigned*)(flag + 1) = 1u;
+                }
+            }
+        }
+        col_scale[threadIdx.x] = __int_as_float((127 - e) << 23);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int idx = threadIdx.x + j * 256, r = idx / 16, q = idx % 16;
+        tile[r][q * 4 + 0] = in[j].x; tile[r][q * 4 + 1] = in[j].y; tile[r][q * 4 + 2] = in[j].z; tile[r][q * 4 + 3] = in[j].w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int idx = threadIdx.x + j * 256, cc = idx / 16, q = idx % 16;      // Bt row n0+cc, columns k0 + q*4 ..
+        const float scale = col_scale[cc];
+        const int kk = (int)k0 + q * 4, nn = (int)n0 + cc;
+        __half h0, h1, h2, h3, b0, b1, b2, b3, l0, l1, l2, l3;
+        f16_split_one(tile[q * 4 + 0][cc], scale, kk + 0, nn, tiny, h0, b0, l0, bad); f16_split_one(tile[q * 4 + 1][cc], scale, kk + 1, nn, tiny, h1, b1, l1, bad);
+        f16_split_one(tile[q * 4 + 2][cc], scale, kk + 2, nn, tiny, h2, b2, l2, bad); f16_split_one(tile[q * 4 + 3][cc], scale, kk + 3, nn, tiny, h3, b3, l3, bad);
+        if (n0 + cc < N && k0 + q * 4 < K) {
+            const size_t at = (n0 + cc) * K + k0 + q * 4;
+            __stcs(reinterpret_cast<uint2*>(bt_hi + at), pack_half4(h0, h1, h2, h3));
+            __stcs(reinterpret_cast<uint2*>(bt_hb + at), pack_half4(b0, b1, b2, b3));
+            __stcs(reinterpret_cast<uint2*>(bt_lo + at), pack_half4(l0, l1, l2, l3));
+        }
+    }
+    if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;
+}
+
+// The products of the elements the planes left out, added in plain f32 after the product kernel (only launched when the list is
+// not empty; F16_TINY_CAP blocks).  Block e serves the row (ROWS) or column of list entry e -- if e is that row's first entry in
+// the list, otherwise it leaves at once -- and applies ALL of the row's entries in ascending k:
+//   ROWS:  C[i, :] += a * B[k, :]  for every noted (i, k, a) of A
+//   else:  C[:, n] += A[:, k] * b  for every noted (k, n, b) of B, skipping the A elements that are noted themselves (their
+//          products with all of B, noted or not, were added by the row pass, which runs first).
+// One owner per output and a fixed order inside it: reproducible, whatever order the atomics filled the list in.
+template <bool ROWS>
+__global__ void __launch_bounds__(256)
+f16_tiny_fix_kernel(float* __restrict__ C, const float* __restrict__ A, const float* __restrict__ B, const int* __restrict__ ea, size_t M, size_t K, size_t N,
+                    const F16Tiny* __restrict__ items, const unsigned* __restrict__ count_ptr) {
+    __shared__ int sel_k[64];
+    __shared__ float sel_v[64];
+    __shared__ int n_sel, n_match;
+    const unsigned count = min(*count_ptr, F16_TINY_CAP);
+    if (blockIdx.x >= count) return;
+    const int mine = ROWS ? items[blockIdx.x].row : items[blockIdx.x].col;
+    bool earlier = false;
+    for (unsigned e = threadIdx.x; e < blockIdx.x; e += 256) earlier |= (ROWS ? items[e].row : items[e].col) == mine;
+    if (__syncthreads_or(earlier)) return;
+    if (threadIdx.x == 0) { n_sel = 0; n_match = 0; }
+    __syncthreads();
+    for (unsigned e = blockIdx.x + threadIdx.x; e < count; e += 256) {          // this row's entries: usually one or two
+        const F16Tiny t = items[e];
+        if ((ROWS ? t.row : t.col) != mine) continue;
+        atomicAdd(&n_match, 1);
+        const int slot = atomicAdd(&n_sel, 1);
+        if (slot < 64) { sel_k[slot] = ROWS ? t.col : t.row; sel_v[slot] = t.val; }
+    }
+    __syncthreads();
+    const bool many = n_match > 64;                               // (a row with more than 64 noted elements: rounds of 64, picked by k, by one thread)
+    int last_k = -1;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int n = many ? 0 : n_sel;
+            if (many) {
+                for (unsigned e = blockIdx.x; e < count; ++e) {
+                    const F16Tiny t = items[e];
+                    if ((ROWS ? t.row : t.col) != mine) continue;
+                    const int k = ROWS ? t.col : t.row;
+                    if (k <= last_k || (n == 64 && k > sel_k[63])) continue;
+                    int y = (n < 64 ? n : 63) - 1;
+                    for (; y >= 0 && sel_k[y] > k; --y) { sel_k[y + 1] = sel_k[y]; sel_v[y + 1] = sel_v[y]; }
+                    sel_k[y + 1] = k; sel_v[y + 1] = t.val;
+                    if (n < 64) ++n;
+                }
+            } else {
+                for (int x = 1; x < n; ++x) {                    // insertion sort by k
+                    const int kx = sel_k[x]; const float vx = sel_v[x];
+                    int y = x - 1;
+                    for (; y >= 0 && sel_k[y] > kx; --y) { sel_k[y + 1] = sel_k[y]; sel_v[y + 1] = sel_v[y]; }
+                    sel_k[y + 1] = kx; sel_v[y + 1] = vx;
+                }
+            }
+            n_sel = n;
+        }
+        __syncthreads();
+        const int ns = n_sel;
+        if (ns == 0) break;
+        if (ROWS) {
+            for (size_t j = threadIdx.x; j < N; j += 256) {
+                float acc = C[(size_t)mine * N + j];
+                for (int x = 0; x < ns; ++x) acc = fmaf(sel_v[x], B[(size_t)sel_k[x] * N + j], acc);
+                C[(size_t)mine * N + j] = acc;
+            }
+        } else {
+            for (size_t i = threadIdx.x; i < M; i += 256) {
+                float acc = C[i * N + mine];
+                const float undo = __int_as_float((127 - ea[i]) << 23);
+                for (int x = 0; x < ns; ++x) {
+                    const float av = A[i * K + sel_k[x]];
+                    if (!(fabsf(av * undo) < F16_KEEP_MIN && av != 0.0f)) acc = fmaf(av, sel_v[x], acc);
+                }
+                C[i * N + mine] = acc;
+            }
+        }
+        last_k = sel_k[ns - 1];
+        if (!many || ns < 64) break;
+    }
+}
+
 // ------------------------------------------------------------------ pre-pass
 // x -> hi = tf32(x) (round to nearest), lo = tf32(x - hi).  The split is only faithful for finite
 // values away from the ends of the exponent range (an infinity would turn into NaN through
@@ -827,6 +1313,19 @@ la_status tc_make_map_bf16(CUtensorMap* map, const void* base, size_t rows, size
     return LA_OK;
 }
 
+// rows x K row-major 16-bit plane (fp16 or bf16), box = box_rows x 32 (64 bytes), 64-byte swizzle: the f16-split engine's operands
+la_status tc_make_map_16(CUtensorMap* map, const void* base, bool bf16, size_t rows, size_t K, int box_rows) {
+    EncodeTiledFn enc; LA_TRY(tc_get_encode(&enc));
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {(cuuint32_t)F16_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return la_fail(LA_ERR_CUDA, "cuTensorMapEncodeTiled (f16-split planes) failed with CUresult %d", (int)r);
+    return LA_OK;
+}
+
 template <int BN, int STAGES>
 la_status tc_launch(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
     using S = TcShape<BN, STAGES>;
@@ -884,37 +1383,28 @@ static double tc_cost(long long tiles, long long pairs, int bn, bool can_split) 
     return ((double)waves + last) * (double)bn / 256.0;
 }
 
-template <int BN, bool BF16X>
-la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs) {
-    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x;
-    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN / 2));
-    if (BF16X) {        // the lo planes hold [bf16(hi) | bf16(x - hi)]
-        const __nv_bfloat16* a16 = reinterpret_cast<const __nv_bfloat16*>(a_lo); const __nv_bfloat16* b16 = reinterpret_cast<const __nv_bfloat16*>(b_lo);
-        LA_TRY(tc_make_map_bf16(&ma_lo, a16, M, K, 128)); LA_TRY(tc_make_map_bf16(&ma_x, a16 + M * K, M, K, 128));
-        LA_TRY(tc_make_map_bf16(&mb_lo, b16, N, K, BN / 2)); LA_TRY(tc_make_map_bf16(&mb_x, b16 + N * K, N, K, BN / 2));
-    } else {
-        LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, BN / 2));
-        ma_x = ma_lo; mb_x = mb_lo;
-    }
-    auto kern = gemm_3xtf32_2cta_kernel<BN, BF16X>;
-    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
+// Accumulation chains (k-blocks of 32 summed inside the tensor cores before the FP32 registers take over).  The tensor
+// cores' accumulation truncates, and a lone chain is where that shows most (K = 64 as one chain, 16M outputs: 6.5e-7 of
+// sum|a||b| against a bar of 5.9e-7), so short products use chains of 32; over long products the chain errors average
+// out (K = 8192: 4.8e-8 with 64-chains, 6.2e-8 with 128, 9.6e-8 with 256, bar 5.4e-7) and longer chains halve the
+// accumulator drains that otherwise bound the kernel once the cross terms run as bf16 (8192^3: 3.63 -> 3.30 -> 3.28 ms).
+// Round 2, measured over 16M outputs against the unrelaxed gate e <= max(E_reference_order, 2^-22) (tools/short_k_probe.py): with
+// 64-chains K = 256 comes out at 2.9e-7 against the reference order's 3.1 - 3.7e-7 -- inside, but by so little that a
+// smaller problem (512 x 256 x 384) fell 1 % outside by chance; with 32-chains and tf32 cross terms it is 1.4e-7, K = 384
+// 1.2e-7; K = 512 with 64-chains and bf16 cross terms 2.0 - 2.3e-7 (0.83 of the bar on a 1024^2 output), K = 1024 1.5e-7
+// (profiles/r2_short_k_probe.txt).  So products below K = 1024 use chains of 32 (and tf32 cross terms, la_tc_cross_bf16).
+int tc_chunk_kb(size_t K) { return g_tc_chunk > 0 ? g_tc_chunk : K < 1024 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB; }
+
+// Work plan of one product on the CTA-pair kernels (this engine's and the f16-split engine's): tiles of 256 x BN, accumulation
+// chains of `chunk_kb` k-blocks (num_kb k-blocks in all, of the calling engine's k-block size), the K-split of a ragged last
+// wave -- and the zeroing of the part of C that then receives two partial sums.
+la_status tc_make_plan(float* C, size_t M, size_t N, int BN, int num_kb, int chunk_kb, cudaStream_t st, long long pairs, TcPlan* out, long long* out_items) {
     const size_t ptm = (M + 255) / 256, tn = (N + BN - 1) / BN;
     const long long tiles = (long long)(ptm * tn);
-
     TcPlan plan = {};
     plan.pair_tiles_m = (int)ptm; plan.tiles_n = (int)tn; plan.raster_group = la_gemm_raster_group(ptm);
-    plan.num_kb = (int)((K + TC_BK - 1) / TC_BK);
-    // Accumulation chains (k-blocks of 32 summed inside the tensor cores before the FP32 registers take over).  The tensor
-    // cores' accumulation truncates, and a lone chain is where that shows most (K = 64 as one chain, 16M outputs: 6.5e-7 of
-    // sum|a||b| against a bar of 5.9e-7), so short products use chains of 32; over long products the chain errors average
-    // out (K = 8192: 4.8e-8 with 64-chains, 6.2e-8 with 128, 9.6e-8 with 256, bar 5.4e-7) and longer chains halve the
-    // accumulator drains that otherwise bound the kernel once the cross terms run as bf16 (8192^3: 3.63 -> 3.30 -> 3.28 ms).
-    // Round 2, measured over 16M outputs against the unrelaxed gate e <= max(E_reference_order, 2^-22) (tools/short_k_probe.py): with
-    // 64-chains K = 256 comes out at 2.9e-7 against the reference order's 3.1 - 3.7e-7 -- inside, but by so little that a
-    // smaller problem (512 x 256 x 384) fell 1 % outside by chance; with 32-chains and tf32 cross terms it is 1.4e-7, K = 384
-    // 1.2e-7; K = 512 with 64-chains and bf16 cross terms 2.0 - 2.3e-7 (0.83 of the bar on a 1024^2 output), K = 1024 1.5e-7
-    // (profiles/r2_short_k_probe.txt).  So products below K = 1024 use chains of 32 (and tf32 cross terms, la_tc_cross_bf16).
-    plan.chunk_kb = g_tc_chunk > 0 ? g_tc_chunk : K < 1024 ? 1 : K >= 8192 ? 8 : K >= 2048 ? 4 : TC_CHUNK_KB;
+    plan.num_kb = num_kb;
+    plan.chunk_kb = chunk_kb;
     plan.num_chunks = (plan.num_kb + plan.chunk_kb - 1) / plan.chunk_kb;
     plan.dp_items = (int)tiles; plan.stream_items = 0; plan.stream_tiles = 0;
     // Ragged last wave: `waves` full waves and `rest` tiles more.  When the remainder fills at most half of the GPU, each of
@@ -948,19 +1438,50 @@ la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, cons
     long long items = plan.dp_items + plan.stream_items;
     plan.persist = 0;
     if (g_tc_persist != 0 && items > pairs) { plan.persist = (int)pairs; items = pairs; }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(2 * items)); cfg.blockDim = dim3(TC3_THREADS); cfg.dynamicSmemBytes = TC3_SMEM_BYTES; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    *out = plan; *out_items = items;
+    return LA_OK;
+}
+void tc_pair_launch_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, long long items, cudaStream_t st) {
+    *cfg = cudaLaunchConfig_t{};
+    cfg->gridDim = dim3((unsigned)(2 * items)); cfg->blockDim = dim3(TC3_THREADS); cfg->dynamicSmemBytes = TC3_SMEM_BYTES; cfg->stream = st;
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    const bool timed = g_tc_timing && g_tc_timed < 64;
-    if (timed) {
-        if (!g_tc_ev_made) { for (auto& e : g_tc_ev) { LA_CUDA(cudaEventCreate(&e[0])); LA_CUDA(cudaEventCreate(&e[1])); } g_tc_ev_made = true; }
-        LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][0], st));
+    cfg->attrs = attr; cfg->numAttrs = 1;
+}
+// la_gemm_kernel_timing: events around the launch of the product kernel, on its stream
+la_status tc_timing_begin(cudaStream_t st) {
+    if (!(g_tc_timing && g_tc_timed < 64)) return LA_OK;
+    if (!g_tc_ev_made) { for (auto& e : g_tc_ev) { LA_CUDA(cudaEventCreate(&e[0])); LA_CUDA(cudaEventCreate(&e[1])); } g_tc_ev_made = true; }
+    LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][0], st));
+    return LA_OK;
+}
+la_status tc_timing_end(cudaStream_t st) {
+    if (!(g_tc_timing && g_tc_timed < 64)) return LA_OK;
+    LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][1], st)); ++g_tc_timed;
+    return LA_OK;
+}
+
+template <int BN, bool BF16X>
+la_status tc_launch_2cta_bn(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs) {
+    CUtensorMap ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x;
+    LA_TRY(tc_make_map(&ma_hi, a_hi, M, K, 128)); LA_TRY(tc_make_map(&mb_hi, b_hi, N, K, BN / 2));
+    if (BF16X) {        // the lo planes hold [bf16(hi) | bf16(x - hi)]
+        const __nv_bfloat16* a16 = reinterpret_cast<const __nv_bfloat16*>(a_lo); const __nv_bfloat16* b16 = reinterpret_cast<const __nv_bfloat16*>(b_lo);
+        LA_TRY(tc_make_map_bf16(&ma_lo, a16, M, K, 128)); LA_TRY(tc_make_map_bf16(&ma_x, a16 + M * K, M, K, 128));
+        LA_TRY(tc_make_map_bf16(&mb_lo, b16, N, K, BN / 2)); LA_TRY(tc_make_map_bf16(&mb_x, b16 + N * K, N, K, BN / 2));
+    } else {
+        LA_TRY(tc_make_map(&ma_lo, a_lo, M, K, 128)); LA_TRY(tc_make_map(&mb_lo, b_lo, N, K, BN / 2));
+        ma_x = ma_lo; mb_x = mb_lo;
     }
+    TcPlan plan; long long items;
+    LA_TRY(tc_make_plan(C, M, N, BN, (int)((K + TC_BK - 1) / TC_BK), tc_chunk_kb(K), st, pairs, &plan, &items));
+    auto kern = gemm_3xtf32_2cta_kernel<BN, BF16X>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute attr[1];
+    tc_pair_launch_config(&cfg, attr, items, st);
+    LA_TRY(tc_timing_begin(st));
     LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_lo, mb_hi, mb_lo, ma_x, mb_x, (int)M, (int)N, plan));
-    if (timed) { LA_CUDA(cudaEventRecord(g_tc_ev[g_tc_timed][1], st)); ++g_tc_timed; }
+    LA_TRY(tc_timing_end(st));
     return LA_OK;
 }
 
@@ -979,28 +1500,33 @@ int g_tc_cross = -1;            // la_gemm_tc_set_cross: -1 by K, 0 tf32 cross t
 int g_tc_adirect = 0;           // la_gemm_tc_set_a_direct: A's hi plane is A itself (tensor cores truncate), see trunc_tf32
 bool la_tc_cross_bf16(size_t K);
 bool tc_a_direct(size_t K) { return g_tc_adirect != 0 && g_tc_variant == 0 && la_tc_cross_bf16(K); }
+// Round 2, end: bf16 cross terms are a tuning setting only (la_gemm_tc_set_cross(1)).  Their ~2^-20 |a||b| per product is above the
+// gate for an output that is essentially one product (B = identity at K >= 1024: 9.5e-7 of sum|a||b| against a bar of 2.4e-7), and
+// the f16-split form now does the fast path's job at 1.5 units with ~2^-23 per product; this form keeps tf32 cross terms at every K.
 bool la_tc_cross_bf16(size_t K) {
-    if (K % 8 != 0 || g_tc_cross == 0 || g_tc_variant != 0) return false;
-    return g_tc_cross > 0 || K >= 1024;
+    if (K % 8 != 0 || g_tc_variant != 0) return false;
+    return g_tc_cross > 0;
 }
 
+int tc_pick_bn(size_t M, size_t K, size_t N, long long pairs) {
+    if (g_tc_bn) return g_tc_bn;
+    const long long ptm = (long long)((M + 255) / 256);
+    const bool can_split = g_tc_stream != 0 && K > 32;
+    int bn = 256;
+    double best = tc_cost(ptm * (long long)((N + 255) / 256), pairs, 256, can_split);
+    for (int cand : {224, 192}) {
+        const double c = tc_cost(ptm * (long long)((N + cand - 1) / cand), pairs, cand, can_split);
+        if (c < 0.90 * best) { best = c; bn = cand; }       // a 224-wide tile costs ~7 % more per flop (8192^3: 4.86 -> 5.23 ms at equal wave count): it must buy more than that
+    }
+    return bn;
+}
 // Tile width.  256 x 256 per CTA pair unless a narrower tile packs the waves better: the 8-GPU shard of the 8192^3 product,
 // 1024 x 8192 x 8192, is 128 tiles = 1.73 waves -> 2 wave-times at width 256, but 148 tiles = exactly 2 waves of 0.875 at 224
 // (measured 0.666 -> 0.645 ms).
 la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, size_t M, size_t K, size_t N, cudaStream_t st) {
     LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
     const long long pairs = info->sm_count / 2;                 // CTA pairs in flight (one per SM pair)
-    const long long ptm = (long long)((M + 255) / 256);
-    const bool can_split = g_tc_stream != 0 && K > 32;
-    int bn = 256;
-    if (g_tc_bn) bn = g_tc_bn;
-    else {
-        double best = tc_cost(ptm * (long long)((N + 255) / 256), pairs, 256, can_split);
-        for (int cand : {224, 192}) {
-            const double c = tc_cost(ptm * (long long)((N + cand - 1) / cand), pairs, cand, can_split);
-            if (c < 0.90 * best) { best = c; bn = cand; }       // a 224-wide tile costs ~7 % more per flop (8192^3: 4.86 -> 5.23 ms at equal wave count): it must buy more than that
-        }
-    }
+    const int bn = tc_pick_bn(M, K, N, pairs);
     if (la_tc_cross_bf16(K)) {
         switch (bn) {
         case 224: return tc_launch_2cta_bn<224, true>(C, a_hi, a_lo, b_hi, b_lo, M, K, N, st, pairs);
@@ -1016,11 +1542,105 @@ la_status tc_launch_2cta(float* C, const float* a_hi, const float* a_lo, const f
 }
 
 
+// ---- f16-split engine: launch.  Chains: the tf32 form's (tc_chunk_kb).
+int g_tc_f16 = -1;              // la_gemm_tc_set_f16: -1 by K, 0 never, 1 wherever the shapes allow
+thread_local int g_tc_last_form = -1;       // la_gemm_tc_last_form: 0 tf32 form, 1 f16-split form (this thread's last tensor-engine product)
+thread_local int g_tc_last_launches = 0;    // la_gemm_tc_last_launches: kernels that product launched
+struct F16Planes { const __half* hi; const __half* hb; const __half* lb; };      // hi = fp16(x), hs = hi * 2^-11, ls = fp16((x - hi) * 2^11) of a scaled operand
+template <int BN>
+la_status f16_launch_bn(float* C, F16Planes a, F16Planes b, const int* ea, const int* eb, size_t M, size_t K, size_t N, cudaStream_t st, long long pairs) {
+    CUtensorMap ma_hi, ma_hb, ma_lb, mb_hi, mb_hb, mb_lb;
+    LA_TRY(tc_make_map_16(&ma_hi, a.hi, false, M, K, 128)); LA_TRY(tc_make_map_16(&ma_hb, a.hb, false, M, K, 128)); LA_TRY(tc_make_map_16(&ma_lb, a.lb, false, M, K, 128));
+    LA_TRY(tc_make_map_16(&mb_hi, b.hi, false, N, K, BN / 2)); LA_TRY(tc_make_map_16(&mb_hb, b.hb, false, N, K, BN / 2)); LA_TRY(tc_make_map_16(&mb_lb, b.lb, false, N, K, BN / 2));
+    TcPlan plan; long long items;
+    // chains as in the tf32 form from K = 1024; below (tuning only) 64 k: measured 1.3 - 1.6e-7 at K = 256 over 16M outputs against a bar of 3.6 - 4.3e-7
+    const int chunk = (K < 1024 && g_tc_chunk <= 0) ? 2 : tc_chunk_kb(K);
+    LA_TRY(tc_make_plan(C, M, N, BN, (int)((K + F16_BK - 1) / F16_BK), chunk, st, pairs, &plan, &items));
+    auto kern = gemm_f16split_2cta_kernel<BN>;
+    LA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC3_SMEM_BYTES));
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute attr[1];
+    tc_pair_launch_config(&cfg, attr, items, st);
+    LA_TRY(tc_timing_begin(st));
+    LA_CUDA(cudaLaunchKernelEx(&cfg, kern, C, ma_hi, ma_hb, ma_lb, mb_hi, mb_hb, mb_lb, ea, eb, (int)M, (int)N, plan));
+    LA_TRY(tc_timing_end(st));
+    return LA_OK;
+}
+la_status f16_launch(float* C, F16Planes a, F16Planes b, const int* ea, const int* eb, size_t M, size_t K, size_t N, cudaStream_t st) {
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    const long long pairs = info->sm_count / 2;
+    switch (tc_pick_bn(M, K, N, pairs)) {
+    case 224: return f16_launch_bn<224>(C, a, b, ea, eb, M, K, N, st, pairs);
+    case 192: return f16_launch_bn<192>(C, a, b, ea, eb, M, K, N, st, pairs);
+    default:  return f16_launch_bn<256>(C, a, b, ea, eb, M, K, N, st, pairs);
+    }
+}
+// the pre-pass of one operand
+// planes of an operand with `elems` elements in one block: fp16 hi | bf16 hi | bf16 lo
+F16Planes f16_planes(void* base, size_t elems) {
+    F16Planes p; p.hi = (const __half*)base; p.hb = (const __half*)((char*)base + elems * 2); p.lb = (const __half*)((char*)base + elems * 4);
+    return p;
+}
+// Scratch of one operand's pre-pass beyond its planes: exponents, the list of left-out elements, and (B) the partial column maxima.
+struct F16Side { int* e; F16Tiny* items; unsigned* count; unsigned* colmax_part; };
+constexpr unsigned F16_MAX_SLICES = 32;
+size_t f16_side_bytes(size_t n, bool with_colmax) {              // n = M (A) or N (B)
+    const size_t n4 = (n + 3) / 4 * 4;
+    return n4 * sizeof(int) + F16_TINY_CAP * sizeof(F16Tiny) + 16 + (with_colmax ? (size_t)F16_MAX_SLICES * n4 * sizeof(unsigned) : 0);
+}
+F16Side f16_side(char* base, size_t n) {
+    const size_t n4 = (n + 3) / 4 * 4;
+    F16Side s; s.e = (int*)base; s.items = (F16Tiny*)(base + n4 * sizeof(int)); s.count = (unsigned*)(base + n4 * sizeof(int) + F16_TINY_CAP * sizeof(F16Tiny));
+    s.colmax_part = (unsigned*)((char*)s.count + 16);
+    return s;
+}
+// The pre-pass: A's rows and (unless B is prepared: `B == nullptr`) B's column maxima in one launch, then B's transposing split.
+// any_host: two mapped host words, [0] for A's list, [1] for B's.
+la_status f16_prepass(F16Planes a, F16Side sa, const float* A, size_t M, F16Planes bt, F16Side sb, const float* B, size_t K, size_t N,
+                      unsigned* flag, unsigned* any_dev, cudaStream_t st) {
+    LaDeviceInfo* info; LA_TRY(la_ensure_init(&info));
+    F16PrepassA pa = {};
+    F16PrepassB pb = {};
+    if (A) {
+        LA_CUDA(cudaMemsetAsync(sa.count, 0, sizeof(unsigned), st));
+        pa.hi = const_cast<__half*>(a.hi); pa.hb = const_cast<__half*>(a.hb); pa.lo = const_cast<__half*>(a.lb); pa.ea = sa.e; pa.A = A; pa.rows = (unsigned)M; pa.K = K;
+        pa.tiny = F16TinyList{sa.items, sa.count, any_dev};
+    }
+    unsigned b_blocks = 0;
+    if (B) {
+        pb.tiny_count = sb.count;
+        pb.colmax_part = sb.colmax_part; pb.B = B; pb.K = K; pb.N = N;
+        pb.col_blocks = (unsigned)((N / 4 + 255) / 256);
+        size_t slices = std::max<size_t>(1, (size_t)info->sm_count * 8 / pb.col_blocks);
+        slices = std::min<size_t>(std::min<size_t>(slices, F16_MAX_SLICES), K);
+        pb.rows_per_slice = (K + slices - 1) / slices;
+        pb.slices = (unsigned)((K + pb.rows_per_slice - 1) / pb.rows_per_slice);
+        b_blocks = pb.col_blocks * pb.slices;
+    }
+    f16_prepass1_kernel<<<pa.rows + b_blocks, 256, 0, st>>>(pa, pb, flag);
+    LA_LAUNCH_CHECK();
+    if (B) {
+        const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
+        if (tk * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "f16-split pre-pass: B is too large");
+        f16_split_transpose_kernel<<<(unsigned)(tk * tn), 256, 0, st>>>(const_cast<__half*>(bt.hi), const_cast<__half*>(bt.hb), const_cast<__half*>(bt.lb), sb.e,
+                                                                        sb.colmax_part, pb.slices, B, K, N, (unsigned)tn, F16TinyList{sb.items, sb.count, any_dev + 1}, flag);
+        LA_LAUNCH_CHECK();
+    }
+    return LA_OK;
+}
+la_status f16_tiny_fix(float* C, const float* A, const float* B, const int* ea, size_t M, size_t K, size_t N, const F16Side& sa, bool a_any, const F16Tiny* b_items, const unsigned* b_count, bool b_any, cudaStream_t st) {
+    if (a_any) { f16_tiny_fix_kernel<true><<<F16_TINY_CAP, 256, 0, st>>>(C, A, B, ea, M, K, N, sa.items, sa.count); LA_LAUNCH_CHECK(); }
+    if (b_any) { f16_tiny_fix_kernel<false><<<F16_TINY_CAP, 256, 0, st>>>(C, A, B, ea, M, K, N, b_items, b_count); LA_LAUNCH_CHECK(); }
+    return LA_OK;
+}
+
 }  // namespace
 
 bool la_tc_a_direct(size_t K) { return tc_a_direct(K); }      // also asked by gemm_host.cu
 
 extern "C" la_status la_gemm_tc_set_variant(int v) { g_tc_variant = v; return LA_OK; }     // tuning hook
+extern "C" int la_gemm_tc_last_form(void) { return g_tc_last_form; }
+extern "C" int la_gemm_tc_last_launches(void) { return g_tc_last_launches; }
+extern "C" la_status la_gemm_tc_set_f16(int v) { g_tc_f16 = v; return LA_OK; }             // tuning hook: f16-split form (-1 by K, 0 never, 1 wherever the shapes allow)
 // Tile order of the tensor engines.  In m-major order one wave of 74 CTA pairs spans every tile row, so each wave streams
 // all of A's planes from HBM: 8.75 GB of DRAM reads for the 1 GB of operand planes at 8192^3 (ncu), 3.5 TB/s demanded at
 // M = 16384, where the kernel then waits on HBM (16384^3 f32 42.6 ms).  Bands of 8 tile rows keep a wave on ~17 row/column
@@ -1113,10 +1733,53 @@ bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_
              M >= (1u << 31) || N >= (1u << 31) || K >= (1u << 31));
 }
 
+// The f16-split form of the engine: used from K = 1024 (below that its longer pre-pass -- row / column maxima first -- eats what
+// its faster product kernel gains: 4096 x 512 x 4096 cold 0.129 ms against the tf32 form's 0.125), K a multiple of 8 (16-byte row
+// pitch of the 16-bit planes), default pair kernel.  Operands outside its range (see the pre-pass) raise the flag and the
+// product is redone by the tf32 form; operands with one-product outputs raise the other flag and the caller's exact engine runs.
+static bool f16_wanted(size_t K) {
+    if (g_tc_f16 == 0 || g_tc_variant != 0 || K % 8 != 0 || K < LA_TC_AUTO_MIN_K || tc_a_direct(K)) return false;      // (below 256 a product is a chain or two: the SIMT engine's)
+    return g_tc_f16 > 0 || K >= 1024;
+}
+static la_status gemm_f16split(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, bool* exact, const la_gemm_prepared* prep) {
+    *handled = false; *exact = false;
+    const bool b_ready = prep && prep->f16_planes;
+    if (prep && !b_ready) return LA_OK;                      // this B did not pass the f16 range test when it was prepared
+    if (b_ready && prep->f16_b_sparse) { *exact = true; return LA_OK; }
+    const size_t a_elems = M * K, b_elems = b_ready ? 0 : K * N;
+    void* scratch; LA_TRY(la_scratch(st, (a_elems + b_elems) * 6 + f16_side_bytes(M, false) + (b_ready ? 0 : f16_side_bytes(N, true)), &scratch));   // planes | A side | B side
+    volatile unsigned* flag_host; unsigned* flag;
+    LA_TRY(la_host_flag(st, &flag_host, &flag));
+    char* p = (char*)scratch + LA_SCRATCH_ZEROED;
+    const F16Planes a = f16_planes(p, a_elems); p += a_elems * 6;
+    F16Planes b = f16_planes(p, b_elems); p += b_elems * 6;
+    const F16Side sa = f16_side(p, M); p += f16_side_bytes(M, false);
+    F16Side sb = f16_side(p, N);
+    if (b_ready) { b = f16_planes(prep->f16_planes, K * N); sb = f16_side((char*)prep->f16_planes + K * N * 6, N); }
+    flag_host[0] = 0u; flag_host[1] = 0u; flag_host[2] = 0u; flag_host[3] = 0u;     // [0] out of range; [1] exact engine wanted; [2] / [3]: A's / B's list of left-out elements is not empty
+    LA_TRY(f16_prepass(a, sa, A, M, b, sb, b_ready ? nullptr : B, K, N, flag, flag + 2, st));
+    cudaEvent_t split_done; LA_TRY(la_stream_event(st, &split_done));
+    LA_CUDA(cudaEventRecord(split_done, st));
+    LA_TRY(f16_launch(C, a, b, sa.e, sb.e, M, K, N, st));
+    LA_CUDA(cudaEventSynchronize(split_done));
+    if (flag_host[1]) { *exact = true; return LA_OK; }      // (the SIMT engine next in the stream overwrites whatever this launch left in C)
+    if (flag_host[0]) return LA_OK;                          // the tf32 form next in the stream overwrites it
+    const bool a_any = flag_host[2] != 0u, b_any = b_ready ? prep->f16_b_tiny : flag_host[3] != 0u;
+    if (a_any || b_any) LA_TRY(f16_tiny_fix(C, A, B, sa.e, M, K, N, sa, a_any, sb.items, sb.count, b_any, st));
+    g_tc_last_form = 1; g_tc_last_launches = (b_ready ? 2 : 3) + (a_any ? 1 : 0) + (b_any ? 1 : 0);      // pre-pass (1 or 2), product, fix-ups
+    *handled = true;
+    return LA_OK;
+}
+
 // `prep`: planes of B^T made earlier by la_tc_prepare_b (la_gemm_prepare_b), or NULL to split B here.
 la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep) {
     *handled = false;
     if (!la_tc_shape_ok(A, B, C, M, K, N)) return LA_OK;      // the SIMT engine takes it
+    if (f16_wanted(K)) {
+        bool exact = false;
+        LA_TRY(gemm_f16split(C, A, B, M, K, N, st, handled, &exact, prep));
+        if (*handled || exact) return LA_OK;                  // exact: an operand with one-product outputs -- the SIMT engine's (the caller's next choice)
+    }
     if (prep && (!prep->tc_hi || prep->tc_cross_bf16 != la_tc_cross_bf16(K))) prep = nullptr;     // no planes, or made under other tuning settings
     const size_t a_elems = M * K, b_elems = prep ? 0 : K * N;
     void* scratch; LA_TRY(la_scratch(st, (2 * a_elems + 2 * b_elems) * sizeof(float), &scratch));
@@ -1137,6 +1800,7 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
     LA_TRY(la_tc_run(C, la_tc_a_direct(K) ? A : a_hi, a_lo, b_hi, b_lo, M, K, N, st));
     LA_CUDA(cudaEventSynchronize(split_done));
     if (*flag_host) return LA_OK;
+    g_tc_last_form = 0; g_tc_last_launches = 2;                  // pre-pass, product
     *handled = true;
     return LA_OK;
 }
@@ -1154,5 +1818,15 @@ la_status la_tc_prepare_b(la_gemm_prepared* h, cudaStream_t st) {
     if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the split of B failed");
     if (s != LA_OK || *flag_host) { cudaFree(planes); return s; }        // out-of-range B: no planes, not an error
     h->tc_hi = planes; h->tc_lo = planes + K * N; h->tc_cross_bf16 = la_tc_cross_bf16(K);
+    // the f16-split form's planes too, where it applies and B is inside its range (otherwise products with this handle use the tf32 form)
+    if (f16_wanted(K)) {
+        char* f16 = nullptr;
+        LA_CUDA(cudaMalloc(&f16, K * N * 6 + f16_side_bytes(N, true)));
+        flag_host[0] = 0u; flag_host[1] = 0u; flag_host[3] = 0u;
+        s = f16_prepass(F16Planes{}, F16Side{}, nullptr, 0, f16_planes(f16, K * N), f16_side(f16 + K * N * 6, N), (const float*)h->B, K, N, flag, flag + 2, st);
+        if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the f16 split of B failed");
+        if (s != LA_OK || flag_host[0]) { cudaFree(f16); flag_host[0] = 0u; return s; }
+        h->f16_planes = f16; h->f16_b_tiny = flag_host[3] != 0u; h->f16_b_sparse = flag_host[1] != 0u;
+    }
     return LA_OK;
 }

@@ -315,7 +315,108 @@ def test_matmat_3xtf32_leaves_non_finite_and_extreme_operands_to_simt(la):
         a = gen.values("f32", M * K, 47); b = gen.values("f32", K * N, 48)      # clean data: tensor engine again
         la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)
         assert lib.la_gemm_last_engine() == 2
+        # from K = 1024 the f16-split form runs first: it declines the same non-finite / huge values (and so does the tf32 form it
+        # hands over to), but a lone 1e-35 is just an element far below its row's maximum, which it leaves out of its planes and
+        # adds in plain f32 afterwards
+        K = 1024
+        for poison, where in ((np.inf, "a"), (np.nan, "b"), (3e33, "b"), (-np.inf, "b")):
+            a = gen.values("f32", M * K, 45).copy(); b = gen.values("f32", K * N, 46).copy()
+            (a if where == "a" else b)[777] = poison
+            C = (la.Matrix.from_vec(a, M, K) * la.Matrix.from_vec(b, K, N)).to_vec()
+            assert lib.la_gemm_last_engine() in (0, 1), (poison, "tensor engine should have declined")
+            with np.errstate(invalid="ignore", over="ignore"):
+                ref = (a.reshape(M, K).astype(np.float64) @ b.reshape(K, N).astype(np.float64)).reshape(-1)
+            assert np.array_equal(np.isnan(C), np.isnan(ref)) and np.array_equal(np.isinf(C), np.isinf(ref)), poison
+        a = gen.values("f32", M * K, 45).copy(); b = gen.values("f32", K * N, 46).copy()
+        a[777] = 1e-35
+        check_f32_gemm(la, a, b, M, K, N, ("1e-35 among ordinary values", M, K, N))
+        assert lib.la_gemm_last_engine() == 2
     finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
+def test_matmat_f16_split_form_handles_what_its_planes_leave_out(la):
+    """The f16-split form (K >= 1024) scales every row of A / column of B to [2^14, 2^15) and keeps elements 2^-23 and more below
+    their row's / column's maximum out of its fp16 planes; their products are added afterwards in plain f32, one owner per output
+    and in a fixed order.  Inside the gate, reproducible, identical with a prepared B; a list that overflows (more than 1024
+    such elements in an operand) sends the product to the tf32 form."""
+    lib = la._lib.lib; P = oracle.port()
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    try:
+        M, K, N = 384, 1024, 512
+        rng = np.random.default_rng(5)
+        a = rng.standard_normal(M * K).astype(np.float32); b = rng.standard_normal(K * N).astype(np.float32)
+        for idx in rng.integers(0, M * K, 40): a[idx] = np.float32(1e-12) * np.float32(rng.standard_normal())
+        for idx in rng.integers(0, K * N, 40): b[idx] = np.float32(1e-13) * np.float32(rng.standard_normal())
+        a[5 * K + 7] = 1e-12; b[7 * N + 9] = 1e-12                  # a left-out element of A meeting a left-out element of B
+        a[9 * K: 9 * K + 200: 2] = 3e-11                            # a row with 100 of them (more than one round of the fix-up takes)
+        C1 = check_f32_gemm(la, a, b, M, K, N, ("left-out elements", M, K, N))
+        assert lib.la_gemm_last_engine() == 2
+        A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+        assert same(C1, (A * B).to_vec()), "not reproducible"
+        assert same(C1, A.mul_prepared(B.prepare()).to_vec()), "prepared B differs"
+        # rows / columns of very different scales (2^-20 .. 2^20): scaled away exactly
+        a2 = (rng.standard_normal(M * K).astype(np.float32).reshape(M, K) * np.exp2(rng.integers(-20, 20, M)).astype(np.float32)[:, None]).reshape(-1)
+        b2 = (rng.standard_normal(K * N).astype(np.float32).reshape(K, N) * np.exp2(rng.integers(-20, 20, N)).astype(np.float32)[None, :]).reshape(-1)
+        check_f32_gemm(la, a2, b2, M, K, N, ("scaled rows and columns", M, K, N))
+        assert lib.la_gemm_last_engine() == 2
+        # 3000 left-out elements in B: the list overflows, the tf32 form takes over
+        b3 = b.copy(); b3[rng.choice(K * N, 3000, replace=False)] = 1e-14
+        check_f32_gemm(la, a, b3, M, K, N, ("list overflow", M, K, N))
+        # all-zero rows and columns
+        a4 = a.copy().reshape(M, K); a4[3] = 0; b4 = b.copy().reshape(K, N); b4[:, 11] = 0
+        C4 = check_f32_gemm(la, a4.reshape(-1), b4.reshape(-1), M, K, N, ("zero row / column", M, K, N)).reshape(M, N)
+        assert not C4[3].any() and not C4[:, 11].any()
+    finally:
+        la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
+
+
+def test_matmat_one_product_outputs_go_to_the_exact_engine(la):
+    """A split product carries an error of up to ~2^-21 |a||b| per PRODUCT, which the gate only absorbs in a sum of several
+    comparable products.  B = identity / permutation / diagonal, one-hot rows, a row with one outlier: every output is essentially
+    one product, which the reference computes exactly -- and so must we (the f16-split form's pre-pass spots rows of A / columns
+    of B with fewer than 16 elements within 2^-6 of their maximum and hands the product to the SIMT engine)."""
+    lib = la._lib.lib; P = oracle.port()
+    M = K = N = 1024
+    rng = np.random.default_rng(9)
+    a = rng.standard_normal(M * K).astype(np.float32)
+    eye = np.eye(K, dtype=np.float32)
+    cases = {"identity": eye, "signed permutation": eye[rng.permutation(K)] * rng.choice(np.float32([-1.0, 1.0]), K)[:, None],
+             "diagonal": np.diag(rng.standard_normal(K).astype(np.float32))}
+    for name, bm in cases.items():
+        b = np.ascontiguousarray(bm, dtype=np.float32).reshape(-1)
+        for prepared in (False, True):
+            A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
+            C = (A.mul_prepared(B.prepare()) if prepared else A * B).to_vec()
+            assert lib.la_gemm_last_engine() in (0, 1), (name, prepared, "the tensor engine should have declined")
+            assert same(C, P.mul_mat_mat(a, b, M, K, N, fma=True)), (name, prepared)
+    # the same on the left: A = a matrix with one outlier per row
+    a1 = (rng.standard_normal(M * K).astype(np.float32) * np.float32(1e-4)).reshape(M, K); a1[np.arange(M), rng.integers(0, K, M)] = 5.0
+    b1 = rng.standard_normal(K * N).astype(np.float32)
+    C = (la.Matrix.from_vec(a1.reshape(-1), M, K) * la.Matrix.from_vec(b1, K, N)).to_vec()
+    assert lib.la_gemm_last_engine() in (0, 1)
+    assert same(C, P.mul_mat_mat(a1.reshape(-1), b1, M, K, N, fma=True))
+
+
+def test_matmat_tf32_form_still_meets_the_bar_from_k_1024(la):
+    """la_gemm_tc_set_f16(0): the tf32 form alone (what K % 8 != 0, out-of-range operands and the host-buffer product use), tf32
+    cross terms at every K; and the f16-split form forced below K = 1024 (a tuning setting: AUTO keeps the tf32 form there)."""
+    lib = la._lib.lib
+    la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
+    try:
+        lib.la_gemm_tc_set_f16(0)
+        for M, K, N in ((512, 1024, 384), (388, 2052, 260), (256, 8192, 512)):
+            check_f32_gemm(la, gen.values("f32", M * K, 81), gen.values("f32", K * N, 82), M, K, N, ("tf32 form", M, K, N))
+            assert lib.la_gemm_last_engine() == 2
+        lib.la_gemm_tc_set_f16(-1)
+        M, K, N = 388, 1028, 260                                  # K % 8 != 0: the tf32 form by default
+        check_f32_gemm(la, gen.values("f32", M * K, 83), gen.values("f32", K * N, 84), M, K, N, ("K % 8 != 0", M, K, N))
+        lib.la_gemm_tc_set_f16(1)
+        for M, K, N in ((512, 256, 384), (1024, 512, 1024), (388, 264, 260), (2048, 256, 2048)):
+            check_f32_gemm(la, gen.values("f32", M * K, 85), gen.values("f32", K * N, 86), M, K, N, ("f16-split form, short K", M, K, N))
+            assert lib.la_gemm_last_engine() == 2
+    finally:
+        lib.la_gemm_tc_set_f16(-1)
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
@@ -583,7 +684,7 @@ def test_matmat_tensor_engine_cross_terms_and_chain_lengths_meet_the_bar(la, cro
     f32 gate on short and long products."""
     lib = la._lib.lib
     la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
-    lib.la_gemm_tc_set_cross(cross)
+    lib.la_gemm_tc_set_cross(cross); lib.la_gemm_tc_set_f16(0)          # the tf32 form (from K = 1024 the f16-split form would run instead)
     try:
         for M, K, N in ((256, 64, 256), (512, 256, 384), (388, 1000, 260), (1024, 2048, 512), (512, 4096, 768)):
             # a forced chain length only where it leaves at least 8 chains: the truncating accumulation inside one chain is
@@ -596,7 +697,7 @@ def test_matmat_tensor_engine_cross_terms_and_chain_lengths_meet_the_bar(la, cro
             check_f32_gemm(la, gen.values("f32", M * K, 71), gen.values("f32", K * N, 72), M, K, N, ("cross", cross, "chunk", chunk, M, K, N), factor)
             assert lib.la_gemm_last_engine() == 2
     finally:
-        lib.la_gemm_tc_set_cross(-1); lib.la_gemm_tc_set_chunk(0)
+        lib.la_gemm_tc_set_cross(-1); lib.la_gemm_tc_set_chunk(0); lib.la_gemm_tc_set_f16(-1)
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 
@@ -666,7 +767,7 @@ def test_matmat_tensor_engine_a_read_in_place_stays_inside_the_gate(la):
     (K >= 1024); below that the flag has no effect.  The prepared-B path must agree with the direct call bit for bit."""
     lib = la._lib.lib
     la._lib.call("la_set_gemm_mode", la._lib.GEMM_3XTF32)
-    lib.la_gemm_tc_set_a_direct(1)
+    lib.la_gemm_tc_set_a_direct(1); lib.la_gemm_tc_set_f16(0); lib.la_gemm_tc_set_cross(1)      # the tf32 form with bf16 cross terms: both tuning settings now
     try:
         for M, K, N in ((512, 1024, 384), (388, 2052, 260), (256, 4096, 512)):
             a = gen.values("f32", M * K, 73); b = gen.values("f32", K * N, 74)
@@ -675,13 +776,14 @@ def test_matmat_tensor_engine_a_read_in_place_stays_inside_the_gate(la):
             A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
             assert same((A * B).to_vec(), A.mul_prepared(B.prepare()).to_vec()), (M, K, N)
         M, K, N = 512, 256, 384                       # tf32 cross terms: the flag changes nothing
+        lib.la_gemm_tc_set_cross(-1)
         a = gen.values("f32", M * K, 75); b = gen.values("f32", K * N, 76)
         A = la.Matrix.from_vec(a, M, K); B = la.Matrix.from_vec(b, K, N)
         with_flag = (A * B).to_vec()
         lib.la_gemm_tc_set_a_direct(0)
         assert same(with_flag, (A * B).to_vec())
     finally:
-        lib.la_gemm_tc_set_a_direct(0)
+        lib.la_gemm_tc_set_a_direct(0); lib.la_gemm_tc_set_f16(-1); lib.la_gemm_tc_set_cross(-1)
         la._lib.call("la_set_gemm_mode", la._lib.GEMM_AUTO)
 
 

@@ -984,6 +984,7 @@ f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_h
                            const F16TinyList tiny, unsigned* flag) {
     __shared__ float tile[64][65];
     __shared__ float col_scale[64];
+    __shared__ unsigned part_max[4][64];
     const size_t k0 = (size_t)(blockIdx.x / tiles_n) * 64, n0 = (size_t)(blockIdx.x % tiles_n) * 64;
     bool bad = false;
     float4 in[4];
@@ -993,23 +994,29 @@ f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_h
         in[j] = (k0 + r < K && n0 + q * 4 < N) ? __ldcs(reinterpret_cast<const float4*>(B + (k0 + r) * N + n0 + q * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     __syncwarp();                            // all four loads are issued before anything else
-    if (threadIdx.x < 64) {
+    {   // this tile's 64 column exponents from the partial maxima: four threads per column, a quarter of the slices each
+        const int c = threadIdx.x & 63, g = threadIdx.x >> 6;
+        const bool col_ok = n0 + c < N;
+        unsigned m = 0;
+        if (col_ok) for (unsigned sl = g; sl < slices; sl += 4) m = max(m, colmax_part[(size_t)sl * N + n0 + c]);
+        part_max[g][c] = m;
+        __syncthreads();
+        m = max(max(part_max[0][c], part_max[1][c]), max(part_max[2][c], part_max[3][c]));
         int e = 0;
-        if (n0 + threadIdx.x < N) {
-            unsigned m = 0;
-            for (unsigned sl = 0; sl < slices; ++sl) m = max(m, colmax_part[(size_t)sl * N + n0 + threadIdx.x]);
-            e = f16_exponent_of_max(__uint_as_float(m), bad);      // (a NaN / inf column maximum has all exponent bits set: flagged)
-            if (k0 == 0) {
-                eb[n0 + threadIdx.x] = e;
-                if (m != 0u && !bad) {                             // slices of rows that hold an element within 2^-6 of the column's scaled 2^14
-                    const float scale_n = __int_as_float((127 - e) << 23);
-                    unsigned with = 0;
-                    for (unsigned sl = 0; sl < slices; ++sl) with += __uint_as_float(colmax_part[(size_t)sl * N + n0 + threadIdx.x]) * scale_n >= F16_COMPARABLE;
-                    if (with < min((unsigned)F16_MIN_COMPARABLE, slices)) *(volatile unsigned*)(flag + 1) = 1u;
-                }
-            }
+        bool col_bad = false;
+        if (col_ok) e = f16_exponent_of_max(__uint_as_float(m), col_bad);      // (a NaN / inf column maximum has all exponent bits set: flagged)
+        bad |= col_bad;
+        const float scale_n = __int_as_float((127 - e) << 23);
+        if (g == 0) { col_scale[c] = scale_n; if (k0 == 0 && col_ok) eb[n0 + c] = e; }
+        if (k0 == 0) {                       // (once per column) slices of rows that hold an element within 2^-6 of the column's scaled 2^14
+            unsigned with = 0;
+            if (col_ok && m != 0u && !col_bad) for (unsigned sl = g; sl < slices; sl += 4) with += __uint_as_float(colmax_part[(size_t)sl * N + n0 + c]) * scale_n >= F16_COMPARABLE;
+            __syncthreads();
+            part_max[g][c] = with;
+            __syncthreads();
+            if (g == 0 && col_ok && m != 0u && !col_bad &&
+                part_max[0][c] + part_max[1][c] + part_max[2][c] + part_max[3][c] < min((unsigned)F16_MIN_COMPARABLE, slices)) *(volatile unsigned*)(flag + 1) = 1u;
         }
-        col_scale[threadIdx.x] = __int_as_float((127 - e) << 23);
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -1036,7 +1043,7 @@ f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_h
 }
 
 // The products of the elements the planes left out, added in plain f32 after the product kernel (only launched when the list is
-// not empty; F16_TINY_CAP blocks).  Block e serves the row (ROWS) or column of list entry e -- if e is that row's first entry in
+// not empty; F16_TINY_CAP x ceil(outputs / 1024) blocks).  Block (e, y) serves 1024 outputs of the row (ROWS) or column of list entry e -- if e is that row's first entry in
 // the list, otherwise it leaves at once -- and applies ALL of the row's entries in ascending k:
 //   ROWS:  C[i, :] += a * B[k, :]  for every noted (i, k, a) of A
 //   else:  C[:, n] += A[:, k] * b  for every noted (k, n, b) of B, skipping the A elements that are noted themselves (their
@@ -1095,22 +1102,34 @@ f16_tiny_fix_kernel(float* __restrict__ C, const float* __restrict__ A, const fl
         __syncthreads();
         const int ns = n_sel;
         if (ns == 0) break;
+        // this block's 1024 outputs of the row / column (blockIdx.y), four per thread, their loads issued together
+        const size_t o0 = (size_t)blockIdx.y * 1024 + threadIdx.x;
+        float acc[4];
         if (ROWS) {
-            for (size_t j = threadIdx.x; j < N; j += 256) {
-                float acc = C[(size_t)mine * N + j];
-                for (int x = 0; x < ns; ++x) acc = fmaf(sel_v[x], B[(size_t)sel_k[x] * N + j], acc);
-                C[(size_t)mine * N + j] = acc;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const size_t j = o0 + 256 * u; acc[u] = j < N ? C[(size_t)mine * N + j] : 0.f; }
+            for (int x = 0; x < ns; ++x) {
+                float bv[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { const size_t j = o0 + 256 * u; bv[u] = j < N ? B[(size_t)sel_k[x] * N + j] : 0.f; }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) acc[u] = fmaf(sel_v[x], bv[u], acc[u]);
             }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const size_t j = o0 + 256 * u; if (j < N) C[(size_t)mine * N + j] = acc[u]; }
         } else {
-            for (size_t i = threadIdx.x; i < M; i += 256) {
-                float acc = C[i * N + mine];
-                const float undo = __int_as_float((127 - ea[i]) << 23);
-                for (int x = 0; x < ns; ++x) {
-                    const float av = A[i * K + sel_k[x]];
-                    if (!(fabsf(av * undo) < F16_KEEP_MIN && av != 0.0f)) acc = fmaf(av, sel_v[x], acc);
-                }
-                C[i * N + mine] = acc;
+            float undo[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const size_t i = o0 + 256 * u; acc[u] = i < M ? C[i * N + mine] : 0.f; undo[u] = i < M ? __int_as_float((127 - ea[i]) << 23) : 0.f; }
+            for (int x = 0; x < ns; ++x) {
+                float av[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { const size_t i = o0 + 256 * u; av[u] = i < M ? A[i * K + sel_k[x]] : 0.f; }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) if (!(fabsf(av[u] * undo[u]) < F16_KEEP_MIN && av[u] != 0.0f)) acc[u] = fmaf(av[u], sel_v[x], acc[u]);
             }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const size_t i = o0 + 256 * u; if (i < M) C[i * N + mine] = acc[u]; }
         }
         last_k = sel_k[ns - 1];
         if (!many || ns < 64) break;
@@ -1628,8 +1647,8 @@ la_status f16_prepass(F16Planes a, F16Side sa, const float* A, size_t M, F16Plan
     return LA_OK;
 }
 la_status f16_tiny_fix(float* C, const float* A, const float* B, const int* ea, size_t M, size_t K, size_t N, const F16Side& sa, bool a_any, const F16Tiny* b_items, const unsigned* b_count, bool b_any, cudaStream_t st) {
-    if (a_any) { f16_tiny_fix_kernel<true><<<F16_TINY_CAP, 256, 0, st>>>(C, A, B, ea, M, K, N, sa.items, sa.count); LA_LAUNCH_CHECK(); }
-    if (b_any) { f16_tiny_fix_kernel<false><<<F16_TINY_CAP, 256, 0, st>>>(C, A, B, ea, M, K, N, b_items, b_count); LA_LAUNCH_CHECK(); }
+    if (a_any) { f16_tiny_fix_kernel<true><<<dim3(F16_TINY_CAP, (unsigned)((N + 1023) / 1024)), 256, 0, st>>>(C, A, B, ea, M, K, N, sa.items, sa.count); LA_LAUNCH_CHECK(); }
+    if (b_any) { f16_tiny_fix_kernel<false><<<dim3(F16_TINY_CAP, (unsigned)((M + 1023) / 1024)), 256, 0, st>>>(C, A, B, ea, M, K, N, b_items, b_count); LA_LAUNCH_CHECK(); }
     return LA_OK;
 }
 
@@ -1746,6 +1765,7 @@ static la_status gemm_f16split(float* C, const float* A, const float* B, size_t 
     const bool b_ready = prep && prep->f16_planes;
     if (prep && !b_ready) return LA_OK;                      // this B did not pass the f16 range test when it was prepared
     if (b_ready && prep->f16_b_sparse) { *exact = true; return LA_OK; }
+    if (M > 65535ull * 1024 || N > 65535ull * 1024) return LA_OK;      // (the fix-up kernels' grid: the tf32 form takes such shapes)
     const size_t a_elems = M * K, b_elems = b_ready ? 0 : K * N;
     void* scratch; LA_TRY(la_scratch(st, (a_elems + b_elems) * 6 + f16_side_bytes(M, false) + (b_ready ? 0 : f16_side_bytes(N, true)), &scratch));   // planes | A side | B side
     volatile unsigned* flag_host; unsigned* flag;

@@ -259,13 +259,13 @@ la_status la_mul_mat_mat_info(int dtype, void* C, const void* A, const void* B, 
 
 /* One B, many products (no counterpart in the reference, whose kernel reads B as it is; SURVEY.md section 8(e): the
  * row-block sharded product keeps B replicated on every GPU, "broadcast once").  Part of what a product does is work on B
- * alone: the tensor engines read B transposed and split into planes (f32: tf32 + bf16 planes of B^T; 8/16/32-bit
- * integers: byte planes of B^T).  la_gemm_prepare_b does that once and keeps the result in a handle;
+ * alone: the tensor engines read B transposed and split into planes (f32: tf32 planes of B^T and, from K = 1024, the
+ * fp16 planes of the column-scaled B^T; 8/16/32-bit integers: byte planes of B^T).  la_gemm_prepare_b does that once and keeps the result in a handle;
  * la_mul_mat_mat_prepared(C, A, handle, M) is then la_mul_mat_mat(dtype, C, A, B, M, K, N) without that part: same engine
  * selection, same kernels, bit-identical results.  Where no tensor engine applies (f64, 64-bit integers, small or ragged
  * shapes, LA_GEMM_SIMT, a B with NaN / inf / extreme exponents) the handle holds nothing extra and the product reads B
  * itself.  B must stay allocated and unchanged while the handle lives (the handle keeps the pointer, not a copy).
- * la_gemm_prepare_b allocates device memory for the planes (f32: 8 bytes per element of B, integers: sizeof(T)) and
+ * la_gemm_prepare_b allocates device memory for the planes (f32: 8, from K = 1024 14 bytes per element of B; integers: sizeof(T)) and
  * returns when they are complete; la_gemm_prepared_free waits for the device before releasing them.  A handle belongs
  * to the device it was made on and may be used from any stream and thread (it is read-only after creation). */
 typedef struct la_gemm_prepared la_gemm_prepared;
@@ -285,14 +285,19 @@ la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const
 /* f32 GEMM engine.
  *  LA_GEMM_SIMT    FP32 FMA pipe, each element accumulated k-ascending with one fused multiply-add
  *                  per k: the reference's own order (src/kernels.cl:136-138).
- *  LA_GEMM_3XTF32  tcgen05 tensor cores: every operand split x = hi + lo (hi = tf32(x)); a product is hi*hi + hi*lo + lo*hi:
- *                  three tf32 MMAs below K = 1024; from there hi*hi as a tf32 MMA and the two cross terms (2^-11 of
- *                  the weight) as bf16 MMAs at twice the rate,
+ *  LA_GEMM_3XTF32  tcgen05 tensor cores: every operand split x = hi + lo with an 11-bit hi; a product is hi*hi + hi*lo + lo*hi.
+ *                  Below K = 1024 hi = tf32(x) and the three terms are tf32 MMAs.  From K = 1024 (K % 8 == 0) rows of A and
+ *                  columns of B are scaled by powers of two (undone exactly at the end), hi = fp16(x), the residual is lifted
+ *                  by 2^6 into fp16 as well, and the three terms are fp16 MMAs at twice the tf32 rate; elements 2^-23 and
+ *                  more below their row's / column's maximum are left out of the planes and added afterwards in plain f32.
  *                  FP32 accumulation in chunks (32 k below K = 1024, 64 below K = 2048, 128 below 8192, 256 from
  *                  there; meets the same f32 tolerance as the SIMT
  *                  engine).  Falls back to SIMT for shapes it does not cover
- *                  (M, N >= 128, K >= 32, all multiples of 4) and whenever an operand holds a NaN, an
- *                  infinity or a magnitude outside [2^-100, 2^100] (the call reads one flag back, so the
+ *                  (M, N >= 128, K >= 32, all multiples of 4), whenever an operand holds a NaN, an
+ *                  infinity or a magnitude outside [2^-100, 2^100], and (from K = 1024) when a row of A or a column of B
+ *                  has fewer than 16 elements within 2^-6 of its maximum -- identity, permutation, diagonal, one-hot
+ *                  operands: outputs that are essentially one product, which only the exact engine computes as accurately
+ *                  as the reference does (the call reads one flag back, so the
  *                  HOST blocks for the length of the pre-pass; the product itself is already queued behind
  *                  the pre-pass, so the GPU does not idle meanwhile).
  *  LA_GEMM_AUTO    (default) LA_GEMM_3XTF32 for products of at least 512^3 multiply-adds (where it overtakes the SIMT

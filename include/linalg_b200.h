@@ -276,7 +276,7 @@ la_status la_gemm_prepared_free(la_gemm_prepared* handle);
 /* The reference user's whole sequence -- Matrix::from_vec(a) * Matrix::from_vec(b), then to_vec()
  * (src/matrix.rs:39-46, 221-265, src/vector.rs:53-78) -- as one call on HOST buffers: B is uploaded
  * once, A and C stream through in row blocks on separate copy streams so uploads, multiplies and
- * downloads overlap.  Same results as la_mul_mat_mat.  Blocks until C_host is complete; pinned host
+ * downloads overlap.  Same engines and the same gate as la_mul_mat_mat (integers: the same bits).  Blocks until C_host is complete; pinned host
  * buffers (la_host_alloc) give full PCIe rate, pageable ones work; any of the three may also be a
  * device pointer (e.g. a B that is already resident).  Calls on the same device run one at a time
  * (a second caller waits): they share one set of copy streams and one range-flag word. */

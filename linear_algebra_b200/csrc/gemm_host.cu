@@ -22,6 +22,11 @@ la_status la_tc_split_bt(float* bt_hi, float* bt_lo, const float* B, size_t K, s
 la_status la_tc_run(float* C, const float* a_hi, const float* a_lo, const float* bt_hi, const float* bt_lo, size_t M, size_t K, size_t N, cudaStream_t st);
 bool la_tc_shape_ok(const void* A, const void* B, const void* C, size_t M, size_t K, size_t N);
 bool la_tc_a_direct(size_t K);
+bool la_f16_wanted(size_t K);                          // the f16-split form of the f32 tensor engine, in pieces (gemm_tc.cu)
+size_t la_f16_b_bytes(size_t K, size_t N);
+size_t la_f16_a_bytes(size_t rows, size_t K);
+la_status la_f16_split_b(void* b_block, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st);
+la_status la_f16_block(float* C, const float* A, const float* B, size_t rows, size_t K, size_t N, void* a_block, void* b_block, unsigned* flag, cudaStream_t st);
 
 namespace {
 
@@ -108,11 +113,17 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     bool tensor = want_tensor && la_tc_shape_ok(Ab[0], Bp, Cb[0], rb, K, N);
     float* ah[2] = {nullptr, nullptr}; float* al[2] = {nullptr, nullptr};
     volatile unsigned* flag_host = nullptr; unsigned* flag = nullptr;
+    const bool f16 = tensor && la_f16_wanted(K);           // the f16-split form (from K = 1024), else the tf32 form: la_mul_mat_mat's choice
     if (tensor) {
         LA_TRY(la_host_flag(hs->cmp, &flag_host, &flag));
-        *flag_host = 0u;
-        LA_TRY(bt_hi.alloc(K * N * 4)); LA_TRY(bt_lo.alloc(K * N * 4));
-        LA_TRY(a_hi0.alloc(rb * K * 4)); LA_TRY(a_lo0.alloc(rb * K * 4)); LA_TRY(a_hi1.alloc(rb * K * 4)); LA_TRY(a_lo1.alloc(rb * K * 4));
+        flag_host[0] = 0u; flag_host[1] = 0u;
+        if (f16) {
+            LA_TRY(bt_hi.alloc(la_f16_b_bytes(K, N)));
+            LA_TRY(a_hi0.alloc(la_f16_a_bytes(rb, K))); LA_TRY(a_hi1.alloc(la_f16_a_bytes(rb, K)));
+        } else {
+            LA_TRY(bt_hi.alloc(K * N * 4)); LA_TRY(bt_lo.alloc(K * N * 4));
+            LA_TRY(a_hi0.alloc(rb * K * 4)); LA_TRY(a_lo0.alloc(rb * K * 4)); LA_TRY(a_hi1.alloc(rb * K * 4)); LA_TRY(a_lo1.alloc(rb * K * 4));
+        }
         ah[0] = (float*)a_hi0.p; al[0] = (float*)a_lo0.p; ah[1] = (float*)a_hi1.p; al[1] = (float*)a_lo1.p;
     }
     // the copy streams may touch the buffers only after the (stream-ordered) allocations exist
@@ -127,7 +138,8 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
         LA_CUDA(cudaEventRecord(hs->b_up, hs->in));
         LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->b_up, 0));
     }
-    if (tensor) LA_TRY(la_tc_split_bt((float*)bt_hi.p, (float*)bt_lo.p, (const float*)Bp, K, N, flag, hs->cmp));
+    if (f16) LA_TRY(la_f16_split_b(bt_hi.p, (const float*)Bp, K, N, flag, hs->cmp));
+    else if (tensor) LA_TRY(la_tc_split_bt((float*)bt_hi.p, (float*)bt_lo.p, (const float*)Bp, K, N, flag, hs->cmp));
     if (dbg) fprintf(stderr, "[hostgemm] setup enqueued at %.3f ms (tensor=%d rb=%zu nblocks=%zu)\n", ms_since(), (int)tensor, rb, nblocks);
 
     for (size_t i = 0; i < nblocks; ++i) {
@@ -142,7 +154,9 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
         if (i >= 2) LA_CUDA(cudaStreamWaitEvent(hs->cmp, hs->out_done[b], 0));
         // The range check of the split is read back once, after everything is queued: no host
         // wait inside the pipeline.  (If it trips, the whole product is redone in plain f32.)
-        if (tensor && rows >= 128 && rows % 4 == 0) {
+        if (f16 && rows >= 128 && rows % 4 == 0) {
+            LA_TRY(la_f16_block((float*)Cb[b], (const float*)Ab[b], (const float*)Bp, rows, K, N, ah[b], bt_hi.p, flag, hs->cmp));
+        } else if (tensor && rows >= 128 && rows % 4 == 0) {
             LA_TRY(la_tc_split_a(ah[b], al[b], (const float*)Ab[b], rows, K, flag, hs->cmp));
             LA_TRY(la_tc_run((float*)Cb[b], la_tc_a_direct(K) ? (const float*)Ab[b] : ah[b], al[b], (const float*)bt_hi.p, (const float*)bt_lo.p, rows, K, N, hs->cmp));
         } else {
@@ -161,7 +175,9 @@ static la_status host_gemm_pass(int dtype, void* C_host, const void* A_host, con
     if (dbg) fprintf(stderr, "[hostgemm] out drained at %.3f ms\n", ms_since());
     LA_CUDA(cudaStreamSynchronize(hs->in));
     LA_CUDA(cudaStreamSynchronize(hs->cmp));
-    if (tensor && *flag_host) *redo = true;      // an operand the tf32 split cannot represent (inf, NaN, extreme exponent)
+    // an operand the split cannot represent (inf, NaN, extreme exponents or scales) or, f16 form, one with one-product outputs:
+    // the whole product again on the SIMT engine
+    if (tensor && (flag_host[0] || (f16 && flag_host[1]))) *redo = true;
     return LA_OK;
 }
 

@@ -1791,6 +1791,23 @@ static la_status gemm_f16split(float* C, const float* A, const float* B, size_t 
     return LA_OK;
 }
 
+// The f16-split form in pieces, for the streamed host-buffer product (gemm_host.cu): B's block once, then per row block of A its
+// pre-pass, the product and the fix-ups -- the latter launched unconditionally (they leave at once when the lists are empty), so
+// that the pipeline never waits for the host to read a word.  `flag`: [0] out of range, [1] exact engine wanted; read at the end.
+bool la_f16_wanted(size_t K) { return f16_wanted(K); }
+size_t la_f16_b_bytes(size_t K, size_t N) { return K * N * 6 + f16_side_bytes(N, true); }
+size_t la_f16_a_bytes(size_t rows, size_t K) { return rows * K * 6 + f16_side_bytes(rows, false); }
+la_status la_f16_split_b(void* b_block, const float* B, size_t K, size_t N, unsigned* flag, cudaStream_t st) {
+    return f16_prepass(F16Planes{}, F16Side{}, nullptr, 0, f16_planes(b_block, K * N), f16_side((char*)b_block + K * N * 6, N), B, K, N, flag, flag + 2, st);
+}
+la_status la_f16_block(float* C, const float* A, const float* B, size_t rows, size_t K, size_t N, void* a_block, void* b_block, unsigned* flag, cudaStream_t st) {
+    const F16Planes a = f16_planes(a_block, rows * K), b = f16_planes(b_block, K * N);
+    const F16Side sa = f16_side((char*)a_block + rows * K * 6, rows), sb = f16_side((char*)b_block + K * N * 6, N);
+    LA_TRY(f16_prepass(a, sa, A, rows, F16Planes{}, F16Side{}, nullptr, K, N, flag, flag + 2, st));
+    LA_TRY(f16_launch(C, a, b, sa.e, sb.e, rows, K, N, st));
+    return f16_tiny_fix(C, A, B, sa.e, rows, K, N, sa, true, sb.items, sb.count, true, st);
+}
+
 // `prep`: planes of B^T made earlier by la_tc_prepare_b (la_gemm_prepare_b), or NULL to split B here.
 la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, size_t K, size_t N, cudaStream_t st, bool* handled, const la_gemm_prepared* prep) {
     *handled = false;

@@ -265,7 +265,7 @@ la_status la_mul_mat_mat_info(int dtype, void* C, const void* A, const void* B, 
  * selection, same kernels, bit-identical results.  Where no tensor engine applies (f64, 64-bit integers, small or ragged
  * shapes, LA_GEMM_SIMT, a B with NaN / inf / extreme exponents) the handle holds nothing extra and the product reads B
  * itself.  B must stay allocated and unchanged while the handle lives (the handle keeps the pointer, not a copy).
- * la_gemm_prepare_b allocates device memory for the planes (f32: 8, from K = 1024 14 bytes per element of B; integers: sizeof(T)) and
+ * la_gemm_prepare_b allocates device memory for the planes (f32: 8, from K = 1024 6 bytes per element of B; integers: sizeof(T)) and
  * returns when they are complete; la_gemm_prepared_free waits for the device before releasing them.  A handle belongs
  * to the device it was made on and may be used from any stream and thread (it is read-only after creation). */
 typedef struct la_gemm_prepared la_gemm_prepared;

@@ -1847,23 +1847,26 @@ la_status la_gemm_3xtf32(float* C, const float* A, const float* B, size_t M, siz
 la_status la_tc_prepare_b(la_gemm_prepared* h, cudaStream_t st) {
     const size_t K = h->K, N = h->N;
     if (N < 128 || K < 32 || K % 4 != 0 || N % 4 != 0 || !la_aligned16(h->B) || N >= (1u << 31) || K >= (1u << 31)) return LA_OK;
-    float* planes = nullptr;
-    LA_CUDA(cudaMalloc(&planes, 2 * K * N * sizeof(float)));
     volatile unsigned* flag_host; unsigned* flag;
-    la_status s = la_host_flag(st, &flag_host, &flag);
-    if (s == LA_OK) { *flag_host = 0u; s = la_tc_split_bt(planes, planes + K * N, (const float*)h->B, K, N, flag, st); }
-    if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the split of B failed");
-    if (s != LA_OK || *flag_host) { cudaFree(planes); return s; }        // out-of-range B: no planes, not an error
-    h->tc_hi = planes; h->tc_lo = planes + K * N; h->tc_cross_bf16 = la_tc_cross_bf16(K);
-    // the f16-split form's planes too, where it applies and B is inside its range (otherwise products with this handle use the tf32 form)
+    LA_TRY(la_host_flag(st, &flag_host, &flag));
+    // The f16-split form's planes where it applies and B is inside its range: 6 bytes per element (+ exponents, list).  A product
+    // whose A then turns out to be outside that range is done by the tf32 form from B itself, exactly as without a handle.
     if (f16_wanted(K)) {
         char* f16 = nullptr;
         LA_CUDA(cudaMalloc(&f16, K * N * 6 + f16_side_bytes(N, true)));
         flag_host[0] = 0u; flag_host[1] = 0u; flag_host[3] = 0u;
-        s = f16_prepass(F16Planes{}, F16Side{}, nullptr, 0, f16_planes(f16, K * N), f16_side(f16 + K * N * 6, N), (const float*)h->B, K, N, flag, flag + 2, st);
+        la_status s = f16_prepass(F16Planes{}, F16Side{}, nullptr, 0, f16_planes(f16, K * N), f16_side(f16 + K * N * 6, N), (const float*)h->B, K, N, flag, flag + 2, st);
         if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the f16 split of B failed");
-        if (s != LA_OK || flag_host[0]) { cudaFree(f16); flag_host[0] = 0u; return s; }
-        h->f16_planes = f16; h->f16_b_tiny = flag_host[3] != 0u; h->f16_b_sparse = flag_host[1] != 0u;
+        if (s != LA_OK) { cudaFree(f16); return s; }
+        if (!flag_host[0]) { h->f16_planes = f16; h->f16_b_tiny = flag_host[3] != 0u; h->f16_b_sparse = flag_host[1] != 0u; return LA_OK; }
+        cudaFree(f16); flag_host[0] = 0u;                       // out of the f16 form's range: the tf32 form's planes below
     }
+    float* planes = nullptr;
+    LA_CUDA(cudaMalloc(&planes, 2 * K * N * sizeof(float)));
+    *flag_host = 0u;
+    la_status s = la_tc_split_bt(planes, planes + K * N, (const float*)h->B, K, N, flag, st);
+    if (s == LA_OK && cudaStreamSynchronize(st) != cudaSuccess) s = la_fail(LA_ERR_CUDA, "la_gemm_prepare_b: the split of B failed");
+    if (s != LA_OK || *flag_host) { cudaFree(planes); return s; }        // out-of-range B: no planes, not an error
+    h->tc_hi = planes; h->tc_lo = planes + K * N; h->tc_cross_bf16 = la_tc_cross_bf16(K);
     return LA_OK;
 }

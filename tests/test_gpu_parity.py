@@ -360,6 +360,18 @@ def test_matmat_f16_split_form_handles_what_its_planes_leave_out(la):
         b2 = (rng.standard_normal(K * N).astype(np.float32).reshape(K, N) * np.exp2(rng.integers(-20, 20, N)).astype(np.float32)[None, :]).reshape(-1)
         check_f32_gemm(la, a2, b2, M, K, N, ("scaled rows and columns", M, K, N))
         assert lib.la_gemm_last_engine() == 2
+        # ragged sizes (multiples of 4 in M and N, of 8 in K)
+        Mr, Kr, Nr = 388, 2056, 260
+        ar = gen.values("f32", Mr * Kr, 87); br = gen.values("f32", Kr * Nr, 88)
+        Cr = check_f32_gemm(la, ar, br, Mr, Kr, Nr, ("ragged", Mr, Kr, Nr))
+        assert lib.la_gemm_last_engine() == 2 and lib.la_gemm_tc_last_form() == 1
+        assert same(Cr, la.Matrix.from_vec(ar, Mr, Kr).mul_prepared(la.Matrix.from_vec(br, Kr, Nr).prepare()).to_vec())
+        # an A outside the f16 form's range (a row maximum of 2^60) with a prepared B: the tf32 form, from B itself, as without a handle
+        ah = a.copy(); ah[17 * K: 18 * K] *= np.float32(2.0 ** 60)
+        Ah = la.Matrix.from_vec(ah, M, K)
+        Ch = check_f32_gemm(la, ah, b, M, K, N, ("row maximum 2^60", M, K, N))
+        assert lib.la_gemm_last_engine() == 2 and lib.la_gemm_tc_last_form() == 0
+        assert same(Ch, Ah.mul_prepared(B.prepare()).to_vec())
         # 3000 left-out elements in B: the list overflows, the tf32 form takes over
         b3 = b.copy(); b3[rng.choice(K * N, 3000, replace=False)] = 1e-14
         check_f32_gemm(la, a, b3, M, K, N, ("list overflow", M, K, N))

@@ -295,7 +295,7 @@ la_status la_mul_mat_mat_host(int dtype, void* C_host, const void* A_host, const
  *                  engine).  Falls back to SIMT for shapes it does not cover
  *                  (M, N >= 128, K >= 32, all multiples of 4), whenever an operand holds a NaN, an
  *                  infinity or a magnitude outside [2^-100, 2^100], and (from K = 1024) when a row of A or a column of B
- *                  has fewer than 16 elements within 2^-6 of its maximum -- identity, permutation, diagonal, one-hot
+ *                  sums to less than 4 times its largest magnitude -- identity, permutation, diagonal, one-hot
  *                  operands: outputs that are essentially one product, which only the exact engine computes as accurately
  *                  as the reference does (the call reads one flag back, so the
  *                  HOST blocks for the length of the pre-pass; the product itself is already queued behind

@@ -854,14 +854,14 @@ gemm_f16split_2cta_kernel(float* __restrict__ C, const __grid_constant__ CUtenso
 // scales that far apart has many, and goes to the tf32 form.
 // A second flag (word 1) asks for the exact engine: the split leaves an error of up to ~2^-21 |a||b| per PRODUCT (the dropped
 // lo*lo and the rounding of ls), which the gate's 2^-22 sum|a||b| only absorbs when an output is a sum of several comparable
-// products.  An output that is essentially one product -- a diagonal or one-hot operand, a row with one outlier -- is computed
-// exactly by the reference, so rows of A / columns of B with fewer than F16_MIN_COMPARABLE elements within 2^-6 of their maximum
-// send the product to the SIMT engine (for B counted per slice of rows: a sufficient condition).
+// products.  An output that is essentially one product -- a diagonal or one-hot operand, a row whose one outlier outweighs all the
+// rest together -- is computed exactly by the reference, so a row of A / column of B whose sum of magnitudes is less than
+// F16_MIN_MASS times its largest magnitude sends the product to the SIMT engine.  (A row with outliers 100x its typical element
+// keeps the tensor cores: over K >= 1024 the typical elements still carry most of the mass.)
 constexpr int F16_EXP_TARGET = 14;
 constexpr float F16_KEEP_MIN = 0.00390625f;      // 2^-8
 constexpr unsigned F16_TINY_CAP = 1024;
-constexpr float F16_COMPARABLE = 256.0f;         // 2^8 = 2^-6 of the smallest possible scaled maximum
-constexpr int F16_MIN_COMPARABLE = 16;
+constexpr float F16_MIN_MASS = 4.0f;
 struct F16Tiny { int row, col; float val; int pad; };
 struct F16TinyList { F16Tiny* items; unsigned* count; unsigned* any_host; };      // any_host: mapped host word, set to 1 when the list is not empty
 
@@ -890,43 +890,43 @@ __device__ __forceinline__ uint2 pack_half4(__half a, __half b, __half c, __half
     return make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
 }
 struct F16PrepassA { __half* hi; __half* hb; __half* lo; int* ea; const float* A; unsigned rows; size_t K; F16TinyList tiny; };
-struct F16PrepassB { unsigned* colmax_part; const float* B; size_t K, N; unsigned col_blocks, slices; size_t rows_per_slice; unsigned* tiny_count; };
+struct F16PrepassB { unsigned* colmax_part; float* colsum_part; const float* B; size_t K, N; unsigned col_blocks, slices; size_t rows_per_slice; unsigned* tiny_count; };
 
 // First launch of the pre-pass.  Blocks 0 .. a.rows-1: one row of A each -- pass 1 finds the row's maximum, pass 2 (the row is in
 // L2 / L1 by then) scales, splits and stores.  The blocks after them (b.col_blocks x b.slices; none when B is prepared): column
 // maxima of B over a slice of its rows, one partial row of maxima per slice (the bits of |x| compare like integers).
 __global__ void __launch_bounds__(256)
 f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
-    __shared__ float red[8];
+    __shared__ float red[8], red_mass[8];
     __shared__ float row_scale;
-    __shared__ int row_comparable;
     bool bad = false;
     if (blockIdx.x == 0 && threadIdx.x == 0 && b.tiny_count) *b.tiny_count = 0u;      // B's list is filled by the second launch
     if (blockIdx.x < a.rows) {
         const size_t row = blockIdx.x, K = a.K;
         const float4* src = reinterpret_cast<const float4*>(a.A + row * K);
         const int n4 = (int)(K / 4);
-        float m = 0.f;
+        float m = 0.f, mass = 0.f;
         for (int i = threadIdx.x; i < n4; i += 256) {
             const float4 v = __ldg(src + i);
             m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+            mass += (fabsf(v.x) + fabsf(v.y)) + (fabsf(v.z) + fabsf(v.w));
             if (!(fabsf(v.x) <= 3.4028235e38f) || !(fabsf(v.y) <= 3.4028235e38f) || !(fabsf(v.z) <= 3.4028235e38f) || !(fabsf(v.w) <= 3.4028235e38f)) m = __int_as_float(0x7f800000);
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+        for (int o = 16; o > 0; o >>= 1) { m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o)); mass += __shfl_xor_sync(0xffffffffu, mass, o); }
+        if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = m; red_mass[threadIdx.x >> 5] = mass; }
         __syncthreads();
         if (threadIdx.x == 0) {
-            float t = red[0];
+            float t = red[0], tm = red_mass[0];
 #pragma unroll
-            for (int w = 1; w < 8; ++w) t = fmaxf(t, red[w]);
+            for (int w = 1; w < 8; ++w) { t = fmaxf(t, red[w]); tm += red_mass[w]; }
+            if (t != 0.0f && t <= 3.4028235e38f && !(tm >= F16_MIN_MASS * t)) *(volatile unsigned*)(flag + 1) = 1u;      // one element outweighs the rest: exact engine
             const int e = f16_exponent_of_max(t, bad);
             a.ea[row] = e;
             row_scale = __int_as_float((127 - e) << 23);
         }
         __syncthreads();
         const float scale = row_scale;
-        int comparable = 0;
         uint2* hp = reinterpret_cast<uint2*>(a.hi + row * K);
         uint2* bp = reinterpret_cast<uint2*>(a.hb + row * K);
         uint2* lp = reinterpret_cast<uint2*>(a.lo + row * K);
@@ -938,15 +938,7 @@ f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
             __stcs(hp + i, pack_half4(h0, h1, h2, h3));
             __stcs(bp + i, pack_half4(b0, b1, b2, b3));
             __stcs(lp + i, pack_half4(l0, l1, l2, l3));
-            comparable += (fabsf(v.x * scale) >= F16_COMPARABLE) + (fabsf(v.y * scale) >= F16_COMPARABLE) + (fabsf(v.z * scale) >= F16_COMPARABLE) + (fabsf(v.w * scale) >= F16_COMPARABLE);
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) comparable += __shfl_xor_sync(0xffffffffu, comparable, o);
-        if (threadIdx.x == 0) row_comparable = 0;
-        __syncthreads();
-        if ((threadIdx.x & 31) == 0 && comparable) atomicAdd(&row_comparable, comparable);
-        __syncthreads();
-        if (threadIdx.x == 0 && row_comparable > 0 && row_comparable < F16_MIN_COMPARABLE) *(volatile unsigned*)(flag + 1) = 1u;     // (0: an all-zero row)
     } else {
         const unsigned c = blockIdx.x - a.rows;
         const size_t c4 = (size_t)(c % b.col_blocks) * 256 + threadIdx.x;          // float4 column index
@@ -954,6 +946,7 @@ f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
         if (c4 * 4 < b.N) {
             const size_t k0 = (size_t)slice * b.rows_per_slice, k1 = min(b.K, k0 + b.rows_per_slice);
             unsigned m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
             size_t k = k0;
             for (; k + 4 <= k1; k += 4) {                                             // four rows in flight
                 float4 v[4];
@@ -963,14 +956,17 @@ f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
                 for (int u = 0; u < 4; ++u) {
                     m0 = max(m0, __float_as_uint(v[u].x) & 0x7fffffffu); m1 = max(m1, __float_as_uint(v[u].y) & 0x7fffffffu);
                     m2 = max(m2, __float_as_uint(v[u].z) & 0x7fffffffu); m3 = max(m3, __float_as_uint(v[u].w) & 0x7fffffffu);
+                    s0 += fabsf(v[u].x); s1 += fabsf(v[u].y); s2 += fabsf(v[u].z); s3 += fabsf(v[u].w);
                 }
             }
             for (; k < k1; ++k) {
                 const float4 v = __ldcs(reinterpret_cast<const float4*>(b.B + k * b.N) + c4);
                 m0 = max(m0, __float_as_uint(v.x) & 0x7fffffffu); m1 = max(m1, __float_as_uint(v.y) & 0x7fffffffu);
                 m2 = max(m2, __float_as_uint(v.z) & 0x7fffffffu); m3 = max(m3, __float_as_uint(v.w) & 0x7fffffffu);
+                s0 += fabsf(v.x); s1 += fabsf(v.y); s2 += fabsf(v.z); s3 += fabsf(v.w);
             }
             *reinterpret_cast<uint4*>(b.colmax_part + (size_t)slice * b.N + c4 * 4) = make_uint4(m0, m1, m2, m3);
+            *reinterpret_cast<float4*>(b.colsum_part + (size_t)slice * b.N + c4 * 4) = make_float4(s0, s1, s2, s3);
         }
     }
     if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;
@@ -980,7 +976,7 @@ f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
 // shared memory as split_transpose_kernel does; the column exponents come from the partial maxima of the first launch.
 __global__ void __launch_bounds__(256)
 f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_hb, __half* __restrict__ bt_lo, int* __restrict__ eb,
-                           const unsigned* __restrict__ colmax_part, unsigned slices, const float* __restrict__ B, size_t K, size_t N, unsigned tiles_n,
+                           const unsigned* __restrict__ colmax_part, const float* __restrict__ colsum_part, unsigned slices, const float* __restrict__ B, size_t K, size_t N, unsigned tiles_n,
                            const F16TinyList tiny, unsigned* flag) {
     __shared__ float tile[64][65];
     __shared__ float col_scale[64];
@@ -1008,14 +1004,16 @@ f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_h
         bad |= col_bad;
         const float scale_n = __int_as_float((127 - e) << 23);
         if (g == 0) { col_scale[c] = scale_n; if (k0 == 0 && col_ok) eb[n0 + c] = e; }
-        if (k0 == 0) {                       // (once per column) slices of rows that hold an element within 2^-6 of the column's scaled 2^14
-            unsigned with = 0;
-            if (col_ok && m != 0u && !col_bad) for (unsigned sl = g; sl < slices; sl += 4) with += __uint_as_float(colmax_part[(size_t)sl * N + n0 + c]) * scale_n >= F16_COMPARABLE;
+        if (k0 == 0) {                       // (once per column) its sum of magnitudes against its maximum
+            float mass = 0.f;
+            if (col_ok) for (unsigned sl = g; sl < slices; sl += 4) mass += colsum_part[(size_t)sl * N + n0 + c];
             __syncthreads();
-            part_max[g][c] = with;
+            part_max[g][c] = __float_as_uint(mass);
             __syncthreads();
-            if (g == 0 && col_ok && m != 0u && !col_bad &&
-                part_max[0][c] + part_max[1][c] + part_max[2][c] + part_max[3][c] < min((unsigned)F16_MIN_COMPARABLE, slices)) *(volatile unsigned*)(flag + 1) = 1u;
+            if (g == 0 && col_ok && m != 0u && !col_bad) {
+                const float total = (__uint_as_float(part_max[0][c]) + __uint_as_float(part_max[1][c])) + (__uint_as_float(part_max[2][c]) + __uint_as_float(part_max[3][c]));
+                if (!(total >= F16_MIN_MASS * __uint_as_float(m))) *(volatile unsigned*)(flag + 1) = 1u;
+            }
         }
     }
 #pragma unroll
@@ -1600,16 +1598,17 @@ F16Planes f16_planes(void* base, size_t elems) {
     return p;
 }
 // Scratch of one operand's pre-pass beyond its planes: exponents, the list of left-out elements, and (B) the partial column maxima.
-struct F16Side { int* e; F16Tiny* items; unsigned* count; unsigned* colmax_part; };
+struct F16Side { int* e; F16Tiny* items; unsigned* count; unsigned* colmax_part; float* colsum_part; };
 constexpr unsigned F16_MAX_SLICES = 32;
 size_t f16_side_bytes(size_t n, bool with_colmax) {              // n = M (A) or N (B)
     const size_t n4 = (n + 3) / 4 * 4;
-    return n4 * sizeof(int) + F16_TINY_CAP * sizeof(F16Tiny) + 16 + (with_colmax ? (size_t)F16_MAX_SLICES * n4 * sizeof(unsigned) : 0);
+    return n4 * sizeof(int) + F16_TINY_CAP * sizeof(F16Tiny) + 16 + (with_colmax ? 2 * (size_t)F16_MAX_SLICES * n4 * sizeof(unsigned) : 0);
 }
 F16Side f16_side(char* base, size_t n) {
     const size_t n4 = (n + 3) / 4 * 4;
     F16Side s; s.e = (int*)base; s.items = (F16Tiny*)(base + n4 * sizeof(int)); s.count = (unsigned*)(base + n4 * sizeof(int) + F16_TINY_CAP * sizeof(F16Tiny));
     s.colmax_part = (unsigned*)((char*)s.count + 16);
+    s.colsum_part = (float*)(s.colmax_part + (size_t)F16_MAX_SLICES * n4);
     return s;
 }
 // The pre-pass: A's rows and (unless B is prepared: `B == nullptr`) B's column maxima in one launch, then B's transposing split.
@@ -1627,7 +1626,7 @@ la_status f16_prepass(F16Planes a, F16Side sa, const float* A, size_t M, F16Plan
     unsigned b_blocks = 0;
     if (B) {
         pb.tiny_count = sb.count;
-        pb.colmax_part = sb.colmax_part; pb.B = B; pb.K = K; pb.N = N;
+        pb.colmax_part = sb.colmax_part; pb.colsum_part = sb.colsum_part; pb.B = B; pb.K = K; pb.N = N;
         pb.col_blocks = (unsigned)((N / 4 + 255) / 256);
         size_t slices = std::max<size_t>(1, (size_t)info->sm_count * 8 / pb.col_blocks);
         slices = std::min<size_t>(std::min<size_t>(slices, F16_MAX_SLICES), K);
@@ -1641,7 +1640,7 @@ la_status f16_prepass(F16Planes a, F16Side sa, const float* A, size_t M, F16Plan
         const size_t tk = (K + 63) / 64, tn = (N + 63) / 64;
         if (tk * tn > 0x7fffffffull) return la_fail(LA_ERR_UNSUPPORTED, "f16-split pre-pass: B is too large");
         f16_split_transpose_kernel<<<(unsigned)(tk * tn), 256, 0, st>>>(const_cast<__half*>(bt.hi), const_cast<__half*>(bt.hb), const_cast<__half*>(bt.lb), sb.e,
-                                                                        sb.colmax_part, pb.slices, B, K, N, (unsigned)tn, F16TinyList{sb.items, sb.count, any_dev + 1}, flag);
+                                                                        sb.colmax_part, sb.colsum_part, pb.slices, B, K, N, (unsigned)tn, F16TinyList{sb.items, sb.count, any_dev + 1}, flag);
         LA_LAUNCH_CHECK();
     }
     return LA_OK;

@@ -387,7 +387,7 @@ def test_matmat_one_product_outputs_go_to_the_exact_engine(la):
     """A split product carries an error of up to ~2^-21 |a||b| per PRODUCT, which the gate only absorbs in a sum of several
     comparable products.  B = identity / permutation / diagonal, one-hot rows, a row with one outlier: every output is essentially
     one product, which the reference computes exactly -- and so must we (the f16-split form's pre-pass spots rows of A / columns
-    of B with fewer than 16 elements within 2^-6 of their maximum and hands the product to the SIMT engine)."""
+    of B whose sum of magnitudes is less than 4 times their largest magnitude and hands the product to the SIMT engine)."""
     lib = la._lib.lib; P = oracle.port()
     M = K = N = 1024
     rng = np.random.default_rng(9)
@@ -408,6 +408,10 @@ def test_matmat_one_product_outputs_go_to_the_exact_engine(la):
     C = (la.Matrix.from_vec(a1.reshape(-1), M, K) * la.Matrix.from_vec(b1, K, N)).to_vec()
     assert lib.la_gemm_last_engine() in (0, 1)
     assert same(C, P.mul_mat_mat(a1.reshape(-1), b1, M, K, N, fma=True))
+    # ... but outliers that do not outweigh the rest of their row (100 x the typical element, K = 1024) keep the tensor cores
+    a2 = rng.standard_normal(M * K).astype(np.float32).reshape(M, K); a2[np.arange(M), rng.integers(0, K, M)] = 100.0
+    check_f32_gemm(la, a2.reshape(-1), b1, M, K, N, ("outliers 100 x typical", M, K, N))
+    assert lib.la_gemm_last_engine() == 2 and lib.la_gemm_tc_last_form() == 1
 
 
 def test_matmat_tf32_form_still_meets_the_bar_from_k_1024(la):

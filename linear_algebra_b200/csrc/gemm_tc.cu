@@ -2,36 +2,42 @@
 // multiply-adds up when K >= 256).
 //
 // Same contract as the SIMT engine in gemm.cu ({T}_mul_mat_mat, src/kernels.cl:161-169), other arithmetic: every f32
-// operand is split x = hi + lo with hi = tf32(x) (round to nearest), and each product is formed as hi*hi + hi*lo + lo*hi
-// on the 5th-generation tensor cores with FP32 accumulation in tensor memory:
-//   K < 1024    three tcgen05.mma kind::tf32 per k-step ("3xTF32"), lo = tf32(x - hi);
-//   K >= 1024   hi*hi as kind::tf32, the two cross terms (2^-11 of the weight) as kind::f16 bf16 MMAs at twice the rate
-//               on the planes bf16(hi) and bf16(x - hi): 2 tensor time units per product instead of 3.
+// operand is split x = hi + lo with an 11-bit hi, and each product is formed as hi*hi + hi*lo + lo*hi on the 5th-generation
+// tensor cores with FP32 accumulation in tensor memory, in one of two operand formats:
+//   tf32 form  (256 <= K < 1024; K % 8 != 0; operands outside the other form's range)   hi = tf32(x), lo = tf32(x - hi), three
+//              tcgen05.mma kind::tf32 per k-step ("3xTF32"): 3 tensor time units per product
+//   f16 form   (K >= 1024)   rows of A / columns of B scaled by powers of two into fp16's range, three fp16 planes (hi, hi * 2^-6,
+//              (x - hi) * 2^6), three kind::f16 MMAs at twice the rate: 1.5 units per product, 6 bytes of planes per element;
+//              elements far below their row's maximum are left out of the planes and added afterwards in f32; operands with
+//              one-product outputs (identity, diagonal, ...) are handed to the exact engine -- see gemm_f16split_2cta_kernel
 // The dropped lo*lo term is below 2^-22 relative.  Accumulation runs in chains of 32 .. 256 k inside the tensor cores
 // (their FP32 accumulation truncates) and in FP32 registers across chains.  Results stay inside the f32 bar of DESIGN.md
-// section 4 -- tests/test_gpu_parity.py gates every cross-term type / chain length / tile width on it, on random and on
+// section 4 -- tests/test_gpu_parity.py gates both forms / every chain length / tile width on it, on random and on
 // structured data; la_set_gemm_mode(LA_GEMM_SIMT) switches the engine off.
 //
-// Kernels in this file (la_gemm_tc_set_variant picks one; 0 is the default):
+// Kernels in this file (la_gemm_tc_set_variant picks one of the tf32 form's; 0 is the default):
+//   -  gemm_f16split_2cta_kernel<BN>      the f16 form: CTA pairs, 4-stage ring of six 8 KB planes, otherwise as the next one
 //   0  gemm_3xtf32_2cta_kernel<BN, BF16X>  CTA pairs (tcgen05 cta_group::2), 256 x BN tile per pair (BN = 256 / 224 / 192 by
 //                                   wave count), 3-stage TMA ring, work items = (tile, chain range) so the ragged last
-//                                   wave can be cut in two along K, banded tile order above 4096 rows
+//                                   wave can be cut in two along K, banded tile order above 4096 rows; BF16X = the cross
+//                                   terms as bf16 MMAs on bf16(hi), bf16(x - hi) planes (2 units; a tuning setting: ~2^-20
+//                                   per product, above the gate for one-product outputs)
 //   5/3 gemm_3xtf32_chunked_kernel  one CTA per 128x256 tile (with / without B multicast), 64-chains  (tuning references)
 //   1/2 gemm_3xtf32_kernel          single accumulation chain (tuning reference; drifts)
 // Common structure:
-//   pre-pass   split_tf32_kernel       A -> A_hi + (A_lo | bf16(A_hi), bf16(A - A_hi))                 (scratch)
-//              split_transpose_kernel  B -> the same planes of B^T (N x K), so both operands are K-major    (scratch)
+//   pre-pass   tf32 form: split_both_kernel / split_tf32_kernel / split_transpose_kernel -- A's planes and the same planes of B^T
+//              (N x K), so both operands are K-major; f16 form: f16_prepass1_kernel (A's rows; B's column maxima and sums),
+//              f16_split_transpose_kernel (B^T's planes), f16_tiny_fix_kernel after the product          (all in scratch)
 //   TMA warp   cp.async.bulk.tensor.2d of the slabs of a 32-wide k-block (128-byte rows / SWIZZLE_128B for tf32 planes,
-//              64-byte rows / SWIZZLE_64B for bf16 planes) into a ring guarded by full/empty mbarriers
+//              64-byte rows / SWIZZLE_64B for 16-bit planes) into a ring guarded by full/empty mbarriers
 //   MMA warp   owns tensor memory; one elected lane issues the MMAs of a k-block and tcgen05.commit's the stage back
 //   epilogue   tcgen05.ld of the FP32 accumulator after every chain, FP32 adds in registers, 16-byte streaming stores to C
 //              (atomicAdd of the two halves for a tile cut along K)
-// Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-pass detects anything
-// outside [2^-100, 2^100] (or NaN) and the call then runs the SIMT engine over the same C, so the tensor engine never
-// changes the result class of a product.
-// Roofline: tensor pipe, 3 (K < 1024) or 2 tf32-equivalent MMA units per useful product; in the second form the kernel is
-// at 90 % of that floor with the L2 -> SM path (11.6 TB/s of operand loads at 8192^3) close to its own limit, see the
-// note in the producer loop.
+// Non-finite inputs: inf * (lo == 0) would be NaN, and tiny values lose their lo part; the pre-passes detect NaN / inf and
+// magnitudes outside their form's range ([2^-40, 2^40] for row / column maxima of the f16 form, [2^-100, 2^100] for the tf32
+// form) and the call then runs the next engine over the same C, so the tensor engine never changes the result class of a product.
+// Roofline: tensor pipe, 1.5 (f16 form) or 3 (tf32 form) tf32-equivalent MMA units per useful product; the f16 form's kernel runs
+// at 0.80 - 0.84 of that floor at 8192^3 (tensor pipe 82 % active).
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include "tc_common.cuh"

@@ -366,6 +366,9 @@ def test_matmat_f16_split_form_handles_what_its_planes_leave_out(la):
         Cr = check_f32_gemm(la, ar, br, Mr, Kr, Nr, ("ragged", Mr, Kr, Nr))
         assert lib.la_gemm_last_engine() == 2 and lib.la_gemm_tc_last_form() == 1
         assert same(Cr, la.Matrix.from_vec(ar, Mr, Kr).mul_prepared(la.Matrix.from_vec(br, Kr, Nr).prepare()).to_vec())
+        for Ms, Ks, Ns in ((132, 1024, 136), (256, 1032, 1028), (1000, 4104, 516)):
+            check_f32_gemm(la, gen.values("f32", Ms * Ks, 89), gen.values("f32", Ks * Ns, 90), Ms, Ks, Ns, ("small / ragged", Ms, Ks, Ns))
+            assert lib.la_gemm_last_engine() == 2 and lib.la_gemm_tc_last_form() == 1
         # an A outside the f16 form's range (a row maximum of 2^60) with a prepared B: the tf32 form, from B itself, as without a handle
         ah = a.copy(); ah[17 * K: 18 * K] *= np.float32(2.0 ** 60)
         Ah = la.Matrix.from_vec(ah, M, K)

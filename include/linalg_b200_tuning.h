@@ -33,7 +33,7 @@ int la_gemm_tc_last_form(void);                    /* this thread's last f32 ten
 int la_gemm_tc_last_launches(void);                /* ... and the kernels it launched (pre-pass, product, fix-ups of left-out elements) */
 la_status la_gemm_tc_set_f16(int mode);            /* f16-split form of the engine (row / column scaled operands, hi = fp16, lo = bf16, three 16-bit MMAs per product): -1 by K (default: from K = 1024), 0 never, 1 wherever the shapes allow (K >= 256, K % 8 == 0) */
 la_status la_gemm_tc_set_a_direct(int on);         /* EXPERIMENT: A is read in place as its own hi plane (hardware truncation to tf32), lo taken against the truncated value */
-la_status la_gemm_tc_set_cross(int mode);          /* cross terms: -1 by K, 0 tf32, 1 bf16 (below K = 1024 gated at twice the reference order's error) */
+la_status la_gemm_tc_set_cross(int mode);          /* tf32 form: cross terms as tf32 MMAs (-1 / 0, the default at every K) or as bf16 MMAs at twice the rate (1; ~2^-20 per product: gated at twice the reference order's error below K = 1024, and above the gate for one-product outputs such as B = identity) */
 la_status la_gemm_tc_set_tile_n(int bn);           /* pair tile width 256 / 224 / 192; 0 = by wave count; bit-identical results with the K-split off */
 la_status la_gemm_set_stream_tail(int mode);       /* K-split of the ragged last wave: -1 by gain model, 0 off, 1 whenever possible */
 la_status la_gemm_set_raster(int tile_rows);       /* band height of the tile walk: -1 by size, 0 m-major; bit-identical results */

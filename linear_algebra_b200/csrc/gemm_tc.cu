@@ -891,9 +891,25 @@ __device__ __forceinline__ void f16_split_one(float x, float scale, int row, int
     ls = __float2half_rn((xs - h) * 64.0f);                       // (x - hi) * 2^6: at most 2^10, and 11 bits of it survive down to |x| = 2^-8
     bad |= !(fabsf(x) <= 3.4028235e38f);                          // NaN / inf
 }
-__device__ __forceinline__ uint2 pack_half4(__half a, __half b, __half c, __half d) {
-    const __half2 p0 = __halves2half2(a, b), p1 = __halves2half2(c, d);
-    return make_uint2(*reinterpret_cast<const uint32_t*>(&p0), *reinterpret_cast<const uint32_t*>(&p1));
+// Two elements at once: packed conversions (one F2FP per pair instead of a scalar F2F per element, which is what bounded the
+// pre-pass), hs = hi * 2^-6 as an exact half2 multiply.  Same bits as f16_split_one.
+__device__ __forceinline__ void f16_split_two(float x0, float x1, float scale, int row0, int col0, int row1, int col1, const F16TinyList& tiny,
+                                              uint32_t& hi, uint32_t& hs, uint32_t& ls, bool& bad) {
+    float s0 = x0 * scale, s1 = x1 * scale;
+    if ((fabsf(s0) < F16_KEEP_MIN && x0 != 0.0f) || (fabsf(s1) < F16_KEEP_MIN && x1 != 0.0f)) {      // rare: the scalar path notes them
+        __half h0, h1, a0, a1, l0, l1;
+        f16_split_one(x0, scale, row0, col0, tiny, h0, a0, l0, bad);
+        f16_split_one(x1, scale, row1, col1, tiny, h1, a1, l1, bad);
+        const __half2 ph = __halves2half2(h0, h1), pa = __halves2half2(a0, a1), pl = __halves2half2(l0, l1);
+        hi = *reinterpret_cast<const uint32_t*>(&ph); hs = *reinterpret_cast<const uint32_t*>(&pa); ls = *reinterpret_cast<const uint32_t*>(&pl);
+        return;
+    }
+    const __half2 h = __floats2half2_rn(s0, s1);
+    const float2 hf = __half22float2(h);
+    const __half2 a = __hmul2(h, __floats2half2_rn(0.015625f, 0.015625f));
+    const __half2 l = __floats2half2_rn((s0 - hf.x) * 64.0f, (s1 - hf.y) * 64.0f);
+    hi = *reinterpret_cast<const uint32_t*>(&h); hs = *reinterpret_cast<const uint32_t*>(&a); ls = *reinterpret_cast<const uint32_t*>(&l);
+    bad |= !(fabsf(x0) <= 3.4028235e38f) || !(fabsf(x1) <= 3.4028235e38f);
 }
 struct F16PrepassA { __half* hi; __half* hb; __half* lo; int* ea; const float* A; unsigned rows; size_t K; F16TinyList tiny; };
 struct F16PrepassB { unsigned* colmax_part; float* colsum_part; const float* B; size_t K, N; unsigned col_blocks, slices; size_t rows_per_slice; unsigned* tiny_count; };
@@ -938,12 +954,12 @@ f16_prepass1_kernel(const F16PrepassA a, const F16PrepassB b, unsigned* flag) {
         uint2* lp = reinterpret_cast<uint2*>(a.lo + row * K);
         for (int i = threadIdx.x; i < n4; i += 256) {
             const float4 v = __ldg(src + i);
-            __half h0, h1, h2, h3, b0, b1, b2, b3, l0, l1, l2, l3;
-            f16_split_one(v.x, scale, (int)row, 4 * i + 0, a.tiny, h0, b0, l0, bad); f16_split_one(v.y, scale, (int)row, 4 * i + 1, a.tiny, h1, b1, l1, bad);
-            f16_split_one(v.z, scale, (int)row, 4 * i + 2, a.tiny, h2, b2, l2, bad); f16_split_one(v.w, scale, (int)row, 4 * i + 3, a.tiny, h3, b3, l3, bad);
-            __stcs(hp + i, pack_half4(h0, h1, h2, h3));
-            __stcs(bp + i, pack_half4(b0, b1, b2, b3));
-            __stcs(lp + i, pack_half4(l0, l1, l2, l3));
+            uint2 h, b, l;
+            f16_split_two(v.x, v.y, scale, (int)row, 4 * i + 0, (int)row, 4 * i + 1, a.tiny, h.x, b.x, l.x, bad);
+            f16_split_two(v.z, v.w, scale, (int)row, 4 * i + 2, (int)row, 4 * i + 3, a.tiny, h.y, b.y, l.y, bad);
+            __stcs(hp + i, h);
+            __stcs(bp + i, b);
+            __stcs(lp + i, l);
         }
     } else {
         const unsigned c = blockIdx.x - a.rows;
@@ -1033,14 +1049,14 @@ f16_split_transpose_kernel(__half* __restrict__ bt_hi, __half* __restrict__ bt_h
         const int idx = threadIdx.x + j * 256, cc = idx / 16, q = idx % 16;      // Bt row n0+cc, columns k0 + q*4 ..
         const float scale = col_scale[cc];
         const int kk = (int)k0 + q * 4, nn = (int)n0 + cc;
-        __half h0, h1, h2, h3, b0, b1, b2, b3, l0, l1, l2, l3;
-        f16_split_one(tile[q * 4 + 0][cc], scale, kk + 0, nn, tiny, h0, b0, l0, bad); f16_split_one(tile[q * 4 + 1][cc], scale, kk + 1, nn, tiny, h1, b1, l1, bad);
-        f16_split_one(tile[q * 4 + 2][cc], scale, kk + 2, nn, tiny, h2, b2, l2, bad); f16_split_one(tile[q * 4 + 3][cc], scale, kk + 3, nn, tiny, h3, b3, l3, bad);
+        uint2 h, b, l;
+        f16_split_two(tile[q * 4 + 0][cc], tile[q * 4 + 1][cc], scale, kk + 0, nn, kk + 1, nn, tiny, h.x, b.x, l.x, bad);
+        f16_split_two(tile[q * 4 + 2][cc], tile[q * 4 + 3][cc], scale, kk + 2, nn, kk + 3, nn, tiny, h.y, b.y, l.y, bad);
         if (n0 + cc < N && k0 + q * 4 < K) {
             const size_t at = (n0 + cc) * K + k0 + q * 4;
-            __stcs(reinterpret_cast<uint2*>(bt_hi + at), pack_half4(h0, h1, h2, h3));
-            __stcs(reinterpret_cast<uint2*>(bt_hb + at), pack_half4(b0, b1, b2, b3));
-            __stcs(reinterpret_cast<uint2*>(bt_lo + at), pack_half4(l0, l1, l2, l3));
+            __stcs(reinterpret_cast<uint2*>(bt_hi + at), h);
+            __stcs(reinterpret_cast<uint2*>(bt_hb + at), b);
+            __stcs(reinterpret_cast<uint2*>(bt_lo + at), l);
         }
     }
     if (__syncthreads_or(bad) && threadIdx.x == 0) *(volatile unsigned*)flag = 1u;
